@@ -1,0 +1,189 @@
+// extern "C" boundary: argument validation, exception -> status code translation.
+#include "../../include/dmb200.h"
+
+#include "engine.cuh"
+
+struct dmb_ctx {
+  dmb::IEngine* eng;
+  int device;
+};
+
+namespace {
+thread_local std::string g_last_error;
+
+template <typename F>
+int guarded(F&& fn) {
+  try {
+    fn();
+    return DMB_OK;
+  } catch (const dmb::Error& e) {
+    g_last_error = e.msg;
+    return e.code ? e.code : 1;
+  } catch (const std::exception& e) {
+    g_last_error = std::string("internal error: ") + e.what();
+    return 1;
+  } catch (...) {
+    g_last_error = "internal error";
+    return 1;
+  }
+}
+
+dmb::TensorMapIn collect(int n, const char* const* names, const void* const* ptrs, const int64_t* numels) {
+  DMB_REQUIRE(n > 0 && names && ptrs && numels, "empty weight list");
+  dmb::TensorMapIn m;
+  for (int i = 0; i < n; ++i) {
+    DMB_REQUIRE(names[i] && ptrs[i] && numels[i] > 0, "null entry in weight list");
+    m[names[i]] = dmb::TensorRef{ptrs[i], numels[i]};
+  }
+  return m;
+}
+inline cudaStream_t st(void* s) { return static_cast<cudaStream_t>(s); }
+inline const long long* ll(const int64_t* p) { return reinterpret_cast<const long long*>(p); }
+}  // namespace
+
+extern "C" {
+
+int dmb_abi_version(void) { return 1; }
+const char* dmb_last_error_string(void) { return g_last_error.c_str(); }
+
+int dmb_ctx_create(int device, int precision, dmb_ctx** out) {
+  return guarded([&] {
+    DMB_REQUIRE(out != nullptr, "out is NULL");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) dmb::fail(4, "no CUDA device available: this library has no CPU fallback");
+    DMB_REQUIRE(device >= 0 && device < count, "device ordinal out of range");
+    dmb::IEngine* eng = nullptr;
+    if (precision == DMB_PRECISION_BF16) eng = dmb::make_engine_bf16(device);
+    else if (precision == DMB_PRECISION_TF32) eng = dmb::make_engine_f32(device);
+    else dmb::fail(2, "invalid argument: unknown precision mode");
+    *out = new dmb_ctx{eng, device};
+  });
+}
+
+int dmb_ctx_destroy(dmb_ctx* ctx) {
+  return guarded([&] {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    delete ctx->eng;
+    delete ctx;
+  });
+}
+
+int dmb_load_unet_weights(dmb_ctx* ctx, int n, const char* const* names, const void* const* ptrs,
+                          const int64_t* numels) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx, "ctx is NULL");
+    ctx->eng->load_unet(collect(n, names, ptrs, numels));
+  });
+}
+
+int dmb_load_vae_dec_weights(dmb_ctx* ctx, int n, const char* const* names, const void* const* ptrs,
+                             const int64_t* numels) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx, "ctx is NULL");
+    ctx->eng->load_vae(collect(n, names, ptrs, numels));
+  });
+}
+
+int dmb_unet_forward(dmb_ctx* ctx, const float* x, const int64_t* t, const int64_t* y, const float* vals,
+                     const float* mask, int B, float* eps_out, float* geom_out, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && x && t && y, "ctx, x, t and y are required");
+    DMB_REQUIRE((vals == nullptr) == (mask == nullptr), "cond_vals and cond_mask must be given together");
+    ctx->eng->unet_forward(x, ll(t), ll(y), vals, mask, B, eps_out, geom_out, st(stream));
+  });
+}
+
+int dmb_denoise_cond_step(dmb_ctx* ctx, const float* x_in, const int64_t* t, const int64_t* y, int null_label,
+                          const float* vals, const float* mask, float guidance_scale, const float* coef, int T,
+                          const float* noise, uint64_t seed, uint64_t sample_offset, float* x_out,
+                          float* eps_out, int B, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && x_in && t && y && coef && x_out, "ctx, x_in, t, y, coef and x_out are required");
+    DMB_REQUIRE((vals == nullptr) == (mask == nullptr), "cond_vals and cond_mask must be given together");
+    DMB_REQUIRE(null_label >= 0 && null_label <= 3, "null_label must index class_emb (0..3)");
+    DMB_REQUIRE(T >= 1, "T must be >= 1");
+    ctx->eng->cfg_step(x_in, ll(t), ll(y), null_label, vals, mask, guidance_scale, coef, T, noise, seed,
+                       sample_offset, x_out, eps_out, B, st(stream));
+  });
+}
+
+int dmb_sample_loop(dmb_ctx* ctx, float* x, const int64_t* y, int null_label, const float* vals,
+                    const float* mask, float guidance_scale, const float* coef, int T, int t_start, int n_steps,
+                    const float* noise, uint64_t seed, uint64_t sample_offset, float* x_dump, float* eps_dump,
+                    int B, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && x && y && coef, "ctx, x, y and coef are required");
+    DMB_REQUIRE((vals == nullptr) == (mask == nullptr), "cond_vals and cond_mask must be given together");
+    DMB_REQUIRE(null_label >= 0 && null_label <= 3, "null_label must index class_emb (0..3)");
+    ctx->eng->sample_loop(x, ll(y), null_label, vals, mask, guidance_scale, coef, T, t_start, n_steps, noise, seed,
+                          sample_offset, x_dump, eps_dump, B, st(stream));
+  });
+}
+
+int dmb_vae_decode(dmb_ctx* ctx, const float* z, int B, float* img_f32, uint8_t* img_u8, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && z, "ctx and z are required");
+    DMB_REQUIRE(img_f32 || img_u8, "at least one output buffer is required");
+    ctx->eng->vae_decode(z, B, img_f32, img_u8, st(stream));
+  });
+}
+
+int dmb_philox_normal(dmb_ctx* ctx, float* out, int B, uint64_t seed, uint64_t sample_offset, int t,
+                      void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && out && B >= 1, "ctx, out and B >= 1 are required");
+    DMB_CUDA(cudaSetDevice(ctx->device));
+    const int HW = dmb::kLatH * dmb::kLatW;
+    dmb::philox_fill_kernel<<<dim3((HW + 127) / 128, B), 128, 0, st(stream)>>>(out, B, HW, seed, sample_offset,
+                                                                              static_cast<unsigned int>(t));
+    DMB_CHECK_LAUNCH();
+  });
+}
+
+int64_t dmb_launch_count(dmb_ctx* ctx) { return ctx ? ctx->eng->launches() : -1; }
+int dmb_reset_launch_count(dmb_ctx* ctx) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx, "ctx is NULL");
+    ctx->eng->reset_launches();
+  });
+}
+
+int dmb_debug_get_tap(dmb_ctx* ctx, const char* name, float* out, int64_t capacity, int64_t* shape4,
+                      void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && name && out && shape4, "ctx, name, out and shape4 are required");
+    ctx->eng->get_tap(name, out, capacity, shape4, st(stream));
+  });
+}
+
+int dmb_op_conv3x3(dmb_ctx* ctx, const float* x, const float* w, int B, int Cin, int Cout, int H, int W,
+                   float* out, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && x && w && out, "ctx, x, w and out are required");
+    DMB_REQUIRE(B >= 1 && Cin >= 1 && Cout >= 1 && H >= 1 && W >= 1, "sizes must be positive");
+    ctx->eng->op_conv3x3(x, w, B, Cin, Cout, H, W, out, st(stream));
+  });
+}
+
+int dmb_op_linear(dmb_ctx* ctx, const float* x, const float* w, const float* bias, int rows, int K, int N,
+                  int act, float* out, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && x && w && out, "ctx, x, w and out are required");
+    DMB_REQUIRE(rows >= 1 && K >= 1 && N >= 1, "sizes must be positive");
+    ctx->eng->op_linear(x, w, bias, rows, K, N, act, out, st(stream));
+  });
+}
+
+int dmb_op_conv_transpose4x4(dmb_ctx* ctx, const float* x, const float* w, const float* bias, int B, int Cin,
+                             int Cout, int H, int W, float* out, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && x && w && out, "ctx, x, w and out are required");
+    DMB_REQUIRE(B >= 1 && Cin >= 1 && Cout >= 1 && H >= 1 && W >= 1, "sizes must be positive");
+    ctx->eng->op_convT4x4(x, w, bias, B, Cin, Cout, H, W, out, st(stream));
+  });
+}
+
+}  // extern "C"

@@ -1,0 +1,283 @@
+// Shared device/host helpers for the sm_100a kernels: error plumbing, the padded
+// pixel-matrix geometry, bf16/fp32 vector access, and the PTX wrappers for mbarrier,
+// TMA (cp.async.bulk.tensor) and tcgen05 (alloc / mma / commit / ld).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+namespace dmb {
+
+// ---------------------------------------------------------------------------
+// Errors.  No exception crosses the C ABI: every entry point catches Error and
+// turns it into a status code + dmb_last_error_string().
+// ---------------------------------------------------------------------------
+struct Error {
+  int code;
+  std::string msg;
+};
+
+[[noreturn]] void fail(int code, const std::string& msg);
+void cuda_check(cudaError_t e, const char* what, const char* file, int line);
+
+#define DMB_CUDA(x) ::dmb::cuda_check((x), #x, __FILE__, __LINE__)
+#define DMB_CHECK_LAUNCH() ::dmb::cuda_check(cudaPeekAtLastError(), "kernel launch", __FILE__, __LINE__)
+#define DMB_REQUIRE(cond, msg)                                        \
+  do {                                                                \
+    if (!(cond)) ::dmb::fail(2, std::string("invalid argument: ") + (msg)); \
+  } while (0)
+
+// ---------------------------------------------------------------------------
+// Geometry of a feature map stored as a padded pixel matrix ("PM"):
+//   rows  = pixels of all samples, channels contiguous per row (NHWC),
+//   every image row carries ONE trailing zero pixel and every image ONE leading
+//   zero row, so that row r + dy*Wp + dx is the (dy,dx) neighbour of pixel r and
+//   lands on a zero pixel whenever the neighbour is outside the image.
+//   One extra zero row closes the last image.  Kernels write real pixels only;
+//   pad pixels keep the zeros of the initial memset.
+// ---------------------------------------------------------------------------
+struct Geo {
+  int n;   // samples
+  int H, W;
+  int Wp;  // W + 1
+  int S;   // (H + 1) * Wp rows per sample
+  int rows_valid;  // n * S
+  int rows_alloc;  // rows_valid + Wp, rounded up to 128
+};
+
+inline Geo make_geo(int n, int H, int W) {
+  Geo g;
+  g.n = n; g.H = H; g.W = W; g.Wp = W + 1; g.S = (H + 1) * (W + 1);
+  g.rows_valid = n * g.S;
+  g.rows_alloc = ((g.rows_valid + g.Wp + 127) / 128) * 128;
+  return g;
+}
+
+__host__ __device__ inline int geo_row(const Geo& g, int b, int y, int x) {
+  return b * g.S + (y + 1) * g.Wp + x;
+}
+
+// Decompose a PM row; returns false on pad pixels.
+__device__ __forceinline__ bool geo_decode(const Geo& g, int r, int& b, int& y, int& x) {
+  if (r < 0 || r >= g.rows_valid) return false;
+  b = r / g.S;
+  int rr = r - b * g.S;
+  int yy = rr / g.Wp;
+  x = rr - yy * g.Wp;
+  y = yy - 1;
+  return yy >= 1 && x < g.W;
+}
+
+// ---------------------------------------------------------------------------
+// Activation element types.  bf16 mode stores activations as bf16 and feeds
+// tcgen05 kind::f16; fp32 mode stores fp32 and feeds kind::tf32.
+// ---------------------------------------------------------------------------
+template <typename T> struct ElemTraits;
+template <> struct ElemTraits<__nv_bfloat16> {
+  static constexpr int kChunkK = 64;   // elements per 128-byte K chunk
+  static constexpr int kMmaK = 16;     // elements per 32-byte tcgen05 K step
+  static constexpr uint32_t kFmt = 1;  // UMMA F16F32Format::BF16
+  static constexpr bool kTf32 = false;
+};
+template <> struct ElemTraits<float> {
+  static constexpr int kChunkK = 32;
+  static constexpr int kMmaK = 8;
+  static constexpr uint32_t kFmt = 2;  // UMMA F16F32Format::TF32
+  static constexpr bool kTf32 = true;
+};
+
+__device__ __forceinline__ float to_f32(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float to_f32(float v) { return v; }
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+
+// 8 consecutive elements <-> float[8] (16 B for bf16, 32 B for fp32); p must be aligned.
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float* v) {
+  uint4 u = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 f = __bfloat1622float2(h[i]);
+    v[2 * i] = f.x; v[2 * i + 1] = f.y;
+  }
+}
+__device__ __forceinline__ void load8(const float* p, float* v) {
+  float4 a = *reinterpret_cast<const float4*>(p);
+  float4 b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float* v) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ void store8(float* p, const float* v) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+
+// Exact (erf) GELU, as nn.GELU() / F.gelu default.
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float silu(float x) { return x / (1.0f + expf(-x)); }
+
+// ---------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_async_proxy() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a pipeline bug must end in a trap (a CUDA error the host reports), never
+// in a hung GPU.  try_wait sleeps in hardware, so the bound is ~seconds, far above any
+// legitimate wait.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  for (uint32_t spin = 0; spin < (1u << 24); ++spin) {
+    if (mbar_try_wait(bar, parity)) return;
+  }
+  __trap();
+}
+
+// 2D tiled TMA load global -> shared, completing on an mbarrier.  Coordinates are signed;
+// out-of-range rows arrive as zeros (that is what implements the conv halo).
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+
+// tcgen05 / TMEM
+// Whole-warp (.sync.aligned) TMEM column allocation; ncols is a power of two >= 32.
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_out, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_out)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem] * B[smem]^T, both operands K-major, issued by ONE thread.
+template <bool kTf32>
+__device__ __forceinline__ void umma_ss(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  if constexpr (kTf32) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+// All previously issued MMAs of this thread arrive on the mbarrier when they retire
+// (implies tcgen05.fence::before_thread_sync).
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// 32 lanes x 32 fp32 columns of the accumulator -> 32 registers per thread (lane = row).
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor for a K-major tile whose rows are 128 bytes and whose
+// 8-row groups are 1024 bytes apart, 128-byte swizzle (what a {128 B x rows} TMA box with
+// CU_TENSOR_MAP_SWIZZLE_128B writes).  Fields per the sm_100 UMMA descriptor: start>>4
+// [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout=SWIZZLE_128B(2) [61,64).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3FFF);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+// Instruction descriptor: fp32 accumulate, A/B format fmt (1 = bf16, 2 = tf32), both K-major.
+__host__ __device__ inline uint32_t umma_idesc(uint32_t fmt, int M, int N) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | (static_cast<uint32_t>(N >> 3) << 17) |
+         (static_cast<uint32_t>(M >> 4) << 24);
+}
+
+}  // namespace dmb

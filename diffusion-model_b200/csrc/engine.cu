@@ -1,0 +1,1169 @@
+// Engine implementation (see engine.cuh).  One Engine<T> per precision mode:
+//   T = __nv_bfloat16 : bf16 activations / weights, tcgen05 kind::f16, fp32 accumulate
+//   T = float         : fp32 activations / weights, tcgen05 kind::tf32, fp32 accumulate
+#include "engine.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace dmb {
+
+[[noreturn]] void fail(int code, const std::string& msg) { throw Error{code, msg}; }
+
+void cuda_check(cudaError_t e, const char* what, const char* file, int line) {
+  if (e != cudaSuccess) {
+    fail(3, std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what + " at " + file + ":" +
+                std::to_string(line));
+  }
+}
+
+namespace {
+
+// ---------------------------------------------------------------------------
+// TMA descriptor encoding through the driver entry point (no link-time libcuda).
+// ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    DMB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+    if (!p || qres != cudaDriverEntryPointSuccess) fail(3, "cuTensorMapEncodeTiled entry point not available");
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2D row-major [rows, inner] tensor, box = {128 bytes of inner, box_rows}, 128B swizzle.
+template <typename T>
+CUtensorMap make_tmap(const void* base, uint64_t inner, uint64_t rows, uint32_t box_rows) {
+  CUtensorMap m;
+  memset(&m, 0, sizeof(m));
+  const cuuint64_t gdim[2] = {inner, rows};
+  const cuuint64_t gstride[1] = {inner * sizeof(T)};
+  const cuuint32_t box[2] = {static_cast<cuuint32_t>(ElemTraits<T>::kChunkK), box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUtensorMapDataType dt = sizeof(T) == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  CUresult r = encode_tiled_fn()(&m, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) fail(3, "cuTensorMapEncodeTiled failed with code " + std::to_string(static_cast<int>(r)));
+  return m;
+}
+
+// ---------------------------------------------------------------------------
+// Device memory owned by the engine.
+// ---------------------------------------------------------------------------
+struct Pool {
+  std::vector<void*> ptrs;
+  size_t bytes = 0;
+  void* alloc(size_t n, bool zero = true) {
+    void* p = nullptr;
+    n = (n + 255) / 256 * 256;
+    DMB_CUDA(cudaMalloc(&p, n));
+    if (zero) DMB_CUDA(cudaMemset(p, 0, n));
+    ptrs.push_back(p);
+    bytes += n;
+    return p;
+  }
+  template <typename U> U* alloc_n(size_t n, bool zero = true) { return static_cast<U*>(alloc(n * sizeof(U), zero)); }
+  void release() {
+    for (void* p : ptrs) cudaFree(p);
+    ptrs.clear();
+    bytes = 0;
+  }
+  ~Pool() { release(); }
+};
+
+int pick_block_n(int N) {
+  if (N % 128 == 0) return 128;
+  if (N % 64 == 0) return 64;
+  if (N % 32 == 0) return 32;
+  return 16;
+}
+
+uint32_t tmem_cols_for(int block_n) {
+  uint32_t need = 2u * block_n, c = 32;
+  while (c < need) c <<= 1;
+  return c;
+}
+
+// Small repack kernels (run once at weight load).
+template <typename T>
+__global__ void repack_conv3x3_kernel(const float* __restrict__ w /*[Co][Ci][3][3]*/, int Co, int Ci, int rows_per_tap,
+                                      T* __restrict__ out /*[9][rows_per_tap][Ci]*/) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long total = 9LL * Co * Ci;
+  if (i >= total) return;
+  const int ci = static_cast<int>(i % Ci);
+  const int co = static_cast<int>((i / Ci) % Co);
+  const int tap = static_cast<int>(i / (static_cast<long long>(Ci) * Co));
+  out[(static_cast<size_t>(tap) * rows_per_tap + co) * Ci + ci] = from_f32<T>(w[(static_cast<size_t>(co) * Ci + ci) * 9 + tap]);
+}
+// ConvTranspose2d(4, stride 2, pad 1) weight [Ci][Co][4][4] -> [phase(a,b)][tap(u,v)][Co][Ci].
+// Output pixel (2y+a, 2x+b) = sum over input pixels (y+dy, x+dx): a=0: (ky=1,dy=0),(ky=3,dy=-1);
+// a=1: (ky=0,dy=+1),(ky=2,dy=0); same for b / kx / dx.  Tap index u selects the first / second pair.
+template <typename T>
+__global__ void repack_convT_kernel(const float* __restrict__ w, int Ci, int Co, T* __restrict__ out) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long total = 16LL * Co * Ci;
+  if (i >= total) return;
+  const int ci = static_cast<int>(i % Ci);
+  const int co = static_cast<int>((i / Ci) % Co);
+  const int tv = static_cast<int>((i / (static_cast<long long>(Ci) * Co)) % 2);
+  const int tu = static_cast<int>((i / (2LL * Ci * Co)) % 2);
+  const int pb = static_cast<int>((i / (4LL * Ci * Co)) % 2);
+  const int pa = static_cast<int>(i / (8LL * Ci * Co));
+  const int ky = (pa == 0) ? (tu == 0 ? 1 : 3) : (tu == 0 ? 0 : 2);
+  const int kx = (pb == 0) ? (tv == 0 ? 1 : 3) : (tv == 0 ? 0 : 2);
+  out[i] = from_f32<T>(w[((static_cast<size_t>(ci) * Co + co) * 4 + ky) * 4 + kx]);
+}
+template <typename T>
+__global__ void cast_kernel(const float* __restrict__ in, long long n, T* __restrict__ out) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = from_f32<T>(in[i]);
+}
+__global__ void transpose_kernel(const float* __restrict__ in, int rows, int cols, float* __restrict__ out,
+                                 int out_ld, int out_col0) {  // out[c][out_col0 + r] = in[r][c]
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * cols) return;
+  const int r = i / cols, c = i % cols;
+  out[static_cast<size_t>(c) * out_ld + out_col0 + r] = in[i];
+}
+
+inline int cdiv(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
+
+}  // namespace
+}  // namespace dmb
+
+namespace dmb {
+
+template <typename T>
+struct GemmW {  // a repacked weight: [ntaps * rows_per_tap, K] K-major, plus its TMA descriptor
+  T* w = nullptr;
+  int K = 0, N = 0, rows_per_tap = 0, ntaps = 0, bn = 0;
+  CUtensorMap tmap;
+  const float* bias = nullptr;
+};
+
+template <typename T>
+struct Act {  // an activation in padded pixel-matrix layout
+  T* p = nullptr;
+  int C = 0;
+  Geo g;
+  CUtensorMap tmap;
+  float2* stats = nullptr;  // [n_stat_tiles][rows_alloc] GroupNorm row partials (conv outputs only)
+  int n_stat_tiles = 0;
+};
+
+using Op = std::function<void(cudaStream_t)>;
+
+template <typename T>
+struct Plan {
+  Pool pool;
+  std::vector<Op> ops;
+  std::map<std::string, Act<T>> taps;
+  int B = 0;
+  bool doubled = false;
+  // bound inputs / state (device)
+  float* x_state = nullptr;
+  long long* t_vec = nullptr;
+  long long* y = nullptr;
+  float* vals = nullptr;
+  float* mask = nullptr;
+  DynParams* dyn = nullptr;
+  float* emb = nullptr;
+  float* embproj = nullptr;
+  float* eps = nullptr;   // eager forward output staging (B,4,28,28)
+  float* geom = nullptr;  // (B,12)
+  Act<T> feat;            // sa6 output
+  cudaGraphExec_t exec_one = nullptr;
+  cudaGraphExec_t exec_chunk = nullptr;
+  int chunk = 0;
+  ~Plan() {
+    if (exec_one) cudaGraphExecDestroy(exec_one);
+    if (exec_chunk) cudaGraphExecDestroy(exec_chunk);
+  }
+};
+
+template <typename T>
+class Engine : public IEngine {
+ public:
+  explicit Engine(int device) : device_(device) {
+    DMB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    DMB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) fail(4, "this library is built for sm_100a (B200); found sm_" + std::to_string(prop.major) + std::to_string(prop.minor));
+    num_sms_ = prop.multiProcessorCount;
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+    DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+    DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+  }
+  ~Engine() override {}
+
+  void load_unet(const TensorMapIn& w) override;
+  void load_vae(const TensorMapIn& w) override;
+  void unet_forward(const float* x, const long long* t, const long long* y, const float* vals, const float* mask,
+                    int B, float* eps, float* geom, cudaStream_t s) override;
+  void cfg_step(const float* x_in, const long long* t, const long long* y, int null_label, const float* vals,
+                const float* mask, float guidance, const float* coef, int T_steps, const float* noise,
+                unsigned long long seed, unsigned long long sample_offset, float* x_out, float* eps_out, int B,
+                cudaStream_t s) override;
+  void sample_loop(float* x, const long long* y, int null_label, const float* vals, const float* mask,
+                   float guidance, const float* coef, int T_steps, int t_start, int n_steps, const float* noise,
+                   unsigned long long seed, unsigned long long sample_offset, float* x_dump, float* eps_dump,
+                   int B, cudaStream_t s) override;
+  void vae_decode(const float* z, int B, float* img_f32, uint8_t* img_u8, cudaStream_t s) override;
+  void get_tap(const char* name, float* out, int64_t capacity, int64_t* shape4, cudaStream_t s) override;
+  void op_conv3x3(const float* x, const float* w, int B, int Cin, int Cout, int H, int W, float* out,
+                  cudaStream_t s) override;
+  void op_linear(const float* x, const float* w, const float* bias, int rows, int K, int N, int act, float* out,
+                 cudaStream_t s) override;
+  void op_convT4x4(const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int H, int W,
+                   float* out, cudaStream_t s) override;
+  long long launches() const override { return launches_; }
+  void reset_launches() override { launches_ = 0; }
+
+ private:
+  static constexpr int kGemmSmemMax = 227 * 1024 - 512;
+
+  // ---- weights
+  const float* f(const std::string& name) const {
+    auto it = blob_.find(name);
+    if (it == blob_.end()) fail(2, "missing weight tensor '" + name + "'");
+    return it->second.first;
+  }
+  int64_t numel(const std::string& name) const {
+    auto it = blob_.find(name);
+    if (it == blob_.end()) fail(2, "missing weight tensor '" + name + "'");
+    return it->second.second;
+  }
+  void upload(const TensorMapIn& w, const std::string& prefix, Pool& pool);
+  GemmW<T> make_conv3x3_w(const std::string& name, int Co, int Ci, Pool& pool);
+  GemmW<T> make_linear_w(const std::string& wname, const std::string& bname, int N, int K, Pool& pool);
+  GemmW<T> make_convT_w(const std::string& wname, const std::string& bname, int Ci, int Co, Pool& pool);
+  GemmW<T> make_conv3x3_from_ptr(const float* w_dev, int Co, int Ci, Pool& pool);
+
+  // ---- launch helpers
+  Act<T> new_act(Pool& pool, int n, int H, int W, int C, bool with_stats, int stat_tiles = 0);
+  void gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* shifts, int ntaps, GemmParams ep,
+            cudaStream_t s);
+  Op op_conv(const Act<T>& in, const GemmW<T>& w, const Act<T>& out);
+  Op op_lin(const Act<T>& in, const GemmW<T>& w, const Act<T>& out, int act, const Act<T>* residual);
+  void build_unet_plan(Plan<T>& p);
+  Plan<T>& get_plan(int B, bool doubled);
+  void bind_inputs(Plan<T>& p, const float* x, const long long* t, const long long* y, const float* vals,
+                   const float* mask, int null_label, cudaStream_t s);
+  void run_ops(Plan<T>& p, cudaStream_t s) {
+    for (auto& op : p.ops) op(s);
+  }
+
+  int device_ = 0;
+  int num_sms_ = 148;
+  long long launches_ = 0;
+  bool counting_ = true;
+
+  Pool wpool_unet_, wpool_vae_;
+  std::map<std::string, std::pair<const float*, int64_t>> blob_;  // name -> fp32 device copy
+  std::map<std::string, GemmW<T>> gw_;
+  EmbWeights embw_{};
+  const float* geom_w1t_ = nullptr;
+  bool unet_loaded_ = false, vae_loaded_ = false;
+
+  std::map<std::pair<int, bool>, std::unique_ptr<Plan<T>>> plans_;
+  Plan<T>* last_plan_ = nullptr;
+
+  struct VaePlan {
+    Pool pool;
+    std::vector<Op> ops;
+    int B = 0;
+    float* z = nullptr;
+    float* img_f32 = nullptr;
+    uint8_t* img_u8 = nullptr;
+  };
+  std::unique_ptr<VaePlan> vae_plan_;
+  void build_vae_plan(VaePlan& p, int B);
+
+  void count(int n = 1) {
+    if (counting_) launches_ += n;
+  }
+};
+
+// ---------------------------------------------------------------------------
+// Weights
+// ---------------------------------------------------------------------------
+template <typename T>
+void Engine<T>::upload(const TensorMapIn& w, const std::string& prefix, Pool& pool) {
+  size_t total = 0;
+  for (auto& kv : w) total += (static_cast<size_t>(kv.second.numel) + 63) / 64 * 64;
+  float* base = pool.alloc_n<float>(total);
+  size_t off = 0;
+  for (auto& kv : w) {
+    DMB_CUDA(cudaMemcpy(base + off, kv.second.ptr, kv.second.numel * sizeof(float), cudaMemcpyDefault));
+    blob_[prefix + kv.first] = {base + off, kv.second.numel};
+    off += (static_cast<size_t>(kv.second.numel) + 63) / 64 * 64;
+  }
+}
+
+template <typename T>
+GemmW<T> Engine<T>::make_conv3x3_from_ptr(const float* w_dev, int Co, int Ci, Pool& pool) {
+  GemmW<T> g;
+  g.K = Ci; g.N = Co; g.ntaps = 9;
+  g.bn = pick_block_n(Co);
+  g.rows_per_tap = (Co + g.bn - 1) / g.bn * g.bn;
+  DMB_REQUIRE(Ci % ElemTraits<T>::kChunkK == 0, "conv input channels must be a multiple of the K chunk");
+  g.w = pool.alloc_n<T>(static_cast<size_t>(9) * g.rows_per_tap * Ci);
+  const long long total = 9LL * Co * Ci;
+  repack_conv3x3_kernel<T><<<cdiv(total, 256), 256>>>(w_dev, Co, Ci, g.rows_per_tap, g.w);
+  DMB_CHECK_LAUNCH();
+  g.tmap = make_tmap<T>(g.w, Ci, static_cast<uint64_t>(9) * g.rows_per_tap, g.bn);
+  return g;
+}
+
+template <typename T>
+GemmW<T> Engine<T>::make_conv3x3_w(const std::string& name, int Co, int Ci, Pool& pool) {
+  DMB_REQUIRE(numel(name) == 9LL * Co * Ci, "unexpected size of " + name);
+  return make_conv3x3_from_ptr(f(name), Co, Ci, pool);
+}
+
+template <typename T>
+GemmW<T> Engine<T>::make_linear_w(const std::string& wname, const std::string& bname, int N, int K, Pool& pool) {
+  DMB_REQUIRE(numel(wname) == static_cast<int64_t>(N) * K, "unexpected size of " + wname);
+  GemmW<T> g;
+  g.K = K; g.N = N; g.ntaps = 1;
+  g.bn = pick_block_n(N);
+  g.rows_per_tap = (N + g.bn - 1) / g.bn * g.bn;
+  g.w = pool.alloc_n<T>(static_cast<size_t>(g.rows_per_tap) * K);
+  cast_kernel<T><<<cdiv(static_cast<long long>(N) * K, 256), 256>>>(f(wname), static_cast<long long>(N) * K, g.w);
+  DMB_CHECK_LAUNCH();
+  g.tmap = make_tmap<T>(g.w, K, g.rows_per_tap, g.bn);
+  if (!bname.empty()) {
+    DMB_REQUIRE(numel(bname) == N, "unexpected size of " + bname);
+    g.bias = f(bname);
+  }
+  return g;
+}
+
+template <typename T>
+GemmW<T> Engine<T>::make_convT_w(const std::string& wname, const std::string& bname, int Ci, int Co, Pool& pool) {
+  DMB_REQUIRE(numel(wname) == 16LL * Co * Ci, "unexpected size of " + wname);
+  GemmW<T> g;
+  g.K = Ci; g.N = Co; g.ntaps = 4;
+  g.bn = pick_block_n(Co);
+  g.rows_per_tap = Co;
+  DMB_REQUIRE(Co % g.bn == 0, "conv-transpose output channels must be a multiple of the N tile");
+  g.w = pool.alloc_n<T>(16ull * Co * Ci);
+  repack_convT_kernel<T><<<cdiv(16LL * Co * Ci, 256), 256>>>(f(wname), Ci, Co, g.w);
+  DMB_CHECK_LAUNCH();
+  g.tmap = make_tmap<T>(g.w, Ci, 16ull * Co, g.bn);
+  if (!bname.empty()) g.bias = f(bname);
+  return g;
+}
+
+}  // namespace dmb
+
+namespace dmb {
+
+static const char* kResBlocks[] = {"inc", "down1.maxpool_conv.1", "down1.maxpool_conv.2", "down2.maxpool_conv.1",
+                                   "down2.maxpool_conv.2", "down3.maxpool_conv.1", "down3.maxpool_conv.2", "bot1",
+                                   "bot2", "bot3", "up1.conv.0", "up1.conv.1", "up2.conv.0", "up2.conv.1",
+                                   "up3.conv.0", "up3.conv.1"};
+// (C_in, C_mid, C_out) of the sixteen ResBlocks, models/unet_cond.py:131-153.
+static const int kResDims[][3] = {{4, 64, 64},      {64, 64, 64},     {64, 128, 128},  {128, 128, 128},
+                                  {128, 256, 256},  {256, 256, 256},  {256, 256, 256}, {256, 512, 512},
+                                  {512, 512, 512},  {512, 256, 256},  {512, 512, 512}, {512, 256, 128},
+                                  {256, 256, 256},  {256, 128, 64},   {128, 128, 128}, {128, 64, 64}};
+static const char* kAttn[] = {"sa1", "sa2", "sa3", "sa4", "sa5", "sa6"};
+static const int kAttnC[] = {128, 256, 256, 128, 64, 64};
+static const char* kEmbLayers[] = {"down1", "down2", "down3", "up1", "up2", "up3"};
+static const int kEmbC[] = {128, 256, 256, 128, 64, 64};
+
+template <typename T>
+void Engine<T>::load_unet(const TensorMapIn& w) {
+  DMB_CUDA(cudaSetDevice(device_));
+  DMB_CUDA(cudaDeviceSynchronize());
+  plans_.clear();
+  last_plan_ = nullptr;
+  gw_.clear();
+  for (auto it = blob_.begin(); it != blob_.end();) {
+    if (it->first.rfind("vae.", 0) == 0) ++it; else it = blob_.erase(it);
+  }
+  wpool_unet_.release();
+  unet_loaded_ = false;
+  upload(w, "", wpool_unet_);
+  Pool& pool = wpool_unet_;
+
+  for (int i = 0; i < 16; ++i) {
+    const std::string p = kResBlocks[i];
+    const int ci = kResDims[i][0], cm = kResDims[i][1], co = kResDims[i][2];
+    if (i > 0) gw_[p + ".double_conv.0.weight"] = make_conv3x3_w(p + ".double_conv.0.weight", cm, ci, pool);
+    else DMB_REQUIRE(numel(p + ".double_conv.0.weight") == 9LL * cm * ci, "unexpected size of inc conv");
+    gw_[p + ".double_conv.3.weight"] = make_conv3x3_w(p + ".double_conv.3.weight", co, cm, pool);
+    DMB_REQUIRE(numel(p + ".double_conv.1.weight") == cm && numel(p + ".double_conv.4.bias") == co, "GroupNorm size");
+  }
+  for (int i = 0; i < 6; ++i) {
+    const std::string p = kAttn[i];
+    const int C = kAttnC[i];
+    gw_[p + ".qkv"] = make_linear_w(p + ".mha.in_proj_weight", p + ".mha.in_proj_bias", 3 * C, C, pool);
+    gw_[p + ".proj"] = make_linear_w(p + ".mha.out_proj.weight", p + ".mha.out_proj.bias", C, C, pool);
+    gw_[p + ".ff1"] = make_linear_w(p + ".ff_self.1.weight", p + ".ff_self.1.bias", C, C, pool);
+    gw_[p + ".ff2"] = make_linear_w(p + ".ff_self.3.weight", p + ".ff_self.3.bias", C, C, pool);
+  }
+  // Embedding path: small fp32 matrices, transposed so that thread o reads column o coalesced.
+  float* w1t = pool.alloc_n<float>(24 * 256);
+  float* w2t = pool.alloc_n<float>(256 * 256);
+  float* projt = pool.alloc_n<float>(256 * kProjCols);
+  float* projb = pool.alloc_n<float>(kProjCols);
+  float* invf = pool.alloc_n<float>(128);
+  transpose_kernel<<<cdiv(256 * 24, 256), 256>>>(f("cond_mlp.0.weight"), 256, 24, w1t, 256, 0);
+  transpose_kernel<<<cdiv(256 * 256, 256), 256>>>(f("cond_mlp.2.weight"), 256, 256, w2t, 256, 0);
+  int col = 0;
+  for (int i = 0; i < 6; ++i) {
+    const std::string p = std::string(kEmbLayers[i]) + ".emb_layer.1";
+    DMB_REQUIRE(numel(p + ".weight") == static_cast<int64_t>(kEmbC[i]) * 256, "unexpected size of " + p);
+    transpose_kernel<<<cdiv(kEmbC[i] * 256, 256), 256>>>(f(p + ".weight"), kEmbC[i], 256, projt, kProjCols, col);
+    DMB_CUDA(cudaMemcpy(projb + col, f(p + ".bias"), kEmbC[i] * sizeof(float), cudaMemcpyDeviceToDevice));
+    col += kEmbC[i];
+  }
+  DMB_CHECK_LAUNCH();
+  {
+    // inv_freq = 1 / 10000^(2j/256) evaluated in fp32 the way torch does (pow then reciprocal);
+    // the host shim overrides it with torch's own values through the "__inv_freq" entry.
+    float h[128];
+    for (int j = 0; j < 128; ++j) h[j] = 1.0f / powf(10000.0f, static_cast<float>(2 * j) / 256.0f);
+    auto it = blob_.find("__inv_freq");
+    if (it != blob_.end()) DMB_CUDA(cudaMemcpy(invf, it->second.first, 128 * sizeof(float), cudaMemcpyDeviceToDevice));
+    else DMB_CUDA(cudaMemcpy(invf, h, sizeof(h), cudaMemcpyHostToDevice));
+  }
+  DMB_REQUIRE(numel("class_emb.weight") == 4 * 256, "class_emb must be (4,256)");
+  embw_.class_emb = f("class_emb.weight");
+  embw_.w1t = w1t; embw_.b1 = f("cond_mlp.0.bias");
+  embw_.w2t = w2t; embw_.b2 = f("cond_mlp.2.bias");
+  embw_.inv_freq = invf; embw_.projt = projt; embw_.projb = projb;
+  float* g1t = pool.alloc_n<float>(64 * 256);
+  transpose_kernel<<<cdiv(256 * 64, 256), 256>>>(f("geom_head.mlp.0.weight"), 256, 64, g1t, 256, 0);
+  DMB_CHECK_LAUNCH();
+  geom_w1t_ = g1t;
+  DMB_REQUIRE(numel("out.weight") == 4 * 64 && numel("out.bias") == 4, "out conv must be 64->4");
+  DMB_CUDA(cudaDeviceSynchronize());
+  unet_loaded_ = true;
+}
+
+template <typename T>
+void Engine<T>::load_vae(const TensorMapIn& w) {
+  DMB_CUDA(cudaSetDevice(device_));
+  DMB_CUDA(cudaDeviceSynchronize());
+  vae_plan_.reset();
+  for (auto it = blob_.begin(); it != blob_.end();) {
+    if (it->first.rfind("vae.", 0) == 0) it = blob_.erase(it); else ++it;
+  }
+  for (auto it = gw_.begin(); it != gw_.end();) {
+    if (it->first.rfind("vae.", 0) == 0) it = gw_.erase(it); else ++it;
+  }
+  wpool_vae_.release();
+  vae_loaded_ = false;
+  upload(w, "vae.", wpool_vae_);
+  Pool& pool = wpool_vae_;
+  DMB_REQUIRE(numel("vae.dec.0.weight") == 256 * 4 * 9, "dec.0 must be conv 4->256");
+  gw_["vae.dec.3"] = make_convT_w("vae.dec.3.weight", "vae.dec.3.bias", 256, 256, pool);
+  gw_["vae.dec.6"] = make_conv3x3_w("vae.dec.6.weight", 128, 256, pool);
+  gw_["vae.dec.6"].bias = f("vae.dec.6.bias");
+  gw_["vae.dec.9"] = make_convT_w("vae.dec.9.weight", "vae.dec.9.bias", 128, 128, pool);
+  gw_["vae.dec.12"] = make_conv3x3_w("vae.dec.12.weight", 64, 128, pool);
+  gw_["vae.dec.12"].bias = f("vae.dec.12.bias");
+  gw_["vae.dec.15"] = make_convT_w("vae.dec.15.weight", "vae.dec.15.bias", 64, 64, pool);
+  gw_["vae.dec.18"] = make_conv3x3_w("vae.dec.18.weight", 3, 64, pool);
+  gw_["vae.dec.18"].bias = f("vae.dec.18.bias");
+  DMB_CUDA(cudaDeviceSynchronize());
+  vae_loaded_ = true;
+}
+
+}  // namespace dmb
+
+namespace dmb {
+
+// ---------------------------------------------------------------------------
+// Launch helpers
+// ---------------------------------------------------------------------------
+template <typename T>
+Act<T> Engine<T>::new_act(Pool& pool, int n, int H, int W, int C, bool with_stats, int stat_tiles) {
+  Act<T> a;
+  a.C = C;
+  a.g = make_geo(n, H, W);
+  a.p = pool.alloc_n<T>(static_cast<size_t>(a.g.rows_alloc) * C);
+  if (C % ElemTraits<T>::kChunkK == 0) a.tmap = make_tmap<T>(a.p, C, a.g.rows_alloc, kTileM);
+  if (with_stats) {
+    a.n_stat_tiles = stat_tiles;
+    a.stats = pool.alloc_n<float2>(static_cast<size_t>(stat_tiles) * a.g.rows_alloc);
+  }
+  return a;
+}
+
+// One launch of the tcgen05 GEMM.  `ep` carries the epilogue fields; the problem fields are
+// filled here from the activation, the weight and the tap list.
+template <typename T>
+void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* shifts, int ntaps, GemmParams ep,
+                     cudaStream_t s) {
+  DMB_REQUIRE(a.C == w.K, "GEMM K mismatch");
+  DMB_REQUIRE(ntaps <= kMaxTaps, "too many taps");
+  GemmParams p = ep;
+  p.num_taps = ntaps;
+  for (int i = 0; i < ntaps; ++i) {
+    p.a_shift[i] = shifts[i];
+    p.b_row[i] = (phase * ntaps + i) * w.rows_per_tap;
+  }
+  p.k_chunks = w.K / ElemTraits<T>::kChunkK;
+  p.block_n = w.bn;
+  p.n_tiles = w.rows_per_tap / w.bn;
+  p.m_tiles = cdiv(a.g.rows_valid, kTileM);
+  const int stage_bytes = kTileM * 128 + w.bn * 128;
+  p.stages = std::min(kMaxStages, (kGemmSmemMax - 1024) / stage_bytes);
+  p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM, w.bn);
+  p.tmem_cols = tmem_cols_for(w.bn);
+  p.geo = a.g;
+  p.rows_alloc = a.g.rows_alloc;
+  p.n_valid = w.N;
+  const int smem = p.stages * stage_bytes + 1024;
+  const int grid = std::min(p.m_tiles * p.n_tiles, num_sms_);
+  gemm_tc_kernel<T><<<grid, 256, smem, s>>>(a.tmap, w.tmap, p);
+  DMB_CHECK_LAUNCH();
+  count();
+}
+
+template <typename T>
+Op Engine<T>::op_conv(const Act<T>& in, const GemmW<T>& w, const Act<T>& out) {
+  return [this, in, w, out](cudaStream_t s) {
+    int shifts[9];
+    for (int ky = 0; ky < 3; ++ky)
+      for (int kx = 0; kx < 3; ++kx) shifts[ky * 3 + kx] = (ky - 1) * in.g.Wp + (kx - 1);
+    GemmParams ep{};
+    ep.epi = EPI_STORE;
+    ep.out = out.p; ep.ldc = out.C;
+    ep.bias = w.bias;
+    ep.rowstats = out.stats;
+    gemm(in, w, 0, shifts, 9, ep, s);
+  };
+}
+
+template <typename T>
+Op Engine<T>::op_lin(const Act<T>& in, const GemmW<T>& w, const Act<T>& out, int act, const Act<T>* residual) {
+  const T* res = residual ? residual->p : nullptr;
+  return [this, in, w, out, act, res](cudaStream_t s) {
+    int shift0 = 0;
+    GemmParams ep{};
+    ep.epi = EPI_STORE;
+    ep.out = out.p; ep.ldc = out.C;
+    ep.bias = w.bias; ep.act = act; ep.residual = res;
+    gemm(in, w, 0, &shift0, 1, ep, s);
+  };
+}
+
+// ---------------------------------------------------------------------------
+// U-Net plan: the launch list of one forward (models/unet_cond_geom.py:52-76) for a fixed
+// effective batch.  doubled = the two CFG passes as one batch of 2B: samples [0,B) carry
+// the null label, [B,2B) the class label (diff.py:147-150).
+// ---------------------------------------------------------------------------
+template <typename T>
+void Engine<T>::build_unet_plan(Plan<T>& P) {
+  Pool& pool = P.pool;
+  const int B = P.B, n = P.doubled ? 2 * B : B;
+  P.x_state = pool.alloc_n<float>(static_cast<size_t>(B) * kLatC * kLatH * kLatW);
+  P.t_vec = pool.alloc_n<long long>(B);
+  P.y = pool.alloc_n<long long>(B);
+  P.vals = pool.alloc_n<float>(B * kCondDim);
+  P.mask = pool.alloc_n<float>(B * kCondDim);
+  P.dyn = pool.alloc_n<DynParams>(1);
+  P.emb = pool.alloc_n<float>(static_cast<size_t>(n) * kEmbDim);
+  P.embproj = pool.alloc_n<float>(static_cast<size_t>(n) * kProjCols);
+  P.eps = pool.alloc_n<float>(static_cast<size_t>(B) * kLatC * kLatH * kLatW);
+  P.geom = pool.alloc_n<float>(B * 12);
+  auto& ops = P.ops;
+
+  {  // embedding + six projections
+    const EmbWeights ew = embw_;
+    Plan<T>* pp = &P;
+    const int doubled = P.doubled ? 1 : 0;
+    ops.push_back([this, ew, pp, n, B, doubled](cudaStream_t s) {
+      emb_kernel<<<n, 256, 0, s>>>(ew, pp->t_vec, pp->y, pp->dyn->flags, pp->vals, pp->mask, B, doubled, pp->emb,
+                                   pp->embproj);
+      DMB_CHECK_LAUNCH();
+      count();
+    });
+  }
+
+  auto gn = [&](const Act<T>& raw, const std::string& gname, int mode, const Act<T>* residual, int emb_off) {
+    Act<T> out = new_act(pool, raw.g.n, raw.g.H, raw.g.W, raw.C, false);
+    const float* gamma = f(gname + ".weight");
+    const float* beta = f(gname + ".bias");
+    const T* res = residual ? residual->p : nullptr;
+    const float* embproj = P.embproj;
+    const int total_vec = raw.g.H * raw.g.W * raw.C / 8;
+    const int splits = std::max(1, std::min(8, total_vec / 2048));
+    ops.push_back([this, raw, out, gamma, beta, mode, res, embproj, emb_off, splits](cudaStream_t s) {
+      gn1_apply_kernel<T><<<dim3(splits, raw.g.n), 256, 0, s>>>(raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc,
+                                                                gamma, beta, mode, res, embproj, emb_off, raw.g,
+                                                                raw.C, out.p);
+      DMB_CHECK_LAUNCH();
+      count();
+    });
+    return out;
+  };
+  auto conv = [&](const Act<T>& in, const std::string& wname) {
+    const GemmW<T>& w = gw_.at(wname);
+    Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, true, w.rows_per_tap / w.bn);
+    ops.push_back(op_conv(in, w, out));
+    return out;
+  };
+  // ResBlock (models/unet_cond.py:10-30); last_mode is what follows the second GroupNorm.
+  auto resblock = [&](const Act<T>& in, const std::string& p, bool residual, int last_mode, int emb_off) {
+    Act<T> r1 = conv(in, p + ".double_conv.0.weight");
+    Act<T> h = gn(r1, p + ".double_conv.1", GN_GELU, nullptr, 0);
+    Act<T> r2 = conv(h, p + ".double_conv.3.weight");
+    return gn(r2, p + ".double_conv.4", residual ? GN_RES_GELU : last_mode, residual ? &in : nullptr, emb_off);
+  };
+  auto attention = [&](const Act<T>& x, const std::string& p) {
+    const int C = x.C, H = x.g.H, W = x.g.W, nn = x.g.n;
+    auto ln = [&](const Act<T>& in, const std::string& name) {
+      Act<T> out = new_act(pool, nn, H, W, C, false);
+      const float* wv = f(name + ".weight");
+      const float* bv = f(name + ".bias");
+      ops.push_back([this, in, out, wv, bv, C](cudaStream_t s) {
+        const long long ntok = static_cast<long long>(in.g.n) * in.g.H * in.g.W;
+        const int grid = cdiv(ntok, 8);
+        if (C == 64) layernorm_kernel<T, 2><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
+        else if (C == 128) layernorm_kernel<T, 4><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
+        else layernorm_kernel<T, 8><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
+        DMB_CHECK_LAUNCH();
+        count();
+      });
+      return out;
+    };
+    Act<T> xl = ln(x, p + ".ln");
+    Act<T> qkv = new_act(pool, nn, H, W, 3 * C, false);
+    ops.push_back(op_lin(xl, gw_.at(p + ".qkv"), qkv, 0, nullptr));
+    Act<T> av = new_act(pool, nn, H, W, C, false);
+    ops.push_back([this, qkv, av, C](cudaStream_t s) {
+      const int L = qkv.g.H * qkv.g.W, D = C / 4;
+      const int threads = std::min(128, (L + 31) / 32 * 32);
+      const dim3 grid(cdiv(L, threads), 4, qkv.g.n);
+      const size_t smem = static_cast<size_t>(L) * D * 2 * sizeof(float);
+      if (D == 16) attention_kernel<T, 16><<<grid, threads, smem, s>>>(qkv.p, qkv.g, C, av.p);
+      else if (D == 32) attention_kernel<T, 32><<<grid, threads, smem, s>>>(qkv.p, qkv.g, C, av.p);
+      else attention_kernel<T, 64><<<grid, threads, smem, s>>>(qkv.p, qkv.g, C, av.p);
+      DMB_CHECK_LAUNCH();
+      count();
+    });
+    Act<T> o = new_act(pool, nn, H, W, C, false);
+    ops.push_back(op_lin(av, gw_.at(p + ".proj"), o, 0, &xl));
+    Act<T> h = ln(o, p + ".ff_self.0");
+    Act<T> f1 = new_act(pool, nn, H, W, C, false);
+    ops.push_back(op_lin(h, gw_.at(p + ".ff1"), f1, 1, nullptr));
+    Act<T> out = new_act(pool, nn, H, W, C, false);
+    ops.push_back(op_lin(f1, gw_.at(p + ".ff2"), out, 0, &o));
+    return out;
+  };
+  auto down = [&](const Act<T>& x, const std::string& p, int emb_off) {
+    Act<T> pooled = new_act(pool, x.g.n, x.g.H / 2, x.g.W / 2, x.C, false);
+    ops.push_back([this, x, pooled](cudaStream_t s) {
+      const long long total = static_cast<long long>(pooled.g.n) * pooled.g.H * pooled.g.W * (x.C / 8);
+      maxpool2_kernel<T><<<cdiv(total, 256), 256, 0, s>>>(x.p, x.g, pooled.g, x.C, pooled.p);
+      DMB_CHECK_LAUNCH();
+      count();
+    });
+    Act<T> a = resblock(pooled, p + ".maxpool_conv.1", true, GN_NONE, 0);
+    return resblock(a, p + ".maxpool_conv.2", false, GN_ADD_EMB, emb_off);
+  };
+  auto up = [&](const Act<T>& x, const Act<T>& skip, const std::string& p, int emb_off) {
+    Act<T> cat = new_act(pool, skip.g.n, skip.g.H, skip.g.W, skip.C + x.C, false);
+    ops.push_back([this, x, skip, cat](cudaStream_t s) {
+      const long long total = static_cast<long long>(cat.g.n) * cat.g.H * cat.g.W * (cat.C / 8);
+      upcat_kernel<T><<<cdiv(total, 256), 256, 0, s>>>(skip.p, skip.C, x.p, x.g, x.C, cat.g, cat.p);
+      DMB_CHECK_LAUNCH();
+      count();
+    });
+    Act<T> a = resblock(cat, p + ".conv.0", true, GN_NONE, 0);
+    return resblock(a, p + ".conv.1", false, GN_ADD_EMB, emb_off);
+  };
+
+  // inc: the 4->64 conv runs on CUDA cores straight from the fp32 latent.
+  Act<T> r0 = new_act(pool, n, kLatH, kLatW, 64, true, 1);
+  {
+    const float* w0 = f("inc.double_conv.0.weight");
+    Plan<T>* pp = &P;
+    ops.push_back([this, r0, w0, pp, B](cudaStream_t s) {
+      conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), r0.g.n, 1), 128, 0, s>>>(pp->x_state, B, w0, nullptr, 1.0f,
+                                                                                  r0.g, 64, r0.p, r0.stats);
+      DMB_CHECK_LAUNCH();
+      count();
+    });
+  }
+  Act<T> h0 = gn(r0, "inc.double_conv.1", GN_GELU, nullptr, 0);
+  Act<T> r1 = conv(h0, "inc.double_conv.3.weight");
+  Act<T> x1 = gn(r1, "inc.double_conv.4", GN_NONE, nullptr, 0);
+  P.taps["inc"] = x1;
+  Act<T> x2 = down(x1, "down1", 0);       P.taps["down1"] = x2;
+  x2 = attention(x2, "sa1");              P.taps["sa1"] = x2;
+  Act<T> x3 = down(x2, "down2", 128);     P.taps["down2"] = x3;
+  x3 = attention(x3, "sa2");              P.taps["sa2"] = x3;
+  Act<T> x4 = down(x3, "down3", 384);     P.taps["down3"] = x4;
+  x4 = attention(x4, "sa3");              P.taps["sa3"] = x4;
+  x4 = resblock(x4, "bot1", false, GN_NONE, 0);  P.taps["bot1"] = x4;
+  x4 = resblock(x4, "bot2", false, GN_NONE, 0);  P.taps["bot2"] = x4;
+  x4 = resblock(x4, "bot3", false, GN_NONE, 0);  P.taps["bot3"] = x4;
+  Act<T> u = up(x4, x3, "up1", 640);      P.taps["up1"] = u;
+  u = attention(u, "sa4");                P.taps["sa4"] = u;
+  u = up(u, x2, "up2", 768);              P.taps["up2"] = u;
+  u = attention(u, "sa5");                P.taps["sa5"] = u;
+  u = up(u, x1, "up3", 832);              P.taps["up3"] = u;
+  u = attention(u, "sa6");                P.taps["sa6"] = u;
+  P.feat = u;
+}
+
+}  // namespace dmb
+
+namespace dmb {
+
+template <typename T>
+Plan<T>& Engine<T>::get_plan(int B, bool doubled) {
+  if (!unet_loaded_) fail(5, "U-Net weights have not been loaded (dmb_load_unet_weights)");
+  DMB_REQUIRE(B >= 1, "batch must be >= 1");
+  auto key = std::make_pair(B, doubled);
+  auto it = plans_.find(key);
+  if (it == plans_.end()) {
+    // Activations of a plan are private buffers; keep at most two plans alive.
+    while (plans_.size() >= 2) {
+      DMB_CUDA(cudaDeviceSynchronize());
+      auto victim = plans_.begin();
+      if (victim->second.get() == last_plan_ && plans_.size() > 1) ++victim;
+      if (victim->second.get() == last_plan_) last_plan_ = nullptr;
+      plans_.erase(victim);
+    }
+    std::unique_ptr<Plan<T>> p(new Plan<T>());
+    p->B = B;
+    p->doubled = doubled;
+    build_unet_plan(*p);
+    DMB_CUDA(cudaDeviceSynchronize());  // allocation memsets are done before first use
+    it = plans_.emplace(key, std::move(p)).first;
+  }
+  last_plan_ = it->second.get();
+  return *it->second;
+}
+
+template <typename T>
+void Engine<T>::bind_inputs(Plan<T>& p, const float* x, const long long* t, const long long* y, const float* vals,
+                            const float* mask, int null_label, cudaStream_t s) {
+  const size_t lat = static_cast<size_t>(p.B) * kLatC * kLatH * kLatW * sizeof(float);
+  if (x) DMB_CUDA(cudaMemcpyAsync(p.x_state, x, lat, cudaMemcpyDefault, s));
+  if (t) DMB_CUDA(cudaMemcpyAsync(p.t_vec, t, p.B * sizeof(long long), cudaMemcpyDefault, s));
+  DMB_REQUIRE(y != nullptr, "class labels y are required");
+  DMB_CUDA(cudaMemcpyAsync(p.y, y, p.B * sizeof(long long), cudaMemcpyDefault, s));
+  const bool has_cond = vals && mask;
+  if (has_cond) {
+    DMB_CUDA(cudaMemcpyAsync(p.vals, vals, p.B * kCondDim * sizeof(float), cudaMemcpyDefault, s));
+    DMB_CUDA(cudaMemcpyAsync(p.mask, mask, p.B * kCondDim * sizeof(float), cudaMemcpyDefault, s));
+  }
+  const int flags[2] = {null_label, has_cond ? 1 : 0};
+  // pageable source: the runtime stages it before returning, so the stack buffer is safe
+  DMB_CUDA(cudaMemcpyAsync(p.dyn->flags, flags, sizeof(flags), cudaMemcpyHostToDevice, s));
+}
+
+template <typename T>
+void Engine<T>::unet_forward(const float* x, const long long* t, const long long* y, const float* vals,
+                             const float* mask, int B, float* eps, float* geom, cudaStream_t s) {
+  DMB_CUDA(cudaSetDevice(device_));
+  Plan<T>& p = get_plan(B, false);
+  bind_inputs(p, x, t, y, vals, mask, 0, s);
+  run_ops(p, s);
+  const Act<T> feat = p.feat;
+  if (eps) {
+    out_conv_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, s>>>(feat.p, feat.g, f("out.weight"), f("out.bias"), eps);
+    DMB_CHECK_LAUNCH();
+    count();
+  }
+  if (geom) {
+    geom_head_kernel<T><<<B, 256, 0, s>>>(feat.p, feat.g, geom_w1t_, f("geom_head.mlp.0.bias"),
+                                          f("geom_head.mlp.2.weight"), f("geom_head.mlp.2.bias"), 12, geom);
+    DMB_CHECK_LAUNCH();
+    count();
+  }
+}
+
+template <typename T>
+void Engine<T>::cfg_step(const float* x_in, const long long* t, const long long* y, int null_label,
+                         const float* vals, const float* mask, float guidance, const float* coef, int T_steps,
+                         const float* noise, unsigned long long seed, unsigned long long sample_offset,
+                         float* x_out, float* eps_out, int B, cudaStream_t s) {
+  DMB_CUDA(cudaSetDevice(device_));
+  Plan<T>& p = get_plan(B, true);
+  bind_inputs(p, x_in, t, y, vals, mask, null_label, s);
+  StepParams sp{};
+  sp.x_in = p.x_state; sp.x_out = x_out; sp.t_vec = p.t_vec; sp.coef = coef; sp.T = T_steps; sp.slot_t0 = 0;
+  sp.guidance = guidance; sp.noise = noise; sp.noise_step_stride = 0; sp.seed = seed;
+  sp.sample_offset = sample_offset; sp.eps_out = eps_out; sp.x_dump = nullptr; sp.dump_step_stride = 0;
+  sp.w_out = f("out.weight"); sp.b_out = f("out.bias");
+  DMB_CUDA(cudaMemcpyAsync(&p.dyn->step, &sp, sizeof(sp), cudaMemcpyHostToDevice, s));
+  run_ops(p, s);
+  cfg_step_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, s>>>(p.feat.p, p.feat.g, B, &p.dyn->step);
+  DMB_CHECK_LAUNCH();
+  count();
+}
+
+// The T-step loop (diff.py:332-344) as CUDA-graph replays: one graph holds `chunk` whole
+// steps (embedding ... U-Net ... fused CFG/DDPM update, t -= 1); everything that varies
+// between calls is read from device memory, so the graph is captured once per batch size.
+template <typename T>
+void Engine<T>::sample_loop(float* x, const long long* y, int null_label, const float* vals, const float* mask,
+                            float guidance, const float* coef, int T_steps, int t_start, int n_steps,
+                            const float* noise, unsigned long long seed, unsigned long long sample_offset,
+                            float* x_dump, float* eps_dump, int B, cudaStream_t s) {
+  DMB_CUDA(cudaSetDevice(device_));
+  DMB_REQUIRE(t_start >= 1 && t_start <= T_steps, "t_start must be in [1, T]");
+  DMB_REQUIRE(n_steps >= 1 && n_steps <= t_start, "n_steps must be in [1, t_start]");
+  Plan<T>& p = get_plan(B, true);
+  bind_inputs(p, x, nullptr, y, vals, mask, null_label, s);
+  fill_t_kernel<<<cdiv(B, 256), 256, 0, s>>>(p.t_vec, B, t_start);
+  DMB_CHECK_LAUNCH();
+  const long long lat = static_cast<long long>(B) * kLatC * kLatH * kLatW;
+  StepParams sp{};
+  sp.x_in = p.x_state; sp.x_out = p.x_state; sp.t_vec = p.t_vec; sp.coef = coef; sp.T = T_steps;
+  sp.slot_t0 = t_start; sp.guidance = guidance; sp.noise = noise; sp.noise_step_stride = lat; sp.seed = seed;
+  sp.sample_offset = sample_offset; sp.eps_out = eps_dump; sp.x_dump = x_dump; sp.dump_step_stride = lat;
+  sp.w_out = f("out.weight"); sp.b_out = f("out.bias");
+  DMB_CUDA(cudaMemcpyAsync(&p.dyn->step, &sp, sizeof(sp), cudaMemcpyHostToDevice, s));
+
+  auto one_step = [&](cudaStream_t cs) {
+    run_ops(p, cs);
+    cfg_step_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, cs>>>(p.feat.p, p.feat.g, B, &p.dyn->step);
+    DMB_CHECK_LAUNCH();
+    advance_t_kernel<<<cdiv(B, 256), 256, 0, cs>>>(p.t_vec, B);
+    DMB_CHECK_LAUNCH();
+    count(2);
+  };
+  const int launches_per_step = static_cast<int>(p.ops.size()) + 2;
+  auto capture = [&](int steps) {
+    cudaStream_t cs;
+    DMB_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    counting_ = false;
+    try {
+      DMB_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+      for (int i = 0; i < steps; ++i) one_step(cs);
+      DMB_CUDA(cudaStreamEndCapture(cs, &graph));
+      DMB_CUDA(cudaGraphInstantiate(&exec, graph, 0));
+    } catch (...) {
+      counting_ = true;
+      if (graph) cudaGraphDestroy(graph);
+      cudaStreamDestroy(cs);
+      throw;
+    }
+    counting_ = true;
+    cudaGraphDestroy(graph);
+    cudaStreamDestroy(cs);
+    return exec;
+  };
+  const int chunk = 10;
+  if (!p.exec_one) p.exec_one = capture(1);
+  if (n_steps >= chunk && !p.exec_chunk) {
+    p.exec_chunk = capture(chunk);
+    p.chunk = chunk;
+  }
+  int left = n_steps;
+  while (left >= chunk && p.exec_chunk) {
+    DMB_CUDA(cudaGraphLaunch(p.exec_chunk, s));
+    launches_ += static_cast<long long>(chunk) * launches_per_step;
+    left -= chunk;
+  }
+  while (left > 0) {
+    DMB_CUDA(cudaGraphLaunch(p.exec_one, s));
+    launches_ += launches_per_step;
+    --left;
+  }
+  DMB_CUDA(cudaMemcpyAsync(x, p.x_state, lat * sizeof(float), cudaMemcpyDefault, s));
+}
+
+}  // namespace dmb
+
+namespace dmb {
+
+// ---------------------------------------------------------------------------
+// VAE decoder plan (models/vae.py:35-49, 64-69) for a chunk of n samples.
+// ---------------------------------------------------------------------------
+template <typename T>
+void Engine<T>::build_vae_plan(VaePlan& P, int n) {
+  Pool& pool = P.pool;
+  P.B = n;
+  auto& ops = P.ops;
+  VaePlan* pp = &P;
+
+  auto gn8 = [&](const Act<T>& raw, const std::string& name) {
+    Act<T> out = new_act(pool, raw.g.n, raw.g.H, raw.g.W, raw.C, false);
+    const int total_vec = raw.g.H * raw.g.W * raw.C / 8;
+    const int chunks = std::max(1, std::min(32, total_vec / 4096));
+    double2* partial = pool.alloc_n<double2>(static_cast<size_t>(raw.g.n) * chunks * 8);
+    const float* gamma = f(name + ".weight");
+    const float* beta = f(name + ".bias");
+    ops.push_back([this, raw, out, chunks, partial, gamma, beta](cudaStream_t s) {
+      gn8_stats_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, raw.g, raw.C, partial);
+      DMB_CHECK_LAUNCH();
+      gn8_apply_gelu_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
+                                                                    raw.C, out.p);
+      DMB_CHECK_LAUNCH();
+      count(2);
+    });
+    return out;
+  };
+  auto conv = [&](const Act<T>& in, const std::string& wname) {
+    const GemmW<T>& w = gw_.at(wname);
+    Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, false);
+    ops.push_back(op_conv(in, w, out));
+    return out;
+  };
+  auto convT = [&](const Act<T>& in, const std::string& wname) {
+    const GemmW<T> w = gw_.at(wname);
+    Act<T> out = new_act(pool, in.g.n, in.g.H * 2, in.g.W * 2, w.N, false);
+    ops.push_back([this, in, w, out](cudaStream_t s) {
+      for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) {
+          int shifts[4];
+          for (int u = 0; u < 2; ++u)
+            for (int v = 0; v < 2; ++v) {
+              const int dy = (a == 0) ? (u == 0 ? 0 : -1) : (u == 0 ? 1 : 0);
+              const int dx = (b == 0) ? (v == 0 ? 0 : -1) : (v == 0 ? 1 : 0);
+              shifts[u * 2 + v] = dy * in.g.Wp + dx;
+            }
+          GemmParams ep{};
+          ep.epi = EPI_STORE;
+          ep.out = out.p; ep.ldc = out.C; ep.bias = w.bias;
+          ep.map_mode = 1; ep.geo_out = out.g; ep.up_a = a; ep.up_b = b;
+          gemm(in, w, a * 2 + b, shifts, 4, ep, s);
+        }
+    });
+    return out;
+  };
+
+  Act<T> r0 = new_act(pool, n, kLatH, kLatW, 256, false);
+  {
+    const float* w0 = f("vae.dec.0.weight");
+    const float* b0 = f("vae.dec.0.bias");
+    ops.push_back([this, r0, w0, b0, pp, n](cudaStream_t s) {
+      conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), n, 4), 128, 0, s>>>(pp->z, n, w0, b0, 0.18215f, r0.g, 256,
+                                                                             r0.p, nullptr);
+      DMB_CHECK_LAUNCH();
+      count();
+    });
+  }
+  Act<T> a = gn8(r0, "vae.dec.1");
+  a = gn8(convT(a, "vae.dec.3"), "vae.dec.4");
+  a = gn8(conv(a, "vae.dec.6"), "vae.dec.7");
+  a = gn8(convT(a, "vae.dec.9"), "vae.dec.10");
+  a = gn8(conv(a, "vae.dec.12"), "vae.dec.13");
+  a = gn8(convT(a, "vae.dec.15"), "vae.dec.16");
+  {
+    const GemmW<T> w = gw_.at("vae.dec.18");
+    ops.push_back([this, a, w, pp](cudaStream_t s) {
+      int shifts[9];
+      for (int ky = 0; ky < 3; ++ky)
+        for (int kx = 0; kx < 3; ++kx) shifts[ky * 3 + kx] = (ky - 1) * a.g.Wp + (kx - 1);
+      GemmParams ep{};
+      ep.epi = EPI_IMAGE;
+      ep.bias = w.bias;
+      ep.img_f32 = pp->img_f32;
+      ep.img_u8 = pp->img_u8;
+      gemm(a, w, 0, shifts, 9, ep, s);
+    });
+  }
+}
+
+template <typename T>
+void Engine<T>::vae_decode(const float* z, int B, float* img_f32, uint8_t* img_u8, cudaStream_t s) {
+  DMB_CUDA(cudaSetDevice(device_));
+  if (!vae_loaded_) fail(5, "VAE decoder weights have not been loaded (dmb_load_vae_dec_weights)");
+  DMB_REQUIRE(B >= 1, "batch must be >= 1");
+  const int kChunk = 32;
+  const size_t lat = static_cast<size_t>(kLatC) * kLatH * kLatW;
+  const size_t img = static_cast<size_t>(3) * 224 * 224;
+  for (int b0 = 0; b0 < B; b0 += kChunk) {
+    const int n = std::min(kChunk, B - b0);
+    if (!vae_plan_ || vae_plan_->B != n) {
+      DMB_CUDA(cudaStreamSynchronize(s));
+      vae_plan_.reset(new VaePlan());
+      build_vae_plan(*vae_plan_, n);
+      DMB_CUDA(cudaDeviceSynchronize());
+    }
+    VaePlan& p = *vae_plan_;
+    p.z = const_cast<float*>(z) + b0 * lat;
+    p.img_f32 = img_f32 ? img_f32 + b0 * img : nullptr;
+    p.img_u8 = img_u8 ? img_u8 + b0 * img : nullptr;
+    for (auto& op : p.ops) op(s);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Debug tap: a named intermediate activation of the last plan, as (n, C, H, W) fp32.
+// ---------------------------------------------------------------------------
+template <typename T>
+void Engine<T>::get_tap(const char* name, float* out, int64_t capacity, int64_t* shape4, cudaStream_t s) {
+  if (!last_plan_) fail(5, "no forward has been run yet");
+  Plan<T>& p = *last_plan_;
+  const std::string nm(name);
+  const int n = p.doubled ? 2 * p.B : p.B;
+  if (nm == "emb" || nm == "embproj") {
+    const int cols = nm == "emb" ? kEmbDim : kProjCols;
+    shape4[0] = n; shape4[1] = cols; shape4[2] = 1; shape4[3] = 1;
+    DMB_REQUIRE(capacity >= static_cast<int64_t>(n) * cols, "tap buffer too small");
+    DMB_CUDA(cudaMemcpyAsync(out, nm == "emb" ? p.emb : p.embproj, static_cast<size_t>(n) * cols * sizeof(float),
+                             cudaMemcpyDefault, s));
+    return;
+  }
+  auto it = p.taps.find(nm);
+  if (it == p.taps.end()) fail(2, "unknown tap '" + nm + "'");
+  const Act<T>& a = it->second;
+  shape4[0] = a.g.n; shape4[1] = a.C; shape4[2] = a.g.H; shape4[3] = a.g.W;
+  const long long total = static_cast<long long>(a.g.n) * a.C * a.g.H * a.g.W;
+  DMB_REQUIRE(capacity >= total, "tap buffer too small");
+  pm_to_nchw_kernel<T><<<cdiv(total, 256), 256, 0, s>>>(a.p, a.g, a.C, a.C, 0, out);
+  DMB_CHECK_LAUNCH();
+}
+
+}  // namespace dmb
+
+namespace dmb {
+
+// ---------------------------------------------------------------------------
+// Op-level entry points (unit tests of the tensor-core kernel through the C ABI).
+// Inputs / outputs are plain fp32 NCHW (or row-major matrices); the conversion to and
+// from the padded pixel-matrix layout happens here.
+// ---------------------------------------------------------------------------
+template <typename T>
+void Engine<T>::op_conv3x3(const float* x, const float* w, int B, int Cin, int Cout, int H, int W, float* out,
+                           cudaStream_t s) {
+  DMB_CUDA(cudaSetDevice(device_));
+  DMB_REQUIRE(Cin % ElemTraits<T>::kChunkK == 0, "Cin must be a multiple of the K chunk (64 bf16 / 32 fp32)");
+  Pool pool;
+  float* wd = pool.alloc_n<float>(9ull * Cout * Cin);
+  DMB_CUDA(cudaMemcpy(wd, w, 9ull * Cout * Cin * sizeof(float), cudaMemcpyDefault));
+  GemmW<T> gw = make_conv3x3_from_ptr(wd, Cout, Cin, pool);
+  Act<T> in = new_act(pool, B, H, W, Cin, false);
+  const int cpad = gw.rows_per_tap;
+  Act<T> o = new_act(pool, B, H, W, cpad, true, gw.rows_per_tap / gw.bn);
+  DMB_CUDA(cudaDeviceSynchronize());
+  const long long tin = static_cast<long long>(B) * Cin * H * W;
+  nchw_to_pm_kernel<T><<<cdiv(tin, 256), 256, 0, s>>>(x, in.g, Cin, in.p);
+  DMB_CHECK_LAUNCH();
+  gw.N = cpad;  // store the padded columns too; only [0, Cout) are read back
+  op_conv(in, gw, o)(s);
+  const long long tout = static_cast<long long>(B) * Cout * H * W;
+  pm_to_nchw_kernel<T><<<cdiv(tout, 256), 256, 0, s>>>(o.p, o.g, Cout, cpad, 0, out);
+  DMB_CHECK_LAUNCH();
+  DMB_CUDA(cudaStreamSynchronize(s));
+}
+
+// out[rows, N] = act(x[rows, K] @ w[N, K]^T + bias); rows are laid out as a 1-pixel-high map.
+template <typename T>
+void Engine<T>::op_linear(const float* x, const float* w, const float* bias, int rows, int K, int N, int act,
+                          float* out, cudaStream_t s) {
+  DMB_CUDA(cudaSetDevice(device_));
+  DMB_REQUIRE(K % ElemTraits<T>::kChunkK == 0, "K must be a multiple of the K chunk (64 bf16 / 32 fp32)");
+  Pool pool;
+  GemmW<T> gw;
+  gw.K = K; gw.N = N; gw.ntaps = 1; gw.bn = pick_block_n(N);
+  gw.rows_per_tap = (N + gw.bn - 1) / gw.bn * gw.bn;
+  float* wd = pool.alloc_n<float>(static_cast<size_t>(N) * K);
+  DMB_CUDA(cudaMemcpy(wd, w, static_cast<size_t>(N) * K * sizeof(float), cudaMemcpyDefault));
+  gw.w = pool.alloc_n<T>(static_cast<size_t>(gw.rows_per_tap) * K);
+  cast_kernel<T><<<cdiv(static_cast<long long>(N) * K, 256), 256>>>(wd, static_cast<long long>(N) * K, gw.w);
+  DMB_CHECK_LAUNCH();
+  gw.tmap = make_tmap<T>(gw.w, K, gw.rows_per_tap, gw.bn);
+  float* bd = nullptr;
+  if (bias) {
+    bd = pool.alloc_n<float>(gw.rows_per_tap);
+    DMB_CUDA(cudaMemcpy(bd, bias, N * sizeof(float), cudaMemcpyDefault));
+  }
+  gw.bias = bd;
+  // rows as an (n=1, H=1, W=rows) map: x is (1, K, 1, rows) in NCHW terms = K-major transposed,
+  // so convert from the row-major matrix directly with a (rows, K) -> PM copy.
+  Act<T> in = new_act(pool, 1, 1, rows, K, false);
+  Act<T> o = new_act(pool, 1, 1, rows, gw.rows_per_tap, false);
+  DMB_CUDA(cudaDeviceSynchronize());
+  // row i of the matrix -> PM row geo_row(0, 0, i); contiguous, so a strided 2D cast does it.
+  float* xd = pool.alloc_n<float>(static_cast<size_t>(rows) * K);
+  DMB_CUDA(cudaMemcpyAsync(xd, x, static_cast<size_t>(rows) * K * sizeof(float), cudaMemcpyDefault, s));
+  cast_kernel<T><<<cdiv(static_cast<long long>(rows) * K, 256), 256, 0, s>>>(
+      xd, static_cast<long long>(rows) * K, in.p + static_cast<size_t>(geo_row(in.g, 0, 0, 0)) * K);
+  DMB_CHECK_LAUNCH();
+  GemmW<T> gw2 = gw;
+  gw2.N = gw.rows_per_tap;
+  op_lin(in, gw2, o, act, nullptr)(s);
+  // read back [rows, N] from PM rows (ld = rows_per_tap)
+  float* od = pool.alloc_n<float>(static_cast<size_t>(rows) * N);
+  // view as NCHW with C = N, H = 1, W = rows gives (N, rows); we want (rows, N): use a transposing readback
+  pm_to_nchw_kernel<T><<<cdiv(static_cast<long long>(rows) * N, 256), 256, 0, s>>>(o.p, o.g, N, gw.rows_per_tap, 0, od);
+  DMB_CHECK_LAUNCH();
+  // od is (N, rows); transpose into out (rows, N)
+  float* ot = pool.alloc_n<float>(static_cast<size_t>(rows) * N);
+  transpose_kernel<<<cdiv(static_cast<long long>(rows) * N, 256), 256, 0, s>>>(od, N, rows, ot, N, 0);
+  DMB_CHECK_LAUNCH();
+  DMB_CUDA(cudaMemcpyAsync(out, ot, static_cast<size_t>(rows) * N * sizeof(float), cudaMemcpyDefault, s));
+  DMB_CUDA(cudaStreamSynchronize(s));
+}
+
+template <typename T>
+void Engine<T>::op_convT4x4(const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int H,
+                            int W, float* out, cudaStream_t s) {
+  DMB_CUDA(cudaSetDevice(device_));
+  DMB_REQUIRE(Cin % ElemTraits<T>::kChunkK == 0, "Cin must be a multiple of the K chunk (64 bf16 / 32 fp32)");
+  Pool pool;
+  GemmW<T> gw;
+  gw.K = Cin; gw.N = Cout; gw.ntaps = 4; gw.bn = pick_block_n(Cout); gw.rows_per_tap = Cout;
+  DMB_REQUIRE(Cout % gw.bn == 0, "Cout must be a multiple of the N tile");
+  float* wd = pool.alloc_n<float>(16ull * Cout * Cin);
+  DMB_CUDA(cudaMemcpy(wd, w, 16ull * Cout * Cin * sizeof(float), cudaMemcpyDefault));
+  gw.w = pool.alloc_n<T>(16ull * Cout * Cin);
+  repack_convT_kernel<T><<<cdiv(16LL * Cout * Cin, 256), 256>>>(wd, Cin, Cout, gw.w);
+  DMB_CHECK_LAUNCH();
+  gw.tmap = make_tmap<T>(gw.w, Cin, 16ull * Cout, gw.bn);
+  float* bd = nullptr;
+  if (bias) {
+    bd = pool.alloc_n<float>(Cout);
+    DMB_CUDA(cudaMemcpy(bd, bias, Cout * sizeof(float), cudaMemcpyDefault));
+  }
+  gw.bias = bd;
+  Act<T> in = new_act(pool, B, H, W, Cin, false);
+  Act<T> o = new_act(pool, B, 2 * H, 2 * W, Cout, false);
+  DMB_CUDA(cudaDeviceSynchronize());
+  nchw_to_pm_kernel<T><<<cdiv(static_cast<long long>(B) * Cin * H * W, 256), 256, 0, s>>>(x, in.g, Cin, in.p);
+  DMB_CHECK_LAUNCH();
+  for (int a = 0; a < 2; ++a)
+    for (int b = 0; b < 2; ++b) {
+      int shifts[4];
+      for (int u = 0; u < 2; ++u)
+        for (int v = 0; v < 2; ++v) {
+          const int dy = (a == 0) ? (u == 0 ? 0 : -1) : (u == 0 ? 1 : 0);
+          const int dx = (b == 0) ? (v == 0 ? 0 : -1) : (v == 0 ? 1 : 0);
+          shifts[u * 2 + v] = dy * in.g.Wp + dx;
+        }
+      GemmParams ep{};
+      ep.epi = EPI_STORE;
+      ep.out = o.p; ep.ldc = o.C; ep.bias = gw.bias;
+      ep.map_mode = 1; ep.geo_out = o.g; ep.up_a = a; ep.up_b = b;
+      gemm(in, gw, a * 2 + b, shifts, 4, ep, s);
+    }
+  pm_to_nchw_kernel<T><<<cdiv(static_cast<long long>(B) * Cout * 4 * H * W, 256), 256, 0, s>>>(o.p, o.g, Cout, Cout, 0, out);
+  DMB_CHECK_LAUNCH();
+  DMB_CUDA(cudaStreamSynchronize(s));
+}
+
+template class Engine<__nv_bfloat16>;
+template class Engine<float>;
+
+IEngine* make_engine_bf16(int device) { return new Engine<__nv_bfloat16>(device); }
+IEngine* make_engine_f32(int device) { return new Engine<float>(device); }
+
+}  // namespace dmb

@@ -1,0 +1,260 @@
+// Multi-tap implicit GEMM on tcgen05 tensor cores with TMEM accumulators, fed by TMA.
+//
+//   D[r, co] = sum_{tap} sum_{ci} A[r + shift(tap), ci] * Wt[tap][co, ci]
+//
+// A is an activation in padded pixel-matrix layout (common.cuh), so a 3x3 / pad-1
+// convolution is 9 taps whose operand tiles are plain 128-row boxes of the same 2D
+// tensor at shifted row coordinates: one TMA box per (tap, K chunk); rows outside the
+// tensor arrive as zeros.  A 1x1 conv / Linear is the one-tap case; a 4x4 stride-2
+// transposed conv is four 4-tap launches (one per output phase) with a scattering row map.
+//
+// CTA = 256 threads, one CTA per SM, persistent over 128 x BLOCK_N output tiles:
+//   warp 0   TMA producer   (one lane)  : fills the smem ring, signals full[s] via complete_tx
+//   warp 1   MMA issuer     (one lane)  : tcgen05.mma SS, commits to empty[s] / tmem_full[a]
+//   warp 2   TMEM allocator
+//   warps 4-7 epilogue      (128 thr)   : tcgen05.ld lane==row, bias/GELU/residual, row
+//                                         statistics for GroupNorm, masked stores
+// Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
+#pragma once
+
+#include "common.cuh"
+
+namespace dmb {
+
+constexpr int kMaxTaps = 9;
+constexpr int kTileM = 128;
+constexpr int kMaxStages = 8;
+
+enum EpiMode : int { EPI_STORE = 0, EPI_IMAGE = 1 };
+
+struct GemmParams {
+  int num_taps;
+  int a_shift[kMaxTaps];  // row shift of the A box per tap
+  int b_row[kMaxTaps];    // first row of the tap's [Cout, Cin] block in the weight matrix
+  int k_chunks;           // Cin / chunkK
+  int m_tiles, n_tiles, block_n, stages;
+  uint32_t idesc;
+  uint32_t tmem_cols;
+
+  Geo geo;     // geometry of the A rows (and of the output rows under the identity map)
+  int epi;     // EpiMode
+  void* out;   // T [rows, ldc]
+  int ldc;
+  int n_valid;            // number of real output columns (<= n_tiles * block_n)
+  const float* bias;      // [n_valid] or null
+  int act;                // 0 none, 1 GELU(erf)
+  const void* residual;   // T [rows, ldc] or null (added after the activation)
+  float2* rowstats;       // [n_tiles][rows_alloc] (sum, sum of squares) or null
+  int rows_alloc;
+  int map_mode;           // 0 identity; 1 = out pixel (2y+up_a, 2x+up_b) of geo_out
+  Geo geo_out;
+  int up_a, up_b;
+  float* img_f32;         // EPI_IMAGE: (n, n_valid, H, W) planar fp32, sigmoid applied
+  uint8_t* img_u8;        // EPI_IMAGE: same, x255 clamp truncate
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const GemmParams p) {
+  using Tr = ElemTraits<T>;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kMaxStages];
+  __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // 128B-swizzled operand tiles need 1024-byte alignment.
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  const uint32_t a_bytes = kTileM * 128;
+  const uint32_t b_bytes = static_cast<uint32_t>(p.block_n) * 128;
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full_bar[a], 1);
+      mbar_init(&tmem_empty_bar[a], 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(&tmem_base_smem, p.tmem_cols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  const int total_tiles = p.m_tiles * p.n_tiles;
+  const int n_iter = p.num_taps * p.k_chunks;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      uint32_t it_global = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n_tile = tile % p.n_tiles;
+        const int m_tile = tile / p.n_tiles;
+        const int m0 = m_tile * kTileM;
+        const int n0 = n_tile * p.block_n;
+        for (int tap = 0; tap < p.num_taps; ++tap) {
+          const int a_row = m0 + p.a_shift[tap];
+          const int b_row = p.b_row[tap] + n0;
+          for (int kc = 0; kc < p.k_chunks; ++kc, ++it_global) {
+            const uint32_t s = it_global % p.stages;
+            const uint32_t ph = (it_global / p.stages) & 1;
+            mbar_wait(&empty_bar[s], ph ^ 1);
+            uint8_t* sa = smem + s * stage_bytes;
+            mbar_expect_tx(&full_bar[s], stage_bytes);
+            tma_load_2d(sa, &tmap_a, &full_bar[s], kc * Tr::kChunkK, a_row);
+            tma_load_2d(sa + a_bytes, &tmap_b, &full_bar[s], kc * Tr::kChunkK, b_row);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      uint32_t it_global = 0;
+      uint32_t tile_count = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tile_count) {
+        const uint32_t as = tile_count & 1;
+        const uint32_t aph = (tile_count >> 1) & 1;
+        mbar_wait(&tmem_empty_bar[as], aph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * p.block_n;
+        for (int it = 0; it < n_iter; ++it, ++it_global) {
+          const uint32_t s = it_global % p.stages;
+          const uint32_t ph = (it_global / p.stages) & 1;
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * stage_bytes);
+          const uint64_t adesc = umma_desc_sw128(sa);
+          const uint64_t bdesc = umma_desc_sw128(sa + a_bytes);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            // advance 32 bytes (one MMA K step) inside the 128-byte swizzle row
+            umma_ss<Tr::kTf32>(d_tmem, adesc + (k * 2), bdesc + (k * 2), p.idesc, (it > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);
+        }
+        umma_commit(&tmem_full_bar[as]);
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------- epilogue
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    T* out = reinterpret_cast<T*>(p.out);
+    const T* residual = reinterpret_cast<const T*>(p.residual);
+    uint32_t tile_count = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tile_count) {
+      const int n_tile = tile % p.n_tiles;
+      const int m_tile = tile / p.n_tiles;
+      const int n0 = n_tile * p.block_n;
+      const int r = m_tile * kTileM + q * 32 + lane;
+      int b = 0, y = 0, x = 0;
+      const bool valid = geo_decode(p.geo, r, b, y, x);
+      int out_r = r;
+      if (p.map_mode == 1 && valid) out_r = geo_row(p.geo_out, b, 2 * y + p.up_a, 2 * x + p.up_b);
+
+      const uint32_t as = tile_count & 1;
+      const uint32_t aph = (tile_count >> 1) & 1;
+      mbar_wait(&tmem_full_bar[as], aph);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * p.block_n;
+
+      if (p.epi == EPI_IMAGE) {
+        float v[16];
+        tmem_ld16(t_row, v);
+        tmem_ld_wait();
+        if (valid) {
+          const size_t plane = static_cast<size_t>(p.geo.H) * p.geo.W;
+          for (int c = 0; c < p.n_valid; ++c) {
+            float s = v[c] + (p.bias ? __ldg(p.bias + c) : 0.f);
+            s = 1.0f / (1.0f + expf(-s));
+            const size_t o = (static_cast<size_t>(b) * p.n_valid + c) * plane + static_cast<size_t>(y) * p.geo.W + x;
+            if (p.img_f32) p.img_f32[o] = s;
+            if (p.img_u8) p.img_u8[o] = static_cast<uint8_t>(fminf(fmaxf(s * 255.0f, 0.f), 255.f));
+          }
+        }
+      } else {
+        float sum = 0.f, sumsq = 0.f;
+        for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+          float v[32];
+          if (p.block_n - c0 >= 32) {
+            tmem_ld32(t_row + c0, v);
+          } else {
+            tmem_ld16(t_row + c0, v);
+#pragma unroll
+            for (int j = 16; j < 32; ++j) v[j] = 0.f;
+          }
+          tmem_ld_wait();
+          const int ncols = min(32, p.block_n - c0);
+          if (valid) {
+            const int col0 = n0 + c0;
+            if (p.bias) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j < ncols) v[j] += __ldg(p.bias + col0 + j);
+            }
+            if (p.act == 1) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+            }
+            if (residual) {
+              const T* rp = residual + static_cast<size_t>(r) * p.ldc + col0;
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                if (j < ncols) {
+                  float rv[8];
+                  load8(rp + j, rv);
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) v[j + i] += rv[i];
+                }
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (j < ncols) {
+                sum += v[j];
+                sumsq += v[j] * v[j];
+              }
+            }
+            T* op = out + static_cast<size_t>(out_r) * p.ldc + col0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              if (j < ncols) store8(op + j, v + j);
+            }
+          }
+        }
+        if (p.rowstats && valid) {
+          p.rowstats[static_cast<size_t>(n_tile) * p.rows_alloc + r] = make_float2(sum, sumsq);
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty_bar[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+}  // namespace dmb

@@ -1,0 +1,678 @@
+// Non-GEMM kernels of the sampling path: embedding, first/last convolutions of the
+// U-Net, GroupNorm application, pooling / upsampling glue, LayerNorm, the attention core,
+// the fused CFG-combine + DDPM update, and the VAE decoder's GroupNorm(8) pair.
+// All activations are padded pixel matrices (common.cuh); T is the storage type.
+#pragma once
+
+#include "common.cuh"
+#include "philox.cuh"
+
+namespace dmb {
+
+constexpr int kEmbDim = 256;
+constexpr int kCondDim = 12;
+constexpr int kProjCols = 896;  // 128 + 256 + 256 + 128 + 64 + 64 emb_layer outputs
+constexpr int kLatC = 4;
+
+// ---------------------------------------------------------------------------
+// Embedding: pos_encoding(t) + class_emb[y] + cond_mlp([vals|mask]) and the six
+// Linear(SiLU(emb)) projections of Down/Up.  unet_cond.py:155-167, 62-65, 82-85;
+// unet_cond_geom.py:89-95.  One CTA (256 threads) per effective sample.
+// ---------------------------------------------------------------------------
+struct EmbWeights {
+  const float* class_emb;  // [4][256]
+  const float* w1t;        // [24][256]  cond_mlp.0 transposed
+  const float* b1;         // [256]
+  const float* w2t;        // [256][256] cond_mlp.2 transposed
+  const float* b2;         // [256]
+  const float* inv_freq;   // [128]
+  const float* projt;      // [256][896] six emb_layer weights, transposed, concatenated
+  const float* projb;      // [896]
+};
+
+static __global__ void __launch_bounds__(256)
+emb_kernel(EmbWeights w, const long long* __restrict__ t_vec, const long long* __restrict__ y,
+           const int* __restrict__ dyn_flags /* {null_label, has_cond} */,
+           const float* __restrict__ vals, const float* __restrict__ mask,
+           int B, int doubled, float* __restrict__ emb_out, float* __restrict__ proj_out) {
+  __shared__ float feat[2 * kCondDim];
+  __shared__ float h1[kEmbDim];
+  __shared__ float semb[kEmbDim];
+  const int be = blockIdx.x;
+  const int b = doubled ? (be % B) : be;
+  const int half = doubled ? (be / B) : 1;
+  const int tid = threadIdx.x;
+  const int null_label = dyn_flags[0];
+  const bool has_cond = dyn_flags[1] != 0;
+  long long yv = (half == 0) ? static_cast<long long>(null_label) : y[b];
+
+  float cond = 0.f;
+  if (has_cond) {
+    if (tid < kCondDim) feat[tid] = vals[b * kCondDim + tid];
+    else if (tid < 2 * kCondDim) feat[tid] = mask[b * kCondDim + tid - kCondDim];
+    __syncthreads();
+    float h = w.b1[tid];
+#pragma unroll
+    for (int i = 0; i < 2 * kCondDim; ++i) h = fmaf(feat[i], w.w1t[i * kEmbDim + tid], h);
+    h1[tid] = silu(h);
+    __syncthreads();
+    float c = w.b2[tid];
+    for (int i = 0; i < kEmbDim; ++i) c = fmaf(h1[i], w.w2t[i * kEmbDim + tid], c);
+    cond = c;
+  }
+  const float tf = static_cast<float>(t_vec[b]);
+  const float arg = tf * w.inv_freq[tid & 127];
+  const float pe = (tid < 128) ? sinf(arg) : cosf(arg);
+  float e = pe + w.class_emb[yv * kEmbDim + tid];
+  if (has_cond) e = e + cond;
+  if (emb_out) emb_out[be * kEmbDim + tid] = e;
+  semb[tid] = silu(e);
+  __syncthreads();
+  for (int o = tid; o < kProjCols; o += 256) {
+    float acc = w.projb[o];
+    for (int i = 0; i < kEmbDim; ++i) acc = fmaf(semb[i], w.projt[i * kProjCols + o], acc);
+    proj_out[be * kProjCols + o] = acc;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Direct 3x3 / pad 1 convolution from an fp32 NCHW latent (4 channels) into a PM
+// activation.  Used for inc.double_conv.0 (4->64, no bias, GroupNorm row statistics)
+// and the VAE decoder's dec.0 (4->256, bias, input divided by the VAE scale factor).
+// Thread = one pixel x 64 output channels; blockIdx.z selects the 64-channel group.
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(128)
+conv_in_kernel(const float* __restrict__ x, int B_src, const float* __restrict__ w_oihw,
+               const float* __restrict__ bias, float in_div, Geo g, int cout,
+               T* __restrict__ out, float2* __restrict__ rowstats) {
+  __shared__ float ws[36 * 64];
+  const int co0 = blockIdx.z * 64;
+  for (int i = threadIdx.x; i < 36 * 64; i += blockDim.x) {
+    const int k = i / 64, co = i % 64;  // k = ci*9 + ky*3 + kx
+    ws[i] = w_oihw[(co0 + co) * 36 + k];
+  }
+  __syncthreads();
+  const int be = blockIdx.y;
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= g.H * g.W) return;
+  const int y = pix / g.W, xx = pix % g.W;
+  const float* xs = x + static_cast<size_t>(be % B_src) * kLatC * g.H * g.W;
+  float in[36];
+#pragma unroll
+  for (int ci = 0; ci < kLatC; ++ci)
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const int iy = y + ky - 1, ix = xx + kx - 1;
+        float v = 0.f;
+        if (iy >= 0 && iy < g.H && ix >= 0 && ix < g.W) v = xs[(ci * g.H + iy) * g.W + ix] / in_div;
+        in[ci * 9 + ky * 3 + kx] = v;
+      }
+  float acc[64];
+#pragma unroll
+  for (int co = 0; co < 64; ++co) acc[co] = bias ? bias[co0 + co] : 0.f;
+#pragma unroll
+  for (int k = 0; k < 36; ++k) {
+    const float v = in[k];
+#pragma unroll
+    for (int co = 0; co < 64; ++co) acc[co] = fmaf(v, ws[k * 64 + co], acc[co]);
+  }
+  const int r = geo_row(g, be, y, xx);
+  T* op = out + static_cast<size_t>(r) * cout + co0;
+  float s = 0.f, ss = 0.f;
+#pragma unroll
+  for (int co = 0; co < 64; co += 8) {
+    store8(op + co, acc + co);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { s += acc[co + i]; ss += acc[co + i] * acc[co + i]; }
+  }
+  if (rowstats) rowstats[r] = make_float2(s, ss);
+}
+
+// ---------------------------------------------------------------------------
+// GroupNorm(1, C) application.  The producing conv left per-row (sum, sumsq) partials;
+// each CTA first reduces its sample's partials in a fixed order (double), then normalises
+// its slice.  mode: 0 affine only, 1 GELU, 2 GELU(residual + .), 3 + emb[b, c].
+// models/unet_cond.py:18-28, 67-70, 98-100.
+// ---------------------------------------------------------------------------
+enum GnMode : int { GN_NONE = 0, GN_GELU = 1, GN_RES_GELU = 2, GN_ADD_EMB = 3 };
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats, int n_stat_tiles,
+                 int rows_alloc, const float* __restrict__ gamma, const float* __restrict__ beta,
+                 int mode, const T* __restrict__ residual, const float* __restrict__ embproj,
+                 int emb_off, Geo g, int C, T* __restrict__ out) {
+  __shared__ double red[2][256];
+  __shared__ float s_mean, s_rstd;
+  const int b = blockIdx.y;
+  const int tid = threadIdx.x;
+  const int HW = g.H * g.W;
+  double s1 = 0.0, s2 = 0.0;
+  for (int i = tid; i < HW; i += 256) {
+    const int r = geo_row(g, b, i / g.W, i % g.W);
+    for (int tn = 0; tn < n_stat_tiles; ++tn) {
+      const float2 v = rowstats[static_cast<size_t>(tn) * rows_alloc + r];
+      s1 += v.x; s2 += v.y;
+    }
+  }
+  red[0][tid] = s1; red[1][tid] = s2;
+  __syncthreads();
+  for (int off = 128; off > 0; off >>= 1) {
+    if (tid < off) { red[0][tid] += red[0][tid + off]; red[1][tid] += red[1][tid + off]; }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const double cnt = static_cast<double>(HW) * C;
+    const double mean = red[0][0] / cnt;
+    double var = red[1][0] / cnt - mean * mean;
+    if (var < 0.0) var = 0.0;
+    s_mean = static_cast<float>(mean);
+    s_rstd = static_cast<float>(1.0 / sqrt(var + 1e-5));
+  }
+  __syncthreads();
+  const float mean = s_mean, rstd = s_rstd;
+  const int vpr = C / 8;
+  const int total = HW * vpr;
+  const int per = (total + gridDim.x - 1) / gridDim.x;
+  const int begin = blockIdx.x * per;
+  const int end = min(total, begin + per);
+  for (int v = begin + tid; v < end; v += 256) {
+    const int pix = v / vpr, c0 = (v % vpr) * 8;
+    const size_t off = static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * C + c0;
+    float xv[8];
+    load8(raw + off, xv);
+    const float4 ga = *reinterpret_cast<const float4*>(gamma + c0), gb = *reinterpret_cast<const float4*>(gamma + c0 + 4);
+    const float4 ba = *reinterpret_cast<const float4*>(beta + c0), bb = *reinterpret_cast<const float4*>(beta + c0 + 4);
+    const float gm[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
+    const float bt[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) xv[i] = (xv[i] - mean) * rstd * gm[i] + bt[i];
+    if (mode == GN_GELU) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xv[i] = gelu_erf(xv[i]);
+    } else if (mode == GN_RES_GELU) {
+      float rv[8];
+      load8(residual + off, rv);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xv[i] = gelu_erf(rv[i] + xv[i]);
+    } else if (mode == GN_ADD_EMB) {
+      const float* e = embproj + static_cast<size_t>(b) * kProjCols + emb_off + c0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xv[i] += e[i];
+    }
+    store8(out + off, xv);
+  }
+}
+
+// MaxPool2d(2), floor.  models/unet_cond.py:58.
+template <typename T>
+__global__ void maxpool2_kernel(const T* __restrict__ in, Geo gi, Geo go, int C, T* __restrict__ out) {
+  const int vpr = C / 8;
+  const long long total = static_cast<long long>(go.n) * go.H * go.W * vpr;
+  const long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (v >= total) return;
+  const int c0 = static_cast<int>(v % vpr) * 8;
+  long long pix = v / vpr;
+  const int x = static_cast<int>(pix % go.W); pix /= go.W;
+  const int y = static_cast<int>(pix % go.H);
+  const int b = static_cast<int>(pix / go.H);
+  float m[8], t[8];
+  load8(in + static_cast<size_t>(geo_row(gi, b, 2 * y, 2 * x)) * C + c0, m);
+  load8(in + static_cast<size_t>(geo_row(gi, b, 2 * y, 2 * x + 1)) * C + c0, t);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m[i] = fmaxf(m[i], t[i]);
+  load8(in + static_cast<size_t>(geo_row(gi, b, 2 * y + 1, 2 * x)) * C + c0, t);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m[i] = fmaxf(m[i], t[i]);
+  load8(in + static_cast<size_t>(geo_row(gi, b, 2 * y + 1, 2 * x + 1)) * C + c0, t);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m[i] = fmaxf(m[i], t[i]);
+  store8(out + static_cast<size_t>(geo_row(go, b, y, x)) * C + c0, m);
+}
+
+// Up-stage input: cat([skip, pad(bilinear_x2_align_corners(x))], channel).
+// models/unet_cond.py:76, 87-97.  Output geometry = skip geometry.
+template <typename T>
+__global__ void upcat_kernel(const T* __restrict__ skip, int Cs, const T* __restrict__ xin, Geo gx, int Cx,
+                             Geo go, T* __restrict__ out) {
+  const int C = Cs + Cx;
+  const int vpr = C / 8;
+  const long long total = static_cast<long long>(go.n) * go.H * go.W * vpr;
+  const long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (v >= total) return;
+  const int c0 = static_cast<int>(v % vpr) * 8;
+  long long pix = v / vpr;
+  const int x = static_cast<int>(pix % go.W); pix /= go.W;
+  const int y = static_cast<int>(pix % go.H);
+  const int b = static_cast<int>(pix / go.H);
+  const int r = geo_row(go, b, y, x);
+  float o[8];
+  if (c0 < Cs) {
+    load8(skip + static_cast<size_t>(r) * Cs + c0, o);
+  } else {
+    const int cx = c0 - Cs;
+    const int Hu = 2 * gx.H, Wu = 2 * gx.W;
+    if (y < Hu && x < Wu) {
+      // align_corners=True: src = dst * (in - 1) / (out - 1), computed in fp32 like ATen.
+      const float sy = (Hu > 1) ? static_cast<float>(gx.H - 1) / static_cast<float>(Hu - 1) : 0.f;
+      const float sx = (Wu > 1) ? static_cast<float>(gx.W - 1) / static_cast<float>(Wu - 1) : 0.f;
+      const float fy = sy * y, fx = sx * x;
+      const int y0 = static_cast<int>(fy), x0 = static_cast<int>(fx);
+      const int y1 = y0 + ((y0 < gx.H - 1) ? 1 : 0), x1 = x0 + ((x0 < gx.W - 1) ? 1 : 0);
+      const float ly1 = fy - y0, ly0 = 1.f - ly1, lx1 = fx - x0, lx0 = 1.f - lx1;
+      float v00[8], v01[8], v10[8], v11[8];
+      load8(xin + static_cast<size_t>(geo_row(gx, b, y0, x0)) * Cx + cx, v00);
+      load8(xin + static_cast<size_t>(geo_row(gx, b, y0, x1)) * Cx + cx, v01);
+      load8(xin + static_cast<size_t>(geo_row(gx, b, y1, x0)) * Cx + cx, v10);
+      load8(xin + static_cast<size_t>(geo_row(gx, b, y1, x1)) * Cx + cx, v11);
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        o[i] = ly0 * (lx0 * v00[i] + lx1 * v01[i]) + ly1 * (lx0 * v10[i] + lx1 * v11[i]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = 0.f;
+    }
+  }
+  store8(out + static_cast<size_t>(r) * C + c0, o);
+}
+
+// LayerNorm over channels of every real pixel (token).  One warp per token, EPL = C/32
+// contiguous channels per lane.  models/unet_cond.py:37, 39, 48.
+template <typename T, int EPL>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const T* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
+                 Geo g, T* __restrict__ out) {
+  constexpr int C = EPL * 32;
+  const int lane = threadIdx.x & 31;
+  const long long tok = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long ntok = static_cast<long long>(g.n) * g.H * g.W;
+  if (tok >= ntok) return;
+  const int HW = g.H * g.W;
+  const int b = static_cast<int>(tok / HW);
+  const int pix = static_cast<int>(tok % HW);
+  const size_t off = static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * C + lane * EPL;
+  float v[EPL];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < EPL; ++i) { v[i] = to_f32(in[off + i]); s += v[i]; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s * (1.0f / C);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < EPL; ++i) { const float d = v[i] - mean; q += d * d; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  const float rstd = rsqrtf(q * (1.0f / C) + 1e-5f);
+#pragma unroll
+  for (int i = 0; i < EPL; ++i) {
+    const int c = lane * EPL + i;
+    out[off + i] = from_f32<T>((v[i] - mean) * rstd * w[c] + bias[c]);
+  }
+}
+
+// Attention core: softmax(q k^T / sqrt(D)) v per (sample, head) over the real pixels.
+// qkv is the in-proj output [rows, 3E] (q | k | v).  K and V of the head live in shared
+// memory as fp32; one thread owns one query and runs an online softmax over key blocks.
+// models/unet_cond.py:36, 49 (nn.MultiheadAttention, 4 heads, batch_first).
+template <typename T, int D>
+__global__ void __launch_bounds__(128)
+attention_kernel(const T* __restrict__ qkv, Geo g, int E, T* __restrict__ out) {
+  extern __shared__ float kv[];
+  const int L = g.H * g.W;
+  float* Ks = kv;
+  float* Vs = kv + static_cast<size_t>(L) * D;
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int ld = 3 * E;
+  constexpr int VPT = D / 8;
+  for (int idx = threadIdx.x; idx < L * VPT; idx += blockDim.x) {
+    const int pix = idx / VPT, dv = (idx % VPT) * 8;
+    const size_t ro = static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * ld + h * D + dv;
+    load8(qkv + ro + E, Ks + pix * D + dv);
+    load8(qkv + ro + 2 * E, Vs + pix * D + dv);
+  }
+  __syncthreads();
+  const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (qi >= L) return;
+  const int qrow = geo_row(g, b, qi / g.W, qi % g.W);
+  float q[D], acc[D];
+  {
+    const T* qp = qkv + static_cast<size_t>(qrow) * ld + h * D;
+    const float sc = rsqrtf(static_cast<float>(D)) * 1.4426950408889634f;  // 1/sqrt(D) * log2(e)
+#pragma unroll
+    for (int d0 = 0; d0 < D; d0 += 8) {
+      load8(qp + d0, q + d0);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { q[d0 + i] *= sc; acc[d0 + i] = 0.f; }
+    }
+  }
+  float m = -INFINITY, l = 0.f;
+  constexpr int KB = 8;
+  for (int j0 = 0; j0 < L; j0 += KB) {
+    float s[KB];
+    float bm = -INFINITY;
+#pragma unroll
+    for (int jj = 0; jj < KB; ++jj) {
+      const int j = j0 + jj;
+      float dot = -INFINITY;
+      if (j < L) {
+        const float4* kp = reinterpret_cast<const float4*>(Ks + j * D);
+        dot = 0.f;
+#pragma unroll
+        for (int d4 = 0; d4 < D / 4; ++d4) {
+          const float4 kk = kp[d4];
+          dot = fmaf(q[4 * d4], kk.x, dot); dot = fmaf(q[4 * d4 + 1], kk.y, dot);
+          dot = fmaf(q[4 * d4 + 2], kk.z, dot); dot = fmaf(q[4 * d4 + 3], kk.w, dot);
+        }
+      }
+      s[jj] = dot;
+      bm = fmaxf(bm, dot);
+    }
+    const float mn = fmaxf(m, bm);
+    const float corr = exp2f(m - mn);
+    l *= corr;
+#pragma unroll
+    for (int d = 0; d < D; ++d) acc[d] *= corr;
+#pragma unroll
+    for (int jj = 0; jj < KB; ++jj) {
+      const int j = j0 + jj;
+      if (j < L) {
+        const float pj = exp2f(s[jj] - mn);
+        l += pj;
+        const float4* vp = reinterpret_cast<const float4*>(Vs + j * D);
+#pragma unroll
+        for (int d4 = 0; d4 < D / 4; ++d4) {
+          const float4 vv = vp[d4];
+          acc[4 * d4] = fmaf(pj, vv.x, acc[4 * d4]); acc[4 * d4 + 1] = fmaf(pj, vv.y, acc[4 * d4 + 1]);
+          acc[4 * d4 + 2] = fmaf(pj, vv.z, acc[4 * d4 + 2]); acc[4 * d4 + 3] = fmaf(pj, vv.w, acc[4 * d4 + 3]);
+        }
+      }
+    }
+    m = mn;
+  }
+  const float inv = 1.0f / l;
+  T* op = out + static_cast<size_t>(qrow) * E + h * D;
+#pragma unroll
+  for (int d0 = 0; d0 < D; d0 += 8) {
+    float o[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = acc[d0 + i] * inv;
+    store8(op + d0, o);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Tail of one reverse step, fused: the `out` 1x1 conv (64 -> 4, bias) on both CFG halves,
+// eps = eps_u + g (eps_c - eps_u), the DDPM posterior mean and the noise injection.
+// unet_cond.py:153; diff.py:141-162.  Thread = one latent pixel (4 channels).
+// feat rows [0, B) are the null-label pass, rows [B, 2B) the class-label pass.
+// ---------------------------------------------------------------------------
+struct StepParams {
+  const float* x_in;       // (B,4,H,W) fp32
+  float* x_out;            // may alias x_in
+  const long long* t_vec;  // (B,) current timestep per sample, 1..T
+  const float* coef;       // (T,3): (1-a)/sqrt(1-abar), sqrt(a), sigma
+  int T;
+  int slot_t0;             // noise / dump slot of a step = slot_t0 - t
+  float guidance;
+  const float* noise;       // injected noise or null (then Philox)
+  long long noise_step_stride;  // elements between consecutive steps' noise (0: single step)
+  unsigned long long seed;
+  unsigned long long sample_offset;
+  float* eps_out;          // optional (B,4,H,W) or, with dump stride, (T,B,4,H,W)
+  float* x_dump;           // optional (steps,B,4,H,W): x_t before the step
+  long long dump_step_stride;
+  const float* w_out;      // [4][64]
+  const float* b_out;      // [4]
+};
+
+template <typename T>
+__global__ void __launch_bounds__(128)
+cfg_step_kernel(const T* __restrict__ feat, Geo g, int B, const StepParams* __restrict__ pp) {
+  const StepParams p = *pp;
+  __shared__ float ws[kLatC * 64];
+  __shared__ float bs[kLatC];
+  for (int i = threadIdx.x; i < kLatC * 64; i += blockDim.x) ws[i] = p.w_out[i];
+  if (threadIdx.x < kLatC) bs[threadIdx.x] = p.b_out[threadIdx.x];
+  __syncthreads();
+  const int HW = g.H * g.W;
+  const int b = blockIdx.y;
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= HW) return;
+  const int y = pix / g.W, x = pix % g.W;
+  float eu[kLatC], ec[kLatC];
+#pragma unroll
+  for (int c = 0; c < kLatC; ++c) { eu[c] = bs[c]; ec[c] = bs[c]; }
+  const T* fu = feat + static_cast<size_t>(geo_row(g, b, y, x)) * 64;
+  const T* fc = feat + static_cast<size_t>(geo_row(g, b + B, y, x)) * 64;
+#pragma unroll
+  for (int k0 = 0; k0 < 64; k0 += 8) {
+    float vu[8], vc[8];
+    load8(fu + k0, vu);
+    load8(fc + k0, vc);
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int c = 0; c < kLatC; ++c) {
+        eu[c] = fmaf(vu[i], ws[c * 64 + k0 + i], eu[c]);
+        ec[c] = fmaf(vc[i], ws[c * 64 + k0 + i], ec[c]);
+      }
+  }
+  const long long t = p.t_vec[b];
+  const int slot = p.slot_t0 - static_cast<int>(t);
+  const float c1 = p.coef[(t - 1) * 3 + 0], sqrt_a = p.coef[(t - 1) * 3 + 1], sigma = p.coef[(t - 1) * 3 + 2];
+  float nz[kLatC] = {0.f, 0.f, 0.f, 0.f};
+  if (t != 1) {
+    if (p.noise) {
+      const float* np = p.noise + p.noise_step_stride * slot + static_cast<size_t>(b) * kLatC * HW + pix;
+#pragma unroll
+      for (int c = 0; c < kLatC; ++c) nz[c] = np[c * HW];
+    } else {
+      philox_normal4(p.seed, p.sample_offset + b, static_cast<uint32_t>(t), static_cast<uint32_t>(pix), nz);
+    }
+  }
+  const size_t base = static_cast<size_t>(b) * kLatC * HW + pix;
+#pragma unroll
+  for (int c = 0; c < kLatC; ++c) {
+    const float xv = p.x_in[base + c * HW];
+    const float eps = eu[c] + p.guidance * (ec[c] - eu[c]);
+    if (p.x_dump) p.x_dump[p.dump_step_stride * slot + base + c * HW] = xv;
+    if (p.eps_out) p.eps_out[p.dump_step_stride * slot + base + c * HW] = eps;
+    const float mu = (xv - c1 * eps) / sqrt_a;
+    p.x_out[base + c * HW] = mu + nz[c] * sigma;
+  }
+}
+
+// `out` conv alone (eager forward): eps (B,4,H,W) fp32.
+template <typename T>
+__global__ void __launch_bounds__(128)
+out_conv_kernel(const T* __restrict__ feat, Geo g, const float* __restrict__ w_out,
+                const float* __restrict__ b_out, float* __restrict__ eps) {
+  __shared__ float ws[kLatC * 64];
+  for (int i = threadIdx.x; i < kLatC * 64; i += blockDim.x) ws[i] = w_out[i];
+  __syncthreads();
+  const int HW = g.H * g.W;
+  const int b = blockIdx.y;
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= HW) return;
+  float e[kLatC];
+#pragma unroll
+  for (int c = 0; c < kLatC; ++c) e[c] = b_out[c];
+  const T* f = feat + static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * 64;
+#pragma unroll
+  for (int k0 = 0; k0 < 64; k0 += 8) {
+    float v[8];
+    load8(f + k0, v);
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int c = 0; c < kLatC; ++c) e[c] = fmaf(v[i], ws[c * 64 + k0 + i], e[c]);
+  }
+#pragma unroll
+  for (int c = 0; c < kLatC; ++c) eps[(static_cast<size_t>(b) * kLatC + c) * HW + pix] = e[c];
+}
+
+// GeomHead: mean over pixels -> Linear(64,256) -> SiLU -> Linear(256,12).
+// unet_cond_geom.py:8-23.  One CTA per sample.
+template <typename T>
+__global__ void __launch_bounds__(256)
+geom_head_kernel(const T* __restrict__ feat, Geo g, const float* __restrict__ w1t, const float* __restrict__ b1,
+                 const float* __restrict__ w2, const float* __restrict__ b2, int out_dim, float* __restrict__ geom) {
+  __shared__ float part[4][64];
+  __shared__ float gmean[64];
+  __shared__ float hid[256];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const int c = tid & 63, grp = tid >> 6;
+  const int HW = g.H * g.W;
+  float s = 0.f;
+  for (int pix = grp; pix < HW; pix += 4)
+    s += to_f32(feat[static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * 64 + c]);
+  part[grp][c] = s;
+  __syncthreads();
+  if (tid < 64) gmean[tid] = (part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid]) / static_cast<float>(HW);
+  __syncthreads();
+  float h = b1[tid];
+  for (int i = 0; i < 64; ++i) h = fmaf(gmean[i], w1t[i * 256 + tid], h);
+  hid[tid] = silu(h);
+  __syncthreads();
+  if (tid < out_dim) {
+    float o = b2[tid];
+    for (int i = 0; i < 256; ++i) o = fmaf(hid[i], w2[tid * 256 + i], o);
+    geom[b * out_dim + tid] = o;
+  }
+}
+
+// t_vec[b] -= 1 (end of a captured step).
+static __global__ void advance_t_kernel(long long* t_vec, int B) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B) t_vec[i] -= 1;
+}
+static __global__ void fill_t_kernel(long long* t_vec, int B, long long t) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B) t_vec[i] = t;
+}
+
+// Standalone Philox fill (B,4,HW) for step t: the exact values cfg_step_kernel would draw.
+static __global__ void philox_fill_kernel(float* out, int B, int HW, unsigned long long seed,
+                                   unsigned long long sample_offset, unsigned int step) {
+  const int b = blockIdx.y;
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= HW) return;
+  float nz[4];
+  philox_normal4(seed, sample_offset + b, step, static_cast<uint32_t>(pix), nz);
+#pragma unroll
+  for (int c = 0; c < 4; ++c) out[(static_cast<size_t>(b) * 4 + c) * HW + pix] = nz[c];
+}
+
+// ---------------------------------------------------------------------------
+// VAE decoder GroupNorm(8, C) + GELU, two passes.  models/vae.py:37-47.
+// Pass 1: per (sample, chunk, group) partial sums.  blockDim 256 is a multiple of the
+// vectors per row, so every thread stays inside one group.
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+gn8_stats_kernel(const T* __restrict__ raw, Geo g, int C, double2* __restrict__ partial) {
+  __shared__ double red[2][256];
+  const int b = blockIdx.y, tid = threadIdx.x;
+  const int vpr = C / 8;
+  const int HW = g.H * g.W;
+  const int total = HW * vpr;
+  const int per = (((total + gridDim.x - 1) / gridDim.x) + vpr - 1) / vpr * vpr;
+  const int begin = blockIdx.x * per;
+  const int end = min(total, begin + per);
+  float s = 0.f, ss = 0.f;
+  for (int v = begin + tid; v < end; v += 256) {
+    const int pix = v / vpr, c0 = (v % vpr) * 8;
+    float xv[8];
+    load8(raw + static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * C + c0, xv);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { s += xv[i]; ss += xv[i] * xv[i]; }
+  }
+  red[0][tid] = s; red[1][tid] = ss;
+  __syncthreads();
+  if (tid < 8) {
+    // thread j's vector column is j % vpr (begin is a multiple of vpr); group = column / (vpr/8)
+    double a = 0.0, q = 0.0;
+    const int vpg = vpr / 8;
+    for (int j = 0; j < 256; ++j) {
+      if (((j % vpr) / vpg) == tid) { a += red[0][j]; q += red[1][j]; }
+    }
+    partial[(static_cast<size_t>(b) * gridDim.x + blockIdx.x) * 8 + tid] = make_double2(a, q);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+gn8_apply_gelu_kernel(const T* __restrict__ raw, const double2* __restrict__ partial, int n_chunks_stats,
+                      const float* __restrict__ gamma, const float* __restrict__ beta, Geo g, int C,
+                      T* __restrict__ out) {
+  __shared__ float s_mean[8], s_rstd[8];
+  const int b = blockIdx.y, tid = threadIdx.x;
+  const int HW = g.H * g.W;
+  if (tid < 8) {
+    double a = 0.0, q = 0.0;
+    for (int k = 0; k < n_chunks_stats; ++k) {
+      const double2 v = partial[(static_cast<size_t>(b) * n_chunks_stats + k) * 8 + tid];
+      a += v.x; q += v.y;
+    }
+    const double cnt = static_cast<double>(HW) * (C / 8);
+    const double mean = a / cnt;
+    double var = q / cnt - mean * mean;
+    if (var < 0.0) var = 0.0;
+    s_mean[tid] = static_cast<float>(mean);
+    s_rstd[tid] = static_cast<float>(1.0 / sqrt(var + 1e-5));
+  }
+  __syncthreads();
+  const int vpr = C / 8, vpg = vpr / 8;
+  const int total = HW * vpr;
+  const int per = (total + gridDim.x - 1) / gridDim.x;
+  const int begin = blockIdx.x * per;
+  const int end = min(total, begin + per);
+  for (int v = begin + tid; v < end; v += 256) {
+    const int pix = v / vpr, vc = v % vpr, c0 = vc * 8;
+    const int grp = vc / vpg;
+    const float mean = s_mean[grp], rstd = s_rstd[grp];
+    const size_t off = static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * C + c0;
+    float xv[8];
+    load8(raw + off, xv);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) xv[i] = gelu_erf((xv[i] - mean) * rstd * gamma[c0 + i] + beta[c0 + i]);
+    store8(out + off, xv);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Layout conversion for the op-level test entry points and debug taps.
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void nchw_to_pm_kernel(const float* __restrict__ in, Geo g, int C, T* __restrict__ out) {
+  const long long total = static_cast<long long>(g.n) * C * g.H * g.W;
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  // iterate in PM order (channel fastest) for coalesced writes
+  const int c = static_cast<int>(i % C);
+  long long pix = i / C;
+  const int x = static_cast<int>(pix % g.W); pix /= g.W;
+  const int y = static_cast<int>(pix % g.H);
+  const int b = static_cast<int>(pix / g.H);
+  out[static_cast<size_t>(geo_row(g, b, y, x)) * C + c] =
+      from_f32<T>(in[((static_cast<size_t>(b) * C + c) * g.H + y) * g.W + x]);
+}
+template <typename T>
+__global__ void pm_to_nchw_kernel(const T* __restrict__ in, Geo g, int C, int ld, int col0, float* __restrict__ out) {
+  const long long total = static_cast<long long>(g.n) * C * g.H * g.W;
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int c = static_cast<int>(i % C);
+  long long pix = i / C;
+  const int x = static_cast<int>(pix % g.W); pix /= g.W;
+  const int y = static_cast<int>(pix % g.H);
+  const int b = static_cast<int>(pix / g.H);
+  out[((static_cast<size_t>(b) * C + c) * g.H + y) * g.W + x] =
+      to_f32(in[static_cast<size_t>(geo_row(g, b, y, x)) * ld + col0 + c]);
+}
+
+}  // namespace dmb
