@@ -178,6 +178,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // in a hung GPU.  try_wait sleeps in hardware, so the bound is ~seconds, far above any
 // legitimate wait.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+#pragma unroll 1
   for (uint32_t spin = 0; spin < (1u << 24); ++spin) {
     if (mbar_try_wait(bar, parity)) return;
   }

@@ -1,0 +1,296 @@
+"""Loader and thin typed wrapper for the C ABI declared in include/dmb200.h."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+from typing import Dict, Optional, Sequence, Tuple
+
+import torch
+
+PRECISION_BF16 = 0
+PRECISION_TF32 = 1
+_PRECISION_NAMES = {"bf16": PRECISION_BF16, "tf32": PRECISION_TF32, "fp32": PRECISION_TF32}
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+class NativeError(RuntimeError):
+    """A non-zero status from libdmb200 (message from dmb_last_error_string)."""
+
+
+def library_path() -> str:
+    return os.environ.get("DMB200_LIBRARY", os.path.join(_HERE, "libdmb200.so"))
+
+
+_lib = None
+_lib_lock = threading.Lock()
+
+# name -> (restype, argtypes); mirrors include/dmb200.h one to one.
+_P = C.c_void_p
+_SIGNATURES = {
+    "dmb_abi_version": (C.c_int, []),
+    "dmb_last_error_string": (C.c_char_p, []),
+    "dmb_ctx_create": (C.c_int, [C.c_int, C.c_int, C.POINTER(_P)]),
+    "dmb_ctx_destroy": (C.c_int, [_P]),
+    "dmb_load_unet_weights": (C.c_int, [_P, C.c_int, C.POINTER(C.c_char_p), C.POINTER(_P), C.POINTER(C.c_int64)]),
+    "dmb_load_vae_dec_weights": (C.c_int, [_P, C.c_int, C.POINTER(C.c_char_p), C.POINTER(_P), C.POINTER(C.c_int64)]),
+    "dmb_unet_forward": (C.c_int, [_P, _P, _P, _P, _P, _P, C.c_int, _P, _P, _P]),
+    "dmb_denoise_cond_step": (C.c_int, [_P, _P, _P, _P, C.c_int, _P, _P, C.c_float, _P, C.c_int, _P, C.c_uint64,
+                                        C.c_uint64, _P, _P, C.c_int, _P]),
+    "dmb_sample_loop": (C.c_int, [_P, _P, _P, C.c_int, _P, _P, C.c_float, _P, C.c_int, C.c_int, C.c_int, _P,
+                                  C.c_uint64, C.c_uint64, _P, _P, C.c_int, _P]),
+    "dmb_vae_decode": (C.c_int, [_P, _P, C.c_int, _P, _P, _P]),
+    "dmb_philox_normal": (C.c_int, [_P, _P, C.c_int, C.c_uint64, C.c_uint64, C.c_int, _P]),
+    "dmb_launch_count": (C.c_int64, [_P]),
+    "dmb_reset_launch_count": (C.c_int, [_P]),
+    "dmb_debug_get_tap": (C.c_int, [_P, C.c_char_p, _P, C.c_int64, C.POINTER(C.c_int64), _P]),
+    "dmb_op_conv3x3": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "dmb_op_linear": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "dmb_op_conv_transpose4x4": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+}
+EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+
+
+def load_library():
+    """dlopen libdmb200.so and set the prototypes.  Raises if the library is absent:
+    the product has no other implementation of the path."""
+    global _lib
+    with _lib_lock:
+        if _lib is None:
+            path = library_path()
+            if not os.path.isfile(path):
+                raise NativeError(
+                    f"libdmb200.so not found at {path}; build it with "
+                    "`python -c 'import __graft_entry__ as g; g.build()'` (there is no CPU fallback)")
+            lib = C.CDLL(path)
+            for name, (res, args) in _SIGNATURES.items():
+                fn = getattr(lib, name)
+                fn.restype = res
+                fn.argtypes = args
+            _lib = lib
+    return _lib
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _check_dev(t: Optional[torch.Tensor], device: torch.device, dtype, name: str):
+    if t is None:
+        return None
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name} must be a torch.Tensor")
+    if t.device != device:
+        raise ValueError(f"{name} lives on {t.device}, context is bound to {device}")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    return t
+
+
+class Context:
+    """One native context = one GPU, one precision mode.  Not thread-safe."""
+
+    def __init__(self, device, precision: str = "bf16"):
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise NativeError("the sampling path runs on a B200 only: no CPU fallback (got device "
+                              f"'{device}')")
+        if device.index is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        if precision not in _PRECISION_NAMES:
+            raise ValueError(f"precision must be one of {sorted(_PRECISION_NAMES)}")
+        self.lib = load_library()
+        self.device = device
+        self.precision = precision
+        self._h = C.c_void_p()
+        self._call("dmb_ctx_create", device.index, _PRECISION_NAMES[precision], C.byref(self._h))
+        self._unet_token = None
+        self._vae_token = None
+
+    # -- plumbing
+    def _call(self, name, *args):
+        rc = getattr(self.lib, name)(*args)
+        if rc != 0:
+            msg = self.lib.dmb_last_error_string().decode("utf-8", "replace")
+            raise NativeError(f"{name} failed ({rc}): {msg}")
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self.lib.dmb_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- weights
+    def _load(self, fn: str, tensors: Dict[str, torch.Tensor]):
+        names = list(tensors)
+        keep = [tensors[k].detach().to(torch.float32).contiguous() for k in names]
+        n = len(names)
+        c_names = (C.c_char_p * n)(*[k.encode() for k in names])
+        c_ptrs = (C.c_void_p * n)(*[t.data_ptr() for t in keep])
+        c_numel = (C.c_int64 * n)(*[t.numel() for t in keep])
+        torch.cuda.synchronize(self.device)
+        self._call(fn, self._h, n, c_names, c_ptrs, c_numel)
+
+    @staticmethod
+    def _token(module: torch.nn.Module, keys: Sequence[str]) -> Tuple:
+        sd = module.state_dict(keep_vars=True)
+        return tuple((k, sd[k].data_ptr(), sd[k]._version) for k in keys)
+
+    def ensure_unet(self, module: torch.nn.Module):
+        """Upload (repack) the U-Net's parameters if they changed since the last call."""
+        sd = module.state_dict(keep_vars=True)
+        keys = list(sd)
+        tok = (id(module),) + self._token(module, keys)
+        if tok != self._unet_token:
+            tensors = {k: v for k, v in sd.items()}
+            # pos_encoding frequencies exactly as the reference computes them (unet_cond.py:156)
+            tensors["__inv_freq"] = 1.0 / (10000 ** (torch.arange(0, 256, 2).float() / 256))
+            self._load("dmb_load_unet_weights", tensors)
+            self._unet_token = tok
+
+    def ensure_vae(self, module: torch.nn.Module):
+        sd = module.state_dict(keep_vars=True)
+        keys = [k for k in sd if k.startswith("dec.")]
+        tok = (id(module),) + self._token(module, keys)
+        if tok != self._vae_token:
+            self._load("dmb_load_vae_dec_weights", {k: sd[k] for k in keys})
+            self._vae_token = tok
+
+    # -- compute
+    def unet_forward(self, x, t, y, vals, mask, want_geom=True):
+        B = x.shape[0]
+        x = _check_dev(x.contiguous(), self.device, torch.float32, "x")
+        t = t.to(torch.long).contiguous()
+        y = y.to(torch.long).contiguous()
+        vals = None if vals is None else vals.to(torch.float32).contiguous()
+        mask = None if mask is None else mask.to(torch.float32).contiguous()
+        eps = torch.empty((B, 4, 28, 28), device=self.device, dtype=torch.float32)
+        geom = torch.empty((B, 12), device=self.device, dtype=torch.float32) if want_geom else None
+        self._call("dmb_unet_forward", self._h, _ptr(x), _ptr(t), _ptr(y), _ptr(vals), _ptr(mask), B, _ptr(eps),
+                   _ptr(geom), self._stream())
+        return eps, geom
+
+    def denoise_cond_step(self, x, t, y, null_label, vals, mask, guidance, coef, noise=None, seed=0,
+                          sample_offset=0, want_eps=False):
+        B = x.shape[0]
+        x = _check_dev(x.contiguous(), self.device, torch.float32, "x")
+        coef = _check_dev(coef, self.device, torch.float32, "coef")
+        noise = _check_dev(noise, self.device, torch.float32, "noise")
+        t = t.to(torch.long).contiguous()
+        y = y.to(torch.long).contiguous()
+        vals = None if vals is None else vals.to(torch.float32).contiguous()
+        mask = None if mask is None else mask.to(torch.float32).contiguous()
+        out = torch.empty_like(x)
+        eps = torch.empty_like(x) if want_eps else None
+        self._call("dmb_denoise_cond_step", self._h, _ptr(x), _ptr(t), _ptr(y), int(null_label), _ptr(vals),
+                   _ptr(mask), float(guidance), _ptr(coef), coef.shape[0], _ptr(noise), int(seed),
+                   int(sample_offset), _ptr(out), _ptr(eps), B, self._stream())
+        return (out, eps) if want_eps else out
+
+    def sample_loop(self, x, y, null_label, vals, mask, guidance, coef, t_start, n_steps, noise=None, seed=0,
+                    sample_offset=0, x_dump=None, eps_dump=None):
+        """In place on x (B,4,28,28)."""
+        B = x.shape[0]
+        _check_dev(x, self.device, torch.float32, "x")
+        coef = _check_dev(coef, self.device, torch.float32, "coef")
+        for nm, tt in (("noise", noise), ("x_dump", x_dump), ("eps_dump", eps_dump)):
+            _check_dev(tt, self.device, torch.float32, nm)
+            if tt is not None and tuple(tt.shape) != (n_steps, B, 4, 28, 28):
+                raise ValueError(f"{nm} must have shape ({n_steps},{B},4,28,28), got {tuple(tt.shape)}")
+        y = y.to(torch.long).contiguous()
+        vals = None if vals is None else vals.to(torch.float32).contiguous()
+        mask = None if mask is None else mask.to(torch.float32).contiguous()
+        self._call("dmb_sample_loop", self._h, _ptr(x), _ptr(y), int(null_label), _ptr(vals), _ptr(mask),
+                   float(guidance), _ptr(coef), coef.shape[0], int(t_start), int(n_steps), _ptr(noise), int(seed),
+                   int(sample_offset), _ptr(x_dump), _ptr(eps_dump), B, self._stream())
+        return x
+
+    def vae_decode(self, z, want_f32=True, want_u8=False):
+        B = z.shape[0]
+        z = _check_dev(z.to(torch.float32).contiguous(), self.device, torch.float32, "z")
+        f32 = torch.empty((B, 3, 224, 224), device=self.device, dtype=torch.float32) if want_f32 else None
+        u8 = torch.empty((B, 3, 224, 224), device=self.device, dtype=torch.uint8) if want_u8 else None
+        self._call("dmb_vae_decode", self._h, _ptr(z), B, _ptr(f32), _ptr(u8), self._stream())
+        return f32, u8
+
+    def philox_normal(self, B, seed, sample_offset, t):
+        out = torch.empty((B, 4, 28, 28), device=self.device, dtype=torch.float32)
+        self._call("dmb_philox_normal", self._h, _ptr(out), B, int(seed), int(sample_offset), int(t), self._stream())
+        return out
+
+    def launch_count(self) -> int:
+        return int(self.lib.dmb_launch_count(self._h))
+
+    def reset_launch_count(self):
+        self._call("dmb_reset_launch_count", self._h)
+
+    def get_tap(self, name: str, capacity_elems: int = 1 << 26):
+        buf = torch.empty((capacity_elems,), device=self.device, dtype=torch.float32)
+        shape = (C.c_int64 * 4)()
+        self._call("dmb_debug_get_tap", self._h, name.encode(), _ptr(buf), capacity_elems, shape, self._stream())
+        n, c, h, w = (int(v) for v in shape)
+        return buf[: n * c * h * w].view(n, c, h, w).clone()
+
+    def op_conv3x3(self, x, w):
+        B, Cin, H, W = x.shape
+        Cout = w.shape[0]
+        x = _check_dev(x.contiguous(), self.device, torch.float32, "x")
+        w = w.to(torch.float32).contiguous()
+        out = torch.empty((B, Cout, H, W), device=self.device, dtype=torch.float32)
+        self._call("dmb_op_conv3x3", self._h, _ptr(x), _ptr(w), B, Cin, Cout, H, W, _ptr(out), self._stream())
+        return out
+
+    def op_linear(self, x, w, bias=None, act=0):
+        rows, K = x.shape
+        N = w.shape[0]
+        x = x.to(torch.float32).contiguous()
+        w = w.to(torch.float32).contiguous()
+        bias = None if bias is None else bias.to(torch.float32).contiguous()
+        out = torch.empty((rows, N), device=self.device, dtype=torch.float32)
+        self._call("dmb_op_linear", self._h, _ptr(x), _ptr(w), _ptr(bias), rows, K, N, int(act), _ptr(out),
+                   self._stream())
+        return out
+
+    def op_conv_transpose4x4(self, x, w, bias=None):
+        B, Cin, H, W = x.shape
+        Cout = w.shape[1]
+        x = _check_dev(x.contiguous(), self.device, torch.float32, "x")
+        w = w.to(torch.float32).contiguous()
+        bias = None if bias is None else bias.to(torch.float32).contiguous()
+        out = torch.empty((B, Cout, 2 * H, 2 * W), device=self.device, dtype=torch.float32)
+        self._call("dmb_op_conv_transpose4x4", self._h, _ptr(x), _ptr(w), _ptr(bias), B, Cin, Cout, H, W,
+                   _ptr(out), self._stream())
+        return out
+
+
+_contexts: Dict[Tuple[int, str], Context] = {}
+
+
+def default_precision() -> str:
+    return os.environ.get("DMB200_PRECISION", "bf16")
+
+
+def context_for(device, precision: Optional[str] = None) -> Context:
+    """The process-wide context of a device (created on first use)."""
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise NativeError(f"the sampling path runs on a B200 only: no CPU fallback (got device '{device}')")
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    precision = precision or default_precision()
+    key = (idx, precision)
+    ctx = _contexts.get(key)
+    if ctx is None:
+        ctx = Context(torch.device("cuda", idx), precision)
+        _contexts[key] = ctx
+    return ctx

@@ -1,0 +1,75 @@
+"""VAE -- B200-native drop-in for ``models/vae.py`` (vae.py:5-75).
+
+Only ``decode`` is on the sampling path (vae.py:64-69); it runs in libdmb200 (tcgen05
+convolutions / transposed convolutions, GroupNorm(8)+GELU, sigmoid).  The encoder's
+parameters are held so that reference checkpoints load, but ``encode`` is not implemented
+(SURVEY.md 8f row N3)."""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from ._holders import slots
+
+
+class VAE(nn.Module):
+    def __init__(self, in_channels=3, z_channels=4, base_channels=64, scale_factor=0.18215):
+        super().__init__()
+        self.in_channels = in_channels
+        self.z_channels = z_channels
+        self.base_channels = base_channels
+        self.scale_factor = scale_factor
+        self.precision = None
+        b = base_channels
+        self.enc = slots({
+            0: nn.Conv2d(in_channels, b, 3, stride=1, padding=1), 1: nn.GroupNorm(8, b),
+            3: nn.Conv2d(b, b, 4, stride=2, padding=1), 4: nn.GroupNorm(8, b),
+            6: nn.Conv2d(b, b * 2, 3, stride=1, padding=1), 7: nn.GroupNorm(8, b * 2),
+            9: nn.Conv2d(b * 2, b * 2, 4, stride=2, padding=1), 10: nn.GroupNorm(8, b * 2),
+            12: nn.Conv2d(b * 2, b * 4, 3, stride=1, padding=1), 13: nn.GroupNorm(8, b * 4),
+            15: nn.Conv2d(b * 4, b * 4, 4, stride=2, padding=1), 16: nn.GroupNorm(8, b * 4),
+        })
+        self.to_mu = nn.Conv2d(b * 4, z_channels, 1)
+        self.to_logvar = nn.Conv2d(b * 4, z_channels, 1)
+        self.dec = slots({
+            0: nn.Conv2d(z_channels, b * 4, 3, padding=1), 1: nn.GroupNorm(8, b * 4),
+            3: nn.ConvTranspose2d(b * 4, b * 4, 4, stride=2, padding=1), 4: nn.GroupNorm(8, b * 4),
+            6: nn.Conv2d(b * 4, b * 2, 3, padding=1), 7: nn.GroupNorm(8, b * 2),
+            9: nn.ConvTranspose2d(b * 2, b * 2, 4, stride=2, padding=1), 10: nn.GroupNorm(8, b * 2),
+            12: nn.Conv2d(b * 2, b, 3, padding=1), 13: nn.GroupNorm(8, b),
+            15: nn.ConvTranspose2d(b, b, 4, stride=2, padding=1), 16: nn.GroupNorm(8, b),
+            18: nn.Conv2d(b, in_channels, 3, padding=1),
+        })
+
+    def _ctx(self, z: torch.Tensor):
+        from dmb200 import context_for
+        if (self.in_channels, self.z_channels, self.base_channels) != (3, 4, 64) or abs(self.scale_factor - 0.18215) > 1e-12:
+            raise NotImplementedError("libdmb200 implements the default VAE (3, 4, 64, scale 0.18215)")
+        if z.dim() != 4 or tuple(z.shape[1:]) != (4, 28, 28):
+            raise ValueError(f"latent must be (B,4,28,28), got {tuple(z.shape)}")
+        dev = self.dec["18"].weight.device
+        if z.device != dev:
+            raise ValueError(f"input on {z.device} but parameters on {dev}")
+        ctx = context_for(dev, self.precision)
+        ctx.ensure_vae(self)
+        return ctx
+
+    def decode(self, z):
+        """z / scale -> decoder -> sigmoid; (B,3,224,224) fp32 in [0,1]  (vae.py:64-69)."""
+        with torch.no_grad():
+            img, _ = self._ctx(z).vae_decode(z, want_f32=True, want_u8=False)
+        return img
+
+    def decode_u8(self, z):
+        """decode + the x*255 / clamp / truncating uint8 cast of Diffuser.reverse_to_img
+        (diff.py:58-61), done in the decoder's epilogue."""
+        with torch.no_grad():
+            _, u8 = self._ctx(z).vae_decode(z, want_f32=False, want_u8=True)
+        return u8
+
+    def encode(self, x):
+        raise NotImplementedError("VAE.encode is not on the sampling path (SURVEY.md 8f N3); "
+                                  "Diffuser.sample_latent_cond derives the latent shape without it")
+
+    def forward(self, x):
+        raise NotImplementedError("VAE.forward (training) is outside the sampling path")

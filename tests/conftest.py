@@ -1,0 +1,45 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PRODUCT = os.path.join(ROOT, "diffusion-model_b200")
+for p in (ROOT, PRODUCT):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a B200 (run with -m gpu on the GPU box)")
+
+
+def pytest_collection_modifyitems(config, items):
+    import torch
+    if torch.cuda.is_available():
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)
+
+
+@pytest.fixture(scope="session")
+def golden():
+    import numpy as np
+    return np.load(os.path.join(GOLDEN, "golden.npz"))
+
+
+@pytest.fixture(scope="session")
+def seeded_models():
+    """Random-init product modules under the benchmark recipe:
+    torch.manual_seed(0); UnetCondWithGeomHead(); VAE()."""
+    import torch
+    from models.unet_cond_geom import UnetCondWithGeomHead
+    from models.vae import VAE
+    torch.manual_seed(0)
+    unet = UnetCondWithGeomHead().eval()
+    vae = VAE().eval()
+    return unet, vae
