@@ -1,6 +1,8 @@
 // extern "C" boundary: argument validation, exception -> status code translation.
 #include "../../include/dmb200.h"
 
+#include <cstring>
+
 #include "engine.cuh"
 
 struct dmb_ctx {
@@ -148,6 +150,22 @@ int dmb_reset_launch_count(dmb_ctx* ctx) {
   return guarded([&] {
     DMB_REQUIRE(ctx, "ctx is NULL");
     ctx->eng->reset_launches();
+  });
+}
+
+int dmb_set_kernel_timing(dmb_ctx* ctx, int on) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx, "ctx is NULL");
+    ctx->eng->set_timing(on != 0);
+  });
+}
+
+int dmb_get_kernel_timing(dmb_ctx* ctx, char* buf, int64_t capacity, int64_t* needed) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && needed, "ctx and needed are required");
+    const std::string js = ctx->eng->timing_json();
+    *needed = static_cast<int64_t>(js.size()) + 1;
+    if (buf && capacity >= *needed) memcpy(buf, js.c_str(), js.size() + 1);
   });
 }
 

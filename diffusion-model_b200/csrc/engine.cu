@@ -163,10 +163,25 @@ struct Act {  // an activation in padded pixel-matrix layout
 
 using Op = std::function<void(cudaStream_t)>;
 
+// Launch list with a label and the algorithmic work of every entry (for the timing mode).
+struct OpList {
+  std::vector<Op> fns;
+  std::vector<std::string> labels;
+  std::vector<double> flops, bytes;
+  std::string next_label = "op";
+  double next_flops = 0, next_bytes = 0;
+  void tag(const std::string& label, double fl = 0, double by = 0) { next_label = label; next_flops = fl; next_bytes = by; }
+  void push_back(Op f) {
+    fns.push_back(std::move(f)); labels.push_back(next_label); flops.push_back(next_flops); bytes.push_back(next_bytes);
+    next_label = "op"; next_flops = 0; next_bytes = 0;
+  }
+  size_t size() const { return fns.size(); }
+};
+
 template <typename T>
 struct Plan {
   Pool pool;
-  std::vector<Op> ops;
+  OpList ops;
   std::map<std::string, Act<T>> taps;
   int B = 0;
   bool doubled = false;
@@ -227,6 +242,12 @@ class Engine : public IEngine {
                  cudaStream_t s) override;
   void op_convT4x4(const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int H, int W,
                    float* out, cudaStream_t s) override;
+  void set_timing(bool on) override {
+    for (auto& t : timed_) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
+    timed_.clear();
+    timing_ = on;
+  }
+  std::string timing_json() override;
   long long launches() const override { return launches_; }
   void reset_launches() override { launches_ = 0; }
 
@@ -260,9 +281,29 @@ class Engine : public IEngine {
   Plan<T>& get_plan(int B, bool doubled);
   void bind_inputs(Plan<T>& p, const float* x, const long long* t, const long long* y, const float* vals,
                    const float* mask, int null_label, cudaStream_t s);
-  void run_ops(Plan<T>& p, cudaStream_t s) {
-    for (auto& op : p.ops) op(s);
+  void run_list(OpList& l, cudaStream_t s) {
+    for (size_t i = 0; i < l.fns.size(); ++i) {
+      if (timing_) {
+        Timed t{l.labels[i], l.flops[i], l.bytes[i], nullptr, nullptr};
+        DMB_CUDA(cudaEventCreate(&t.e0));
+        DMB_CUDA(cudaEventCreate(&t.e1));
+        DMB_CUDA(cudaEventRecord(t.e0, s));
+        l.fns[i](s);
+        DMB_CUDA(cudaEventRecord(t.e1, s));
+        timed_.push_back(t);
+      } else {
+        l.fns[i](s);
+      }
+    }
   }
+  void run_ops(Plan<T>& p, cudaStream_t s) { run_list(p.ops, s); }
+  struct Timed {
+    std::string label;
+    double flops, bytes;
+    cudaEvent_t e0, e1;
+  };
+  bool timing_ = false;
+  std::vector<Timed> timed_;
 
   int device_ = 0;
   int num_sms_ = 148;
@@ -281,7 +322,7 @@ class Engine : public IEngine {
 
   struct VaePlan {
     Pool pool;
-    std::vector<Op> ops;
+    OpList ops;
     int B = 0;
     float* z = nullptr;
     float* img_f32 = nullptr;
@@ -589,6 +630,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     const EmbWeights ew = embw_;
     Plan<T>* pp = &P;
     const int doubled = P.doubled ? 1 : 0;
+    ops.tag("emb");
     ops.push_back([this, ew, pp, n, B, doubled](cudaStream_t s) {
       emb_kernel<<<n, 256, 0, s>>>(ew, pp->t_vec, pp->y, pp->dyn->flags, pp->vals, pp->mask, B, doubled, pp->emb,
                                    pp->embproj);
@@ -605,6 +647,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     const float* embproj = P.embproj;
     const int total_vec = raw.g.H * raw.g.W * raw.C / 8;
     const int splits = std::max(1, std::min(8, total_vec / 2048));
+    ops.tag("gn1_apply", 0, static_cast<double>(raw.g.n) * total_vec * 8 * sizeof(T) * (residual ? 3 : 2));
     ops.push_back([this, raw, out, gamma, beta, mode, res, embproj, emb_off, splits](cudaStream_t s) {
       gn1_apply_kernel<T><<<dim3(splits, raw.g.n), 256, 0, s>>>(raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc,
                                                                 gamma, beta, mode, res, embproj, emb_off, raw.g,
@@ -617,6 +660,8 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   auto conv = [&](const Act<T>& in, const std::string& wname) {
     const GemmW<T>& w = gw_.at(wname);
     Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, true, w.rows_per_tap / w.bn);
+    ops.tag("conv3x3 " + std::to_string(w.K) + "->" + std::to_string(w.N) + " @" + std::to_string(in.g.H),
+            2.0 * in.g.n * in.g.H * in.g.W * 9.0 * w.K * w.N);
     ops.push_back(op_conv(in, w, out));
     return out;
   };
@@ -633,6 +678,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       Act<T> out = new_act(pool, nn, H, W, C, false);
       const float* wv = f(name + ".weight");
       const float* bv = f(name + ".bias");
+      ops.tag("layernorm", 0, 2.0 * in.g.n * in.g.H * in.g.W * C * sizeof(T));
       ops.push_back([this, in, out, wv, bv, C](cudaStream_t s) {
         const long long ntok = static_cast<long long>(in.g.n) * in.g.H * in.g.W;
         const int grid = cdiv(ntok, 8);
@@ -646,8 +692,14 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     };
     Act<T> xl = ln(x, p + ".ln");
     Act<T> qkv = new_act(pool, nn, H, W, 3 * C, false);
+    const double tok = static_cast<double>(nn) * H * W;
+    auto lin_tag = [&](int K, int N) {
+      ops.tag("linear " + std::to_string(K) + "->" + std::to_string(N) + " @" + std::to_string(H), 2.0 * tok * K * N);
+    };
+    lin_tag(C, 3 * C);
     ops.push_back(op_lin(xl, gw_.at(p + ".qkv"), qkv, 0, nullptr));
     Act<T> av = new_act(pool, nn, H, W, C, false);
+    ops.tag("attention L=" + std::to_string(H * W) + " d=" + std::to_string(C / 4), 4.0 * nn * H * W * H * W * C);
     ops.push_back([this, qkv, av, C](cudaStream_t s) {
       const int L = qkv.g.H * qkv.g.W, D = C / 4;
       const int threads = std::min(128, (L + 31) / 32 * 32);
@@ -660,16 +712,20 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       count();
     });
     Act<T> o = new_act(pool, nn, H, W, C, false);
+    lin_tag(C, C);
     ops.push_back(op_lin(av, gw_.at(p + ".proj"), o, 0, &xl));
     Act<T> h = ln(o, p + ".ff_self.0");
     Act<T> f1 = new_act(pool, nn, H, W, C, false);
+    lin_tag(C, C);
     ops.push_back(op_lin(h, gw_.at(p + ".ff1"), f1, 1, nullptr));
     Act<T> out = new_act(pool, nn, H, W, C, false);
+    lin_tag(C, C);
     ops.push_back(op_lin(f1, gw_.at(p + ".ff2"), out, 0, &o));
     return out;
   };
   auto down = [&](const Act<T>& x, const std::string& p, int emb_off) {
     Act<T> pooled = new_act(pool, x.g.n, x.g.H / 2, x.g.W / 2, x.C, false);
+    ops.tag("maxpool", 0, 1.25 * pooled.g.n * x.g.H * x.g.W * x.C * sizeof(T));
     ops.push_back([this, x, pooled](cudaStream_t s) {
       const long long total = static_cast<long long>(pooled.g.n) * pooled.g.H * pooled.g.W * (x.C / 8);
       maxpool2_kernel<T><<<cdiv(total, 256), 256, 0, s>>>(x.p, x.g, pooled.g, x.C, pooled.p);
@@ -681,6 +737,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   };
   auto up = [&](const Act<T>& x, const Act<T>& skip, const std::string& p, int emb_off) {
     Act<T> cat = new_act(pool, skip.g.n, skip.g.H, skip.g.W, skip.C + x.C, false);
+    ops.tag("upcat", 0, 2.0 * cat.g.n * cat.g.H * cat.g.W * cat.C * sizeof(T));
     ops.push_back([this, x, skip, cat](cudaStream_t s) {
       const long long total = static_cast<long long>(cat.g.n) * cat.g.H * cat.g.W * (cat.C / 8);
       upcat_kernel<T><<<cdiv(total, 256), 256, 0, s>>>(skip.p, skip.C, x.p, x.g, x.C, cat.g, cat.p);
@@ -696,6 +753,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   {
     const float* w0 = f("inc.double_conv.0.weight");
     Plan<T>* pp = &P;
+    ops.tag("conv_in 4->64 @28", 2.0 * n * kLatH * kLatW * 36.0 * 64);
     ops.push_back([this, r0, w0, pp, B](cudaStream_t s) {
       conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), r0.g.n, 1), 128, 0, s>>>(pp->x_state, B, w0, nullptr, 1.0f,
                                                                                   r0.g, 64, r0.p, r0.stats);
@@ -809,9 +867,15 @@ void Engine<T>::cfg_step(const float* x_in, const long long* t, const long long*
   sp.w_out = f("out.weight"); sp.b_out = f("out.bias");
   DMB_CUDA(cudaMemcpyAsync(&p.dyn->step, &sp, sizeof(sp), cudaMemcpyHostToDevice, s));
   run_ops(p, s);
-  cfg_step_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, s>>>(p.feat.p, p.feat.g, B, &p.dyn->step);
-  DMB_CHECK_LAUNCH();
-  count();
+  OpList tail;
+  tail.tag("cfg_step (out conv + CFG + DDPM)", 0, static_cast<double>(B) * kLatH * kLatW * (2 * 64 * sizeof(T) + 4 * 4 * 3));
+  Plan<T>* pp = &p;
+  tail.push_back([this, pp, B](cudaStream_t cs) {
+    cfg_step_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, cs>>>(pp->feat.p, pp->feat.g, B, &pp->dyn->step);
+    DMB_CHECK_LAUNCH();
+    count();
+  });
+  run_list(tail, s);
 }
 
 // The T-step loop (diff.py:332-344) as CUDA-graph replays: one graph holds `chunk` whole
@@ -909,6 +973,7 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
     double2* partial = pool.alloc_n<double2>(static_cast<size_t>(raw.g.n) * chunks * 8);
     const float* gamma = f(name + ".weight");
     const float* beta = f(name + ".bias");
+    ops.tag("vae gn8+gelu", 0, 3.0 * raw.g.n * total_vec * 8 * sizeof(T));
     ops.push_back([this, raw, out, chunks, partial, gamma, beta](cudaStream_t s) {
       gn8_stats_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, raw.g, raw.C, partial);
       DMB_CHECK_LAUNCH();
@@ -922,12 +987,16 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
   auto conv = [&](const Act<T>& in, const std::string& wname) {
     const GemmW<T>& w = gw_.at(wname);
     Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, false);
+    ops.tag("vae conv3x3 " + std::to_string(w.K) + "->" + std::to_string(w.N) + " @" + std::to_string(in.g.H),
+            2.0 * in.g.n * in.g.H * in.g.W * 9.0 * w.K * w.N);
     ops.push_back(op_conv(in, w, out));
     return out;
   };
   auto convT = [&](const Act<T>& in, const std::string& wname) {
     const GemmW<T> w = gw_.at(wname);
     Act<T> out = new_act(pool, in.g.n, in.g.H * 2, in.g.W * 2, w.N, false);
+    ops.tag("vae convT4x4 " + std::to_string(w.K) + "->" + std::to_string(w.N) + " @" + std::to_string(in.g.H),
+            2.0 * in.g.n * in.g.H * in.g.W * 16.0 * w.K * w.N);
     ops.push_back([this, in, w, out](cudaStream_t s) {
       for (int a = 0; a < 2; ++a)
         for (int b = 0; b < 2; ++b) {
@@ -952,6 +1021,7 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
   {
     const float* w0 = f("vae.dec.0.weight");
     const float* b0 = f("vae.dec.0.bias");
+    ops.tag("vae conv_in 4->256 @28", 2.0 * n * kLatH * kLatW * 36.0 * 256);
     ops.push_back([this, r0, w0, b0, pp, n](cudaStream_t s) {
       conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), n, 4), 128, 0, s>>>(pp->z, n, w0, b0, 0.18215f, r0.g, 256,
                                                                              r0.p, nullptr);
@@ -967,6 +1037,7 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
   a = gn8(convT(a, "vae.dec.15"), "vae.dec.16");
   {
     const GemmW<T> w = gw_.at("vae.dec.18");
+    ops.tag("vae conv3x3 64->3 @224 +sigmoid", 2.0 * n * 224.0 * 224 * 9 * 64 * 3);
     ops.push_back([this, a, w, pp](cudaStream_t s) {
       int shifts[9];
       for (int ky = 0; ky < 3; ++ky)
@@ -1001,7 +1072,7 @@ void Engine<T>::vae_decode(const float* z, int B, float* img_f32, uint8_t* img_u
     p.z = const_cast<float*>(z) + b0 * lat;
     p.img_f32 = img_f32 ? img_f32 + b0 * img : nullptr;
     p.img_u8 = img_u8 ? img_u8 + b0 * img : nullptr;
-    for (auto& op : p.ops) op(s);
+    run_list(p.ops, s);
   }
 }
 
@@ -1158,6 +1229,31 @@ void Engine<T>::op_convT4x4(const float* x, const float* w, const float* bias, i
   pm_to_nchw_kernel<T><<<cdiv(static_cast<long long>(B) * Cout * 4 * H * W, 256), 256, 0, s>>>(o.p, o.g, Cout, Cout, 0, out);
   DMB_CHECK_LAUNCH();
   DMB_CUDA(cudaStreamSynchronize(s));
+}
+
+template <typename T>
+std::string Engine<T>::timing_json() {
+  DMB_CUDA(cudaDeviceSynchronize());
+  struct Agg { int count = 0; double ms = 0, flops = 0, bytes = 0; };
+  std::map<std::string, Agg> agg;
+  std::vector<std::string> order;
+  for (auto& t : timed_) {
+    float ms = 0.f;
+    DMB_CUDA(cudaEventElapsedTime(&ms, t.e0, t.e1));
+    if (!agg.count(t.label)) order.push_back(t.label);
+    Agg& a = agg[t.label];
+    a.count += 1; a.ms += ms; a.flops += t.flops; a.bytes += t.bytes;
+  }
+  std::string out = "[";
+  for (size_t i = 0; i < order.size(); ++i) {
+    const Agg& a = agg[order[i]];
+    char buf[512];
+    snprintf(buf, sizeof(buf), "%s{\"label\": \"%s\", \"count\": %d, \"ms\": %.6f, \"flops\": %.6e, \"bytes\": %.6e}",
+             i ? ", " : "", order[i].c_str(), a.count, a.ms, a.flops, a.bytes);
+    out += buf;
+  }
+  out += "]";
+  return out;
 }
 
 template class Engine<__nv_bfloat16>;

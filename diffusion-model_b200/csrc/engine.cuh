@@ -52,6 +52,8 @@ class IEngine {
                          float* out, cudaStream_t s) = 0;
   virtual void op_convT4x4(const float* x, const float* w, const float* bias, int B, int Cin, int Cout, int H,
                            int W, float* out, cudaStream_t s) = 0;
+  virtual void set_timing(bool on) = 0;
+  virtual std::string timing_json() = 0;
   virtual long long launches() const = 0;
   virtual void reset_launches() = 0;
 };

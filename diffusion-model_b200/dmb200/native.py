@@ -44,6 +44,8 @@ _SIGNATURES = {
     "dmb_philox_normal": (C.c_int, [_P, _P, C.c_int, C.c_uint64, C.c_uint64, C.c_int, _P]),
     "dmb_launch_count": (C.c_int64, [_P]),
     "dmb_reset_launch_count": (C.c_int, [_P]),
+    "dmb_set_kernel_timing": (C.c_int, [_P, C.c_int]),
+    "dmb_get_kernel_timing": (C.c_int, [_P, C.c_char_p, C.c_int64, C.POINTER(C.c_int64)]),
     "dmb_debug_get_tap": (C.c_int, [_P, C.c_char_p, _P, C.c_int64, C.POINTER(C.c_int64), _P]),
     "dmb_op_conv3x3": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "dmb_op_linear": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
@@ -234,6 +236,18 @@ class Context:
 
     def reset_launch_count(self):
         self._call("dmb_reset_launch_count", self._h)
+
+    def set_kernel_timing(self, on: bool):
+        self._call("dmb_set_kernel_timing", self._h, 1 if on else 0)
+
+    def kernel_timing(self):
+        """[{label, count, ms, flops, bytes}] of the eager calls made since set_kernel_timing(True)."""
+        import json
+        need = C.c_int64(0)
+        self._call("dmb_get_kernel_timing", self._h, None, 0, C.byref(need))
+        buf = C.create_string_buffer(need.value)
+        self._call("dmb_get_kernel_timing", self._h, buf, need.value, C.byref(need))
+        return json.loads(buf.value.decode())
 
     def get_tap(self, name: str, capacity_elems: int = 1 << 26):
         buf = torch.empty((capacity_elems,), device=self.device, dtype=torch.float32)

@@ -98,6 +98,13 @@ int dmb_philox_normal(dmb_ctx* ctx, float* out, int B, uint64_t seed, uint64_t s
 int64_t dmb_launch_count(dmb_ctx* ctx);
 int dmb_reset_launch_count(dmb_ctx* ctx);
 
+/* Per-kernel device timing (CUDA events around every launch of the EAGER entry points:
+ * dmb_unet_forward, dmb_denoise_cond_step, dmb_vae_decode).  dmb_get_kernel_timing synchronises
+ * and writes a JSON array [{label,count,ms,flops,bytes}] (algorithmic FLOPs / bytes per label)
+ * into buf; *needed receives the size including the terminator. */
+int dmb_set_kernel_timing(dmb_ctx* ctx, int on);
+int dmb_get_kernel_timing(dmb_ctx* ctx, char* buf, int64_t capacity, int64_t* needed);
+
 /* ---- test / debug entry points (unit-level parity of the kernels through the same ABI) ---- */
 
 /* Named intermediate activation of the most recent forward / step as (n,C,H,W) fp32 [dev].

@@ -1,0 +1,171 @@
+"""Host-side logic of the drop-in modules (no GPU): schedule table, condition building,
+CSV front-end, error behaviour, and that nothing runs on the CPU."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import load_reference
+from oracle import ref_torch as R
+from oracle import synth
+
+
+def test_schedule_is_bit_identical(golden):
+    from diff import Diffuser
+    d = Diffuser(num_timesteps=1000)
+    np.testing.assert_array_equal(d.betas.numpy(), golden["F_betas"])
+    np.testing.assert_array_equal(d.alpha_bars.numpy(), golden["F_alpha_bars"])
+    coef = d.step_coefficients()
+    assert coef.shape == (1000, 3) and coef.dtype == torch.float32
+    # same expressions as diff.py:141-144, 160-161
+    t = torch.tensor([1, 2, 500, 1000])
+    a, ab = d.alphas[t - 1], d.alpha_bars[t - 1]
+    abp = d.alpha_bars[torch.clamp(t - 2, min=0)]
+    assert torch.equal(coef[t - 1, 0], (1 - a) / torch.sqrt(1 - ab))
+    assert torch.equal(coef[t - 1, 1], torch.sqrt(a))
+    assert torch.equal(coef[t - 1, 2], torch.sqrt((1 - a) * (1 - abp) / (1 - ab)))
+
+
+def test_step_update_formula_matches_oracle():
+    """(x - c1 eps)/sqrt(a) + sigma noise with the table == the reference expression."""
+    from diff import Diffuser
+    d = Diffuser(num_timesteps=1000)
+    _, alphas, abars = R.schedule(1000)
+    g = torch.Generator().manual_seed(0)
+    x, eps, nz = (torch.randn((3, 4, 28, 28), generator=g) for _ in range(3))
+    for tt in (1000, 17, 1):
+        t = torch.full((3,), tt, dtype=torch.long)
+        ref = R.ddpm_update(x, eps, t, nz, alphas, abars)
+        c = d.step_coefficients()[tt - 1]
+        got = (x - c[0] * eps) / c[1] + (0 if tt == 1 else 1) * nz * c[2]
+        assert torch.allclose(got, ref, rtol=0, atol=1e-6 * float(ref.abs().max()))
+
+
+@pytest.mark.parametrize("cls", [1, 2, 3])
+def test_csv_sampler_condition(tmp_path, golden, cls):
+    from diff import Diffuser
+    from entityCsvSampler import EntityCsvSampler
+    path = os.path.join(tmp_path, "rows.csv")
+    np.savetxt(path, golden["E_rows"], delimiter=",", fmt="%.6f")
+    s = EntityCsvSampler(Diffuser(device="cpu"), None, None, class_id=cls, device=torch.device("cpu"))
+    vals, mask = s.load_cond(path)
+    np.testing.assert_array_equal(vals.numpy(), golden[f"E_vals_{cls}"])
+    np.testing.assert_array_equal(mask.numpy(), golden[f"E_mask_{cls}"])
+    v2, m2 = s.load_cond(path, count=3, start=5)
+    np.testing.assert_array_equal(v2.numpy(), golden[f"E_vals_{cls}"][5:8])
+    with pytest.raises(ValueError):
+        s.load_cond(path, count=1, start=99)  # empty selection
+    s.set_class_id(7)
+    with pytest.raises(ValueError):
+        s.load_cond(path)
+
+
+def test_infer_base_wh(tmp_path):
+    import pandas as pd
+    from diff import Diffuser
+    from entityCsvSampler import EntityCsvSampler
+    rows = synth.synth_rows(8, seed=1)
+    rows[0, 1] = 399.2
+    rows[1, 2] = 280.9
+    rows[:, [2, 4]] = np.minimum(rows[:, [2, 4]], 280.9)
+    s = EntityCsvSampler(Diffuser(), None, None, class_id=1, base_wh=None, device=torch.device("cpu"))
+    assert s._infer_base_wh(pd.DataFrame(rows), 1) == (400.0, 280.0)
+
+
+def _ref_condition(kwargs, class_counts):
+    """What the reference's sample_latent_cond builds, captured at its first denoise call."""
+    captured = {}
+
+    class Stop(Exception):
+        pass
+
+    with load_reference.reference_modules() as ref:
+        d = ref.diff.Diffuser(num_timesteps=2, device="cpu")
+
+        def fake(**kw):
+            captured.update(kw)
+            raise Stop()
+
+        d.denoise_cond = fake
+        try:
+            d.sample_latent_cond(None, class_counts, z_shape=(4, 28, 28), progress=False, **kwargs)
+        except Stop:
+            pass
+    return captured["y"], captured["cond_vals"], captured["cond_mask"]
+
+
+@pytest.mark.skipif(not load_reference.available(), reason="reference tree not present")
+@pytest.mark.parametrize("case", range(6))
+def test_condition_building_matches_reference(case):
+    from diff import _build_condition, _normalise_counts, KEY_ORDER, CLASS_KEYS
+    cc = [{1: 2, 3: 1}, (2, 3), [(1, 1), (2, 1), (3, 1)], {3: 2}, (1, 2), [(2, 2)]][case]
+    t = torch.arange(36, dtype=torch.float32).reshape(3, 12) / 36
+    t[0, 3] = 0.0
+    kw = [
+        dict(cond={1: {"x1": .1, "y2": .9, "bogus": 1}, 3: {"ar": .2}}, cond_mask={1: {"x1": 0.0, "x2": 1.0}}),
+        dict(cond=t),
+        dict(cond=t, cond_mask=(t > 0.5).float()),
+        dict(cond=[{"ax": .5}, {"theta1": .25, "theta2": .75}], cond_mask=[{"ax": 0.0}, {"ay": 1.0}]),
+        dict(),
+        dict(cond_mask=torch.ones(2, 12)),
+    ][case]
+    y_ref, v_ref, m_ref = _ref_condition(kw, cc)
+    items = _normalise_counts(cc)
+    y_list = [c for c, n in items for _ in range(n)]
+    v, m = _build_condition(kw.get("cond"), kw.get("cond_mask"), y_list, list(KEY_ORDER), CLASS_KEYS, "cpu")
+    assert y_list == y_ref.tolist()
+    assert torch.equal(v, v_ref) and torch.equal(m, m_ref)
+
+
+def test_argument_errors_match_reference_types():
+    from diff import Diffuser, _build_condition, _normalise_counts, KEY_ORDER, CLASS_KEYS
+    with pytest.raises(ValueError):
+        _normalise_counts("nope")
+    with pytest.raises(ValueError):
+        _normalise_counts({1: 0})
+    with pytest.raises(ValueError):
+        _build_condition(torch.zeros(2, 11), None, [1, 1], list(KEY_ORDER), CLASS_KEYS, "cpu")
+    with pytest.raises(ValueError):
+        _build_condition(torch.zeros(2, 12), torch.zeros(2, 3), [1, 1], list(KEY_ORDER), CLASS_KEYS, "cpu")
+    with pytest.raises(ValueError):
+        _build_condition([{}], None, [1, 1], list(KEY_ORDER), CLASS_KEYS, "cpu")
+    d = Diffuser(num_timesteps=10)
+    x = torch.zeros(1, 4, 28, 28)
+    with pytest.raises(AssertionError):
+        d.denoise_cond(None, x, torch.tensor([11]), y=torch.tensor([1]), guidance_scale=3.0)
+    with pytest.raises(UnboundLocalError):
+        d.denoise_cond(None, x, torch.tensor([3]), y=torch.tensor([1]), guidance_scale=0.0)
+    with pytest.raises(ValueError):
+        d.sample_latent_cond(None, (1, 1), z_shape=None, vae=None)
+
+
+def test_no_cpu_fallback(seeded_models):
+    """The product fails loudly instead of computing on the CPU."""
+    from dmb200 import NativeError
+    unet, vae = seeded_models
+    x = torch.zeros(1, 4, 28, 28)
+    with pytest.raises(NativeError):
+        unet(x, torch.tensor([1]), torch.tensor([1]))
+    with pytest.raises(NativeError):
+        vae.decode(x)
+    with pytest.raises(RuntimeError):
+        unet.inc(x)  # parameter holders do not compute
+
+
+def test_product_does_not_import_oracle():
+    import re
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "diffusion-model_b200")
+    for dp, _, fns in os.walk(root):
+        for fn in fns:
+            if fn.endswith(".py"):
+                src = open(os.path.join(dp, fn)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", src, re.M), fn
+
+
+def test_reverse_to_img_truncates():
+    from diff import Diffuser
+    x = torch.tensor([0.0, 0.999 / 255, 1.0 / 255, 0.5, 1.0, 1.5, -0.2]).reshape(1, 1, 7).repeat(3, 1, 1)
+    img = Diffuser().reverse_to_img(x)
+    assert img.mode == "RGB" and img.size == (7, 1)
+    assert list(np.array(img)[0, :, 0]) == [0, 0, 1, 127, 255, 255, 0]
