@@ -159,12 +159,15 @@ class Diffuser:
         seed: Optional[int] = None,
         sample_offset: int = 0,
         latent_dump: bool = False,
+        return_u8: bool = False,
     ):
         """Class + numeric-condition CFG sampling (diff.py:174-369).
 
         Returns what the reference returns: the latent if ``vae is None``, a (B,3,224,224)
         tensor if ``to_pil=False``, else a list of PIL images.  With ``latent_dump=True`` a
         second value, the (T,B,4,28,28) tensor of x_t before each step, is returned as well.
+        ``return_u8=True`` returns the decoded batch as one (B,3,224,224) uint8 device tensor
+        (the x*255 / clamp / truncate of reverse_to_img done in the decoder's epilogue).
         """
         device = self.device
         items = _normalise_counts(class_counts)
@@ -210,6 +213,8 @@ class Diffuser:
         if vae is None:
             return ret(x)
         vae.eval()
+        if return_u8:
+            return ret(vae.decode_u8(x))
         if to_pil and hasattr(vae, "decode_u8"):
             u8 = vae.decode_u8(x).cpu()  # one device->host copy for the whole batch
             return ret([_chw_u8_to_pil(u8[i]) for i in range(B)])
