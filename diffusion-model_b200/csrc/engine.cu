@@ -2,6 +2,9 @@
 //   T = __nv_bfloat16 : bf16 activations / weights, tcgen05 kind::f16, fp32 accumulate
 //   T = float         : fp32 activations / weights, tcgen05 kind::tf32, fp32 accumulate
 #include "engine.cuh"
+#include "attention_tc.cuh"
+
+#include <type_traits>
 
 #include <algorithm>
 #include <cmath>
@@ -219,6 +222,13 @@ class Engine : public IEngine {
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+    if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+      DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+      DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+      DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+    }
+    const char* env = getenv("DMB200_CUDA_CORE_ATTENTION");
+    use_tc_attention_ = !(env && env[0] == '1');
   }
   ~Engine() override {}
 
@@ -309,6 +319,7 @@ class Engine : public IEngine {
   int num_sms_ = 148;
   long long launches_ = 0;
   bool counting_ = true;
+  bool use_tc_attention_ = true;
 
   Pool wpool_unet_, wpool_vae_;
   std::map<std::string, std::pair<const float*, int64_t>> blob_;  // name -> fp32 device copy
@@ -702,6 +713,18 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.tag("attention L=" + std::to_string(H * W) + " d=" + std::to_string(C / 4), 4.0 * nn * H * W * H * W * C);
     ops.push_back([this, qkv, av, C](cudaStream_t s) {
       const int L = qkv.g.H * qkv.g.W, D = C / 4;
+      if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+        if (use_tc_attention_) {
+          const dim3 grid(cdiv(L, kAttnBlock), 4, qkv.g.n);
+          const size_t smem = attention_tc_smem_bytes(L, D);
+          if (D == 16) attention_tc_kernel<16><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p);
+          else if (D == 32) attention_tc_kernel<32><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p);
+          else attention_tc_kernel<64><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p);
+          DMB_CHECK_LAUNCH();
+          count();
+          return;
+        }
+      }
       const int threads = std::min(128, (L + 31) / 32 * 32);
       const dim3 grid(cdiv(L, threads), 4, qkv.g.n);
       const size_t smem = static_cast<size_t>(L) * D * 2 * sizeof(float);
