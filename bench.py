@@ -197,6 +197,7 @@ def run_native(args):
     from models.vae import VAE
     from diff import Diffuser
     from dmb200 import context_for
+    from dmb200.sharding import gather_shards, shard_range
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -222,10 +223,9 @@ def run_native(args):
 
     # this rank's shard of the global batch: contiguous, conditions ordered by class globally
     y_all, vals_all, mask_all, _ = synth.mixed_conditions(B * world, seed=0)
-    sl = slice(rank * B, (rank + 1) * B)
+    sl = slice(*shard_range(B * world, rank, world))
     y_h, vals_h, mask_h = y_all[sl].contiguous(), vals_all[sl].contiguous(), mask_all[sl].contiguous()
     y, vals, mask = y_h.to(dev), vals_h.to(dev), mask_h.to(dev)
-    gathered = torch.empty((world * B, 3, 224, 224), dtype=torch.uint8, device=dev) if world > 1 else None
 
     def barrier():
         if world > 1:
@@ -239,7 +239,7 @@ def run_native(args):
                         sample_offset=rank * B)
         _, u8 = ctx.vae_decode(x, want_f32=False, want_u8=True)
         if world > 1:
-            dist.all_gather_into_tensor(gathered, u8)
+            return gather_shards(u8, world * B)  # one NCCL all-gather of the u8 images
         return u8
 
     for i in range(args.warmup):
