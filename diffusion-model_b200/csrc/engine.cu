@@ -83,7 +83,9 @@ struct Pool {
   ~Pool() { release(); }
 };
 
+bool g_allow_bn256 = true;   // 128 x 256 tiles where C_out allows (DMB200_BN256=0 turns it off)
 int pick_block_n(int N) {
+  if (g_allow_bn256 && N % 256 == 0) return 256;
   if (N % 128 == 0) return 128;
   if (N % 64 == 0) return 64;
   if (N % 32 == 0) return 32;
@@ -203,6 +205,7 @@ struct Plan {
   cudaGraphExec_t exec_one = nullptr;
   cudaGraphExec_t exec_chunk = nullptr;
   int chunk = 0;
+  int launches_per_step = 0;
   ~Plan() {
     if (exec_one) cudaGraphExecDestroy(exec_one);
     if (exec_chunk) cudaGraphExecDestroy(exec_chunk);
@@ -227,6 +230,8 @@ class Engine : public IEngine {
       DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
       DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     }
+    const char* bn = getenv("DMB200_BN256");
+    g_allow_bn256 = !(bn && bn[0] == '0');
     const char* env = getenv("DMB200_CUDA_CORE_ATTENTION");
     use_tc_attention_ = !(env && env[0] == '1');
   }
@@ -262,7 +267,7 @@ class Engine : public IEngine {
   void reset_launches() override { launches_ = 0; }
 
  private:
-  static constexpr int kGemmSmemMax = 227 * 1024 - 512;
+  static constexpr int kGemmSmemMax = 227 * 1024 - 2048;  // static smem (barriers, stat_part) comes out of the same 227 KB
 
   // ---- weights
   const float* f(const std::string& name) const {
@@ -284,7 +289,7 @@ class Engine : public IEngine {
   // ---- launch helpers
   Act<T> new_act(Pool& pool, int n, int H, int W, int C, bool with_stats, int stat_tiles = 0);
   void gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* shifts, int ntaps, GemmParams ep,
-            cudaStream_t s);
+            cudaStream_t s, const Act<T>* out_act = nullptr);
   Op op_conv(const Act<T>& in, const GemmW<T>& w, const Act<T>& out);
   Op op_lin(const Act<T>& in, const GemmW<T>& w, const Act<T>& out, int act, const Act<T>* residual);
   void build_unet_plan(Plan<T>& p);
@@ -558,10 +563,12 @@ Act<T> Engine<T>::new_act(Pool& pool, int n, int H, int W, int C, bool with_stat
 }
 
 // One launch of the tcgen05 GEMM.  `ep` carries the epilogue fields; the problem fields are
-// filled here from the activation, the weight and the tap list.
+// filled here from the activation, the weight and the tap list.  `out_act` (optional) is the
+// output activation when the tile can leave through a TMA store (identity row map, 128-byte
+// column blocks); otherwise the epilogue stores per thread.
 template <typename T>
 void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* shifts, int ntaps, GemmParams ep,
-                     cudaStream_t s) {
+                     cudaStream_t s, const Act<T>* out_act) {
   DMB_REQUIRE(a.C == w.K, "GEMM K mismatch");
   DMB_REQUIRE(ntaps <= kMaxTaps, "too many taps");
   GemmParams p = ep;
@@ -574,16 +581,21 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   p.block_n = w.bn;
   p.n_tiles = w.rows_per_tap / w.bn;
   p.m_tiles = cdiv(a.g.rows_valid, kTileM);
+  p.tma_store = (out_act && ep.epi == EPI_STORE && ep.map_mode == 0 && w.bn % ElemTraits<T>::kChunkK == 0 &&
+                 out_act->C % ElemTraits<T>::kChunkK == 0 && out_act->C >= p.n_tiles * w.bn &&
+                 out_act->g.rows_alloc == a.g.rows_alloc && ep.out == out_act->p && ep.ldc == out_act->C)
+                    ? 1 : 0;
   const int stage_bytes = kTileM * 128 + w.bn * 128;
-  p.stages = std::min(kMaxStages, (kGemmSmemMax - 1024) / stage_bytes);
+  const int staging = p.tma_store ? kStagingBytes : 0;
+  p.stages = std::min(kMaxStages, (kGemmSmemMax - 1024 - staging) / stage_bytes);
   p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM, w.bn);
   p.tmem_cols = tmem_cols_for(w.bn);
   p.geo = a.g;
   p.rows_alloc = a.g.rows_alloc;
   p.n_valid = w.N;
-  const int smem = p.stages * stage_bytes + 1024;
+  const int smem = p.stages * stage_bytes + staging + 1024;
   const int grid = std::min(p.m_tiles * p.n_tiles, num_sms_);
-  gemm_tc_kernel<T><<<grid, 256, smem, s>>>(a.tmap, w.tmap, p);
+  gemm_tc_kernel<T><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap, p.tma_store ? out_act->tmap : a.tmap, p);
   DMB_CHECK_LAUNCH();
   count();
 }
@@ -599,7 +611,7 @@ Op Engine<T>::op_conv(const Act<T>& in, const GemmW<T>& w, const Act<T>& out) {
     ep.out = out.p; ep.ldc = out.C;
     ep.bias = w.bias;
     ep.rowstats = out.stats;
-    gemm(in, w, 0, shifts, 9, ep, s);
+    gemm(in, w, 0, shifts, 9, ep, s, &out);
   };
 }
 
@@ -612,7 +624,7 @@ Op Engine<T>::op_lin(const Act<T>& in, const GemmW<T>& w, const Act<T>& out, int
     ep.epi = EPI_STORE;
     ep.out = out.p; ep.ldc = out.C;
     ep.bias = w.bias; ep.act = act; ep.residual = res;
-    gemm(in, w, 0, &shift0, 1, ep, s);
+    gemm(in, w, 0, &shift0, 1, ep, s, &out);
   };
 }
 
@@ -657,12 +669,18 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     const T* res = residual ? residual->p : nullptr;
     const float* embproj = P.embproj;
     const int total_vec = raw.g.H * raw.g.W * raw.C / 8;
-    const int splits = std::max(1, std::min(8, total_vec / 2048));
+    // enough CTAs to fill the chip at small batch, whole samples per CTA at large batch
+    const int want = (8 * num_sms_ + raw.g.n - 1) / raw.g.n;
+    const int splits = std::max(1, std::min(std::min(want, 16), total_vec / 512));
     ops.tag("gn1_apply", 0, static_cast<double>(raw.g.n) * total_vec * 8 * sizeof(T) * (residual ? 3 : 2));
     ops.push_back([this, raw, out, gamma, beta, mode, res, embproj, emb_off, splits](cudaStream_t s) {
-      gn1_apply_kernel<T><<<dim3(splits, raw.g.n), 256, 0, s>>>(raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc,
-                                                                gamma, beta, mode, res, embproj, emb_off, raw.g,
-                                                                raw.C, out.p);
+      const dim3 grid(splits, raw.g.n);
+#define DMB_GN_ARGS raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc, gamma, beta, res, embproj, emb_off, raw.g, raw.C, out.p
+      if (mode == GN_GELU) gn1_apply_kernel<T, GN_GELU><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
+      else if (mode == GN_RES_GELU) gn1_apply_kernel<T, GN_RES_GELU><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
+      else if (mode == GN_ADD_EMB) gn1_apply_kernel<T, GN_ADD_EMB><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
+      else gn1_apply_kernel<T, GN_NONE><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
+#undef DMB_GN_ARGS
       DMB_CHECK_LAUNCH();
       count();
     });
@@ -691,11 +709,12 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       const float* bv = f(name + ".bias");
       ops.tag("layernorm", 0, 2.0 * in.g.n * in.g.H * in.g.W * C * sizeof(T));
       ops.push_back([this, in, out, wv, bv, C](cudaStream_t s) {
-        const long long ntok = static_cast<long long>(in.g.n) * in.g.H * in.g.W;
-        const int grid = cdiv(ntok, 8);
-        if (C == 64) layernorm_kernel<T, 2><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
-        else if (C == 128) layernorm_kernel<T, 4><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
-        else layernorm_kernel<T, 8><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
+        // C/8 lanes per token; each block walks rows with a grid stride
+        const int tpb = 256 / (C / 8);
+        const int grid = std::max(1, std::min(cdiv(in.g.rows_valid, tpb * 2), num_sms_ * 8));
+        if (C == 64) layernorm_kernel<T, 8><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
+        else if (C == 128) layernorm_kernel<T, 16><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
+        else layernorm_kernel<T, 32><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
         DMB_CHECK_LAUNCH();
         count();
       });
@@ -715,11 +734,16 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       const int L = qkv.g.H * qkv.g.W, D = C / 4;
       if constexpr (std::is_same<T, __nv_bfloat16>::value) {
         if (use_tc_attention_) {
-          const dim3 grid(cdiv(L, kAttnBlock), 4, qkv.g.n);
+          // whole (sample, head) per CTA when there are enough of them to fill the chip twice
+          // over; otherwise the query blocks are spread over more CTAs
+          const int nqb = cdiv(L, kAttnQ);
+          const int qsplit = std::max(1, std::min(nqb, cdiv(4 * num_sms_, 4 * qkv.g.n)));
+          const int qpc = cdiv(nqb, qsplit);
+          const dim3 grid(cdiv(nqb, qpc), 4, qkv.g.n);
           const size_t smem = attention_tc_smem_bytes(L, D);
-          if (D == 16) attention_tc_kernel<16><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p);
-          else if (D == 32) attention_tc_kernel<32><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p);
-          else attention_tc_kernel<64><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p);
+          if (D == 16) attention_tc_kernel<16><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
+          else if (D == 32) attention_tc_kernel<32><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
+          else attention_tc_kernel<64><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
           DMB_CHECK_LAUNCH();
           count();
           return;
@@ -932,25 +956,25 @@ void Engine<T>::sample_loop(float* x, const long long* y, int null_label, const 
     DMB_CHECK_LAUNCH();
     count(2);
   };
-  const int launches_per_step = static_cast<int>(p.ops.size()) + 2;
   auto capture = [&](int steps) {
     cudaStream_t cs;
     DMB_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
-    counting_ = false;
+    const long long before = launches_;  // kernels recorded into the graph are counted per replay
     try {
       DMB_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
       for (int i = 0; i < steps; ++i) one_step(cs);
       DMB_CUDA(cudaStreamEndCapture(cs, &graph));
       DMB_CUDA(cudaGraphInstantiate(&exec, graph, 0));
     } catch (...) {
-      counting_ = true;
+      launches_ = before;
       if (graph) cudaGraphDestroy(graph);
       cudaStreamDestroy(cs);
       throw;
     }
-    counting_ = true;
+    p.launches_per_step = static_cast<int>((launches_ - before) / steps);
+    launches_ = before;
     cudaGraphDestroy(graph);
     cudaStreamDestroy(cs);
     return exec;
@@ -964,12 +988,12 @@ void Engine<T>::sample_loop(float* x, const long long* y, int null_label, const 
   int left = n_steps;
   while (left >= chunk && p.exec_chunk) {
     DMB_CUDA(cudaGraphLaunch(p.exec_chunk, s));
-    launches_ += static_cast<long long>(chunk) * launches_per_step;
+    launches_ += static_cast<long long>(chunk) * p.launches_per_step;
     left -= chunk;
   }
   while (left > 0) {
     DMB_CUDA(cudaGraphLaunch(p.exec_one, s));
-    launches_ += launches_per_step;
+    launches_ += p.launches_per_step;
     --left;
   }
   DMB_CUDA(cudaMemcpyAsync(x, p.x_state, lat * sizeof(float), cudaMemcpyDefault, s));

@@ -8,13 +8,19 @@
 // tensor arrive as zeros.  A 1x1 conv / Linear is the one-tap case; a 4x4 stride-2
 // transposed conv is four 4-tap launches (one per output phase) with a scattering row map.
 //
-// CTA = 256 threads, one CTA per SM, persistent over 128 x BLOCK_N output tiles:
-//   warp 0   TMA producer   (one lane)  : fills the smem ring, signals full[s] via complete_tx
-//   warp 1   MMA issuer     (one lane)  : tcgen05.mma SS, commits to empty[s] / tmem_full[a]
-//   warp 2   TMEM allocator
-//   warps 4-7 epilogue      (128 thr)   : tcgen05.ld lane==row, bias/GELU/residual, row
-//                                         statistics for GroupNorm, masked stores
+// CTA = 384 threads, one CTA per SM, persistent over 128 x BLOCK_N output tiles:
+//   warp 0    TMA producer   (one lane)  : fills the smem ring, signals full[s] via complete_tx
+//   warp 1    MMA issuer     (one lane)  : tcgen05.mma SS, commits to empty[s] / tmem_full[a]
+//   warp 2    TMEM allocator
+//   warps 4-11 epilogue      (256 thr)   : two warps per TMEM lane quadrant (each takes half of
+//                                          the columns): tcgen05.ld lane==row, bias / GELU /
+//                                          residual, row statistics for GroupNorm, then the
+//                                          tile goes through a 128B-swizzled staging buffer
+//                                          and out with ONE TMA store per 128-byte column
+//                                          block (pad-pixel rows are stored as zeros).
 // Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
+// Scattering outputs (conv-transpose phases), the image epilogue and tiles narrower than
+// 128 bytes keep per-thread stores.
 #pragma once
 
 #include "common.cuh"
@@ -49,21 +55,29 @@ struct GemmParams {
   int map_mode;           // 0 identity; 1 = out pixel (2y+up_a, 2x+up_b) of geo_out
   Geo geo_out;
   int up_a, up_b;
+  int tma_store;          // 1: epilogue stores through smem + TMA (tmap_out); 0: per-thread stores
   float* img_f32;         // EPI_IMAGE: (n, n_valid, H, W) planar fp32, sigmoid applied
   uint8_t* img_u8;        // EPI_IMAGE: same, x255 clamp truncate
 };
 
+constexpr int kGemmThreads = 384;
+constexpr int kEpiThreads = 256;
+constexpr int kStagingBytes = 2 * kTileM * 128;  // two 128-row x 128-byte sub-tiles
+
 template <typename T>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-               const GemmParams p) {
+               const __grid_constant__ CUtensorMap tmap_out, const GemmParams p) {
   using Tr = ElemTraits<T>;
+  constexpr int kSubN = Tr::kChunkK;   // columns per 128-byte sub-tile (64 bf16 / 32 fp32)
+  constexpr int kHalf = kSubN / 2;     // columns one epilogue warp takes of a sub-tile
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_smem;
+  __shared__ float2 stat_part[kTileM];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -74,10 +88,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const uint32_t a_bytes = kTileM * 128;
   const uint32_t b_bytes = static_cast<uint32_t>(p.block_n) * 128;
   const uint32_t stage_bytes = a_bytes + b_bytes;
+  uint8_t* staging = smem + static_cast<size_t>(p.stages) * stage_bytes;  // 1024-aligned (stage_bytes % 1024 == 0)
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
+    if (p.tma_store) tma_prefetch_desc(&tmap_out);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < p.stages; ++s) {
@@ -86,7 +102,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full_bar[a], 1);
-      mbar_init(&tmem_empty_bar[a], 128);
+      mbar_init(&tmem_empty_bar[a], kEpiThreads);
     }
     fence_mbar_init();
   }
@@ -156,43 +172,129 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
   } else if (warp >= 4) {
     // ------------------------------------------------------------- epilogue
-    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    const int q = warp & 3;          // TMEM lane quadrant this warp may read
+    const int h = (warp - 4) >> 2;   // which half of the columns this warp takes
+    const int row_in_tile = q * 32 + lane;
+    const bool store_thread = threadIdx.x == 128;
     T* out = reinterpret_cast<T*>(p.out);
     const T* residual = reinterpret_cast<const T*>(p.residual);
     uint32_t tile_count = 0;
+    uint32_t sub_count = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tile_count) {
       const int n_tile = tile % p.n_tiles;
       const int m_tile = tile / p.n_tiles;
       const int n0 = n_tile * p.block_n;
-      const int r = m_tile * kTileM + q * 32 + lane;
+      const int m0 = m_tile * kTileM;
+      const int r = m0 + row_in_tile;
       int b = 0, y = 0, x = 0;
       const bool valid = geo_decode(p.geo, r, b, y, x);
-      int out_r = r;
-      if (p.map_mode == 1 && valid) out_r = geo_row(p.geo_out, b, 2 * y + p.up_a, 2 * x + p.up_b);
 
       const uint32_t as = tile_count & 1;
       const uint32_t aph = (tile_count >> 1) & 1;
       mbar_wait(&tmem_full_bar[as], aph);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * p.block_n;
+      float sum = 0.f, sumsq = 0.f;
 
-      if (p.epi == EPI_IMAGE) {
-        float v[16];
-        tmem_ld16(t_row, v);
-        tmem_ld_wait();
-        if (valid) {
-          const size_t plane = static_cast<size_t>(p.geo.H) * p.geo.W;
-          for (int c = 0; c < p.n_valid; ++c) {
-            float s = v[c] + (p.bias ? __ldg(p.bias + c) : 0.f);
-            s = 1.0f / (1.0f + expf(-s));
-            const size_t o = (static_cast<size_t>(b) * p.n_valid + c) * plane + static_cast<size_t>(y) * p.geo.W + x;
-            if (p.img_f32) p.img_f32[o] = s;
-            if (p.img_u8) p.img_u8[o] = static_cast<uint8_t>(fminf(fmaxf(s * 255.0f, 0.f), 255.f));
+      if (p.tma_store) {
+        const int n_sub = p.block_n / kSubN;
+        for (int k = 0; k < n_sub; ++k) {
+          float v[32];
+          if constexpr (kHalf == 32) {
+            tmem_ld32(t_row + k * kSubN + h * kHalf, v);
+          } else {
+            tmem_ld16(t_row + k * kSubN + h * kHalf, v);
+          }
+          tmem_ld_wait();
+          if (k == n_sub - 1) {  // accumulator fully read: hand it back to the MMA issuer
+            tc_fence_before();
+            mbar_arrive(&tmem_empty_bar[as]);
+          }
+          const int col0 = n0 + k * kSubN + h * kHalf;
+          if (valid) {
+            if (p.bias) {
+#pragma unroll
+              for (int j = 0; j < kHalf; j += 4) {
+                const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+                v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
+              }
+            }
+            if (p.act == 1) {
+#pragma unroll
+              for (int j = 0; j < kHalf; ++j) v[j] = gelu_erf(v[j]);
+            }
+            if (residual) {
+              const T* rp = residual + static_cast<size_t>(r) * p.ldc + col0;
+#pragma unroll
+              for (int j = 0; j < kHalf; j += 8) {
+                float rv[8];
+                load8(rp + j, rv);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[j + i] += rv[i];
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < kHalf; ++j) {
+              sum += v[j];
+              sumsq += v[j] * v[j];
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < kHalf; ++j) v[j] = 0.f;  // pad pixels stay zero
+          }
+          uint8_t* buf = staging + (sub_count & 1) * (kTileM * 128);
+          if (store_thread) tma_store_wait_read<1>();  // the store that used this buffer two sub-tiles ago
+          named_bar_sync(1, kEpiThreads);
+          {
+            uint8_t* rowp = buf + row_in_tile * 128;
+            const int sw = row_in_tile & 7;
+            if constexpr (sizeof(T) == 2) {
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                uint4 u;
+                __nv_bfloat162* hp = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) hp[i] = __floats2bfloat162_rn(v[c * 8 + 2 * i], v[c * 8 + 2 * i + 1]);
+                *reinterpret_cast<uint4*>(rowp + (((h * 4 + c) ^ sw) << 4)) = u;
+              }
+            } else {
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                *reinterpret_cast<float4*>(rowp + (((h * 4 + c) ^ sw) << 4)) =
+                    make_float4(v[c * 4], v[c * 4 + 1], v[c * 4 + 2], v[c * 4 + 3]);
+              }
+            }
+          }
+          fence_async_proxy();
+          named_bar_sync(1, kEpiThreads);
+          if (store_thread) {
+            tma_store_2d(&tmap_out, buf, n0 + k * kSubN, m0);
+            tma_store_commit();
+          }
+          ++sub_count;
+        }
+      } else if (p.epi == EPI_IMAGE) {
+        if (h == 0) {
+          float v[16];
+          tmem_ld16(t_row, v);
+          tmem_ld_wait();
+          if (valid) {
+            const size_t plane = static_cast<size_t>(p.geo.H) * p.geo.W;
+            for (int c = 0; c < p.n_valid; ++c) {
+              float s = v[c] + (p.bias ? __ldg(p.bias + c) : 0.f);
+              s = 1.0f / (1.0f + expf(-s));
+              const size_t o = (static_cast<size_t>(b) * p.n_valid + c) * plane + static_cast<size_t>(y) * p.geo.W + x;
+              if (p.img_f32) p.img_f32[o] = s;
+              if (p.img_u8) p.img_u8[o] = static_cast<uint8_t>(fminf(fmaxf(s * 255.0f, 0.f), 255.f));
+            }
           }
         }
+        tc_fence_before();
+        mbar_arrive(&tmem_empty_bar[as]);
       } else {
-        float sum = 0.f, sumsq = 0.f;
-        for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+        int out_r = r;
+        if (p.map_mode == 1 && valid) out_r = geo_row(p.geo_out, b, 2 * y + p.up_a, 2 * x + p.up_b);
+        for (int c0 = h * 32; c0 < p.block_n; c0 += 64) {
           float v[32];
           if (p.block_n - c0 >= 32) {
             tmem_ld32(t_row + c0, v);
@@ -240,13 +342,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
           }
         }
-        if (p.rowstats && valid) {
-          p.rowstats[static_cast<size_t>(n_tile) * p.rows_alloc + r] = make_float2(sum, sumsq);
-        }
+        tc_fence_before();
+        mbar_arrive(&tmem_empty_bar[as]);
       }
-      tc_fence_before();
-      mbar_arrive(&tmem_empty_bar[as]);
+      if (p.rowstats) {
+        // the two column halves of a row meet in shared memory; fixed order -> deterministic
+        if (h == 1) stat_part[row_in_tile] = make_float2(sum, sumsq);
+        named_bar_sync(1, kEpiThreads);
+        if (h == 0 && valid) {
+          const float2 o = stat_part[row_in_tile];
+          p.rowstats[static_cast<size_t>(n_tile) * p.rows_alloc + r] = make_float2(sum + o.x, sumsq + o.y);
+        }
+        named_bar_sync(1, kEpiThreads);
+      }
     }
+    if (store_thread) tma_store_wait_all<0>();
   }
 
   tc_fence_before();

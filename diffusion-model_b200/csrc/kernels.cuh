@@ -139,71 +139,113 @@ conv_in_kernel(const float* __restrict__ x, int B_src, const float* __restrict__
 // ---------------------------------------------------------------------------
 enum GnMode : int { GN_NONE = 0, GN_GELU = 1, GN_RES_GELU = 2, GN_ADD_EMB = 3 };
 
-template <typename T>
-__global__ void __launch_bounds__(256)
-gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats, int n_stat_tiles,
-                 int rows_alloc, const float* __restrict__ gamma, const float* __restrict__ beta,
-                 int mode, const T* __restrict__ residual, const float* __restrict__ embproj,
+// Streams one sample's PM block [S rows x C] contiguously: a thread owns one 8-channel vector
+// column (scale / shift live in registers) and walks the rows; pad rows are skipped (they
+// stay zero in `out`).  grid = (splits, n).  MODE is a template parameter to keep the
+// register count low enough for 4 CTAs per SM (the erf GELU makes this kernel issue-bound
+// as much as HBM-bound).
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256, 4)
+gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats, int n_stat_tiles, int rows_alloc,
+                 const float* __restrict__ gamma, const float* __restrict__ beta,
+                 const T* __restrict__ residual, const float* __restrict__ embproj,
                  int emb_off, Geo g, int C, T* __restrict__ out) {
-  __shared__ double red[2][256];
-  __shared__ float s_mean, s_rstd;
   const int b = blockIdx.y;
   const int tid = threadIdx.x;
-  const int HW = g.H * g.W;
-  double s1 = 0.0, s2 = 0.0;
-  for (int i = tid; i < HW; i += 256) {
-    const int r = geo_row(g, b, i / g.W, i % g.W);
-    for (int tn = 0; tn < n_stat_tiles; ++tn) {
-      const float2 v = rowstats[static_cast<size_t>(tn) * rows_alloc + r];
-      s1 += v.x; s2 += v.y;
+  const int vpr = C >> 3;                  // vectors per row: 8, 16, 32 or 64
+  const int rows_per_iter = 256 / vpr;
+  const int cv = tid % vpr;
+  const int c0 = cv * 8;
+  // ---- statistics: the producing conv left per-row (sum, sumsq) partials; every CTA of the
+  // sample reduces them in the same fixed order (double), so the result does not depend on
+  // the sample's position in the batch nor on how the batch is sharded.
+  __shared__ double red[2][8];
+  __shared__ float s_mean, s_rstd;
+  {
+    double s1 = 0.0, s2 = 0.0;
+    const size_t sbase = static_cast<size_t>(b) * g.S;
+    for (int rr = g.Wp + tid; rr < g.S; rr += 256) {
+      if (rr % g.Wp == g.W) continue;
+      float a1 = 0.f, a2 = 0.f;
+      for (int tn = 0; tn < n_stat_tiles; ++tn) {
+        const float2 v = rowstats[static_cast<size_t>(tn) * rows_alloc + sbase + rr];
+        a1 += v.x; a2 += v.y;
+      }
+      s1 += a1; s2 += a2;
     }
-  }
-  red[0][tid] = s1; red[1][tid] = s2;
-  __syncthreads();
-  for (int off = 128; off > 0; off >>= 1) {
-    if (tid < off) { red[0][tid] += red[0][tid + off]; red[1][tid] += red[1][tid + off]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    if ((tid & 31) == 0) { red[0][tid >> 5] = s1; red[1][tid >> 5] = s2; }
+    __syncthreads();
+    if (tid == 0) {
+      double t1 = 0.0, t2 = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) { t1 += red[0][w]; t2 += red[1][w]; }
+      const double cnt = static_cast<double>(g.H) * g.W * C;
+      const double mean = t1 / cnt;
+      double var = t2 / cnt - mean * mean;
+      if (var < 0.0) var = 0.0;
+      s_mean = static_cast<float>(mean);
+      s_rstd = rsqrtf(static_cast<float>(var) + 1e-5f);
+    }
     __syncthreads();
   }
-  if (tid == 0) {
-    const double cnt = static_cast<double>(HW) * C;
-    const double mean = red[0][0] / cnt;
-    double var = red[1][0] / cnt - mean * mean;
-    if (var < 0.0) var = 0.0;
-    s_mean = static_cast<float>(mean);
-    s_rstd = static_cast<float>(1.0 / sqrt(var + 1e-5));
-  }
-  __syncthreads();
-  const float mean = s_mean, rstd = s_rstd;
-  const int vpr = C / 8;
-  const int total = HW * vpr;
-  const int per = (total + gridDim.x - 1) / gridDim.x;
-  const int begin = blockIdx.x * per;
-  const int end = min(total, begin + per);
-  for (int v = begin + tid; v < end; v += 256) {
-    const int pix = v / vpr, c0 = (v % vpr) * 8;
-    const size_t off = static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * C + c0;
-    float xv[8];
-    load8(raw + off, xv);
+  float sc[8], sh[8];   // y = x * sc + sh  ==  (x - mean) * rstd * gamma + beta (+ emb)
+  {
+    const float mean = s_mean, rstd = s_rstd;
     const float4 ga = *reinterpret_cast<const float4*>(gamma + c0), gb = *reinterpret_cast<const float4*>(gamma + c0 + 4);
     const float4 ba = *reinterpret_cast<const float4*>(beta + c0), bb = *reinterpret_cast<const float4*>(beta + c0 + 4);
     const float gm[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
     const float bt[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
-    for (int i = 0; i < 8; ++i) xv[i] = (xv[i] - mean) * rstd * gm[i] + bt[i];
-    if (mode == GN_GELU) {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) xv[i] = gelu_erf(xv[i]);
-    } else if (mode == GN_RES_GELU) {
-      float rv[8];
-      load8(residual + off, rv);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) xv[i] = gelu_erf(rv[i] + xv[i]);
-    } else if (mode == GN_ADD_EMB) {
+    for (int i = 0; i < 8; ++i) {
+      sc[i] = rstd * gm[i];
+      sh[i] = fmaf(-mean, sc[i], bt[i]);
+    }
+    if (MODE == GN_ADD_EMB) {
       const float* e = embproj + static_cast<size_t>(b) * kProjCols + emb_off + c0;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) xv[i] += e[i];
+      for (int i = 0; i < 8; ++i) sh[i] += e[i];
     }
-    store8(out + off, xv);
+  }
+  // rows of this CTA: [r_begin, r_end) of the sample's S rows, skipping the leading pad row
+  const int rows = g.S - g.Wp;
+  const int per = (rows + gridDim.x - 1) / gridDim.x;
+  const int r_begin = g.Wp + blockIdx.x * per;
+  const int r_end = min(g.S, r_begin + per);
+  const size_t base = static_cast<size_t>(b) * g.S;
+  constexpr int U = 2;  // rows in flight per thread
+  for (int rr0 = r_begin + tid / vpr; rr0 < r_end; rr0 += U * rows_per_iter) {
+    float xv[U][8], rv[U][8];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int rr = rr0 + u * rows_per_iter;
+      ok[u] = rr < r_end && (rr % g.Wp != g.W);
+      if (ok[u]) {
+        const size_t off = (base + rr) * C + c0;
+        load8(raw + off, xv[u]);
+        if (MODE == GN_RES_GELU) load8(residual + off, rv[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!ok[u]) continue;
+      const size_t off = (base + rr0 + u * rows_per_iter) * C + c0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xv[u][i] = fmaf(xv[u][i], sc[i], sh[i]);
+      if (MODE == GN_GELU) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) xv[u][i] = gelu_erf(xv[u][i]);
+      } else if (MODE == GN_RES_GELU) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) xv[u][i] = gelu_erf(rv[u][i] + xv[u][i]);
+      }
+      store8(out + off, xv[u]);
+    }
   }
 }
 
@@ -279,38 +321,65 @@ __global__ void upcat_kernel(const T* __restrict__ skip, int Cs, const T* __rest
   store8(out + static_cast<size_t>(r) * C + c0, o);
 }
 
-// LayerNorm over channels of every real pixel (token).  One warp per token, EPL = C/32
-// contiguous channels per lane.  models/unet_cond.py:37, 39, 48.
-template <typename T, int EPL>
+// LayerNorm over the channels of every real pixel (token).  LPT = C/8 lanes share a token,
+// 16 bytes per lane; the PM rows are streamed contiguously and pad rows are skipped (they
+// stay zero in `out`).  models/unet_cond.py:37, 39, 48.
+template <typename T, int LPT>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const T* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
                  Geo g, T* __restrict__ out) {
-  constexpr int C = EPL * 32;
-  const int lane = threadIdx.x & 31;
-  const long long tok = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const long long ntok = static_cast<long long>(g.n) * g.H * g.W;
-  if (tok >= ntok) return;
-  const int HW = g.H * g.W;
-  const int b = static_cast<int>(tok / HW);
-  const int pix = static_cast<int>(tok % HW);
-  const size_t off = static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * C + lane * EPL;
-  float v[EPL];
-  float s = 0.f;
+  constexpr int C = LPT * 8;
+  constexpr int TPB = 256 / LPT;  // tokens (PM rows) per block iteration
+  const int sub = threadIdx.x % LPT;
+  const int c0 = sub * 8;
+  float wv[8], bv[8];
+  {
+    const float4 wa = *reinterpret_cast<const float4*>(w + c0), wb = *reinterpret_cast<const float4*>(w + c0 + 4);
+    const float4 ba = *reinterpret_cast<const float4*>(bias + c0), bb = *reinterpret_cast<const float4*>(bias + c0 + 4);
+    wv[0] = wa.x; wv[1] = wa.y; wv[2] = wa.z; wv[3] = wa.w; wv[4] = wb.x; wv[5] = wb.y; wv[6] = wb.z; wv[7] = wb.w;
+    bv[0] = ba.x; bv[1] = ba.y; bv[2] = ba.z; bv[3] = ba.w; bv[4] = bb.x; bv[5] = bb.y; bv[6] = bb.z; bv[7] = bb.w;
+  }
+  constexpr int U = 2;
+  for (long long r0 = static_cast<long long>(blockIdx.x) * TPB * U + threadIdx.x / LPT; r0 < g.rows_valid;
+       r0 += static_cast<long long>(gridDim.x) * TPB * U) {
+    float v[U][8];
+    bool ok[U];
 #pragma unroll
-  for (int i = 0; i < EPL; ++i) { v[i] = to_f32(in[off + i]); s += v[i]; }
+    for (int u = 0; u < U; ++u) {
+      const long long r = r0 + u * TPB;
+      ok[u] = false;
+      if (r < g.rows_valid) {
+        const int rr = static_cast<int>(r % g.S);
+        ok[u] = rr >= g.Wp && (rr % g.Wp) != g.W;
+      }
+      if (ok[u]) load8(in + static_cast<size_t>(r) * C + c0, v[u]);
+      else {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  const float mean = s * (1.0f / C);
-  float q = 0.f;
+        for (int i = 0; i < 8; ++i) v[u][i] = 0.f;
+      }
+    }
 #pragma unroll
-  for (int i = 0; i < EPL; ++i) { const float d = v[i] - mean; q += d * d; }
+    for (int u = 0; u < U; ++u) {
+      // all lanes take part in the shuffles; pad rows just do not store
+      float s = 0.f;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
-  const float rstd = rsqrtf(q * (1.0f / C) + 1e-5f);
+      for (int i = 0; i < 8; ++i) s += v[u][i];
 #pragma unroll
-  for (int i = 0; i < EPL; ++i) {
-    const int c = lane * EPL + i;
-    out[off + i] = from_f32<T>((v[i] - mean) * rstd * w[c] + bias[c]);
+      for (int o = LPT / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      const float mean = s * (1.0f / C);
+      float q = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { const float d = v[u][i] - mean; q += d * d; }
+#pragma unroll
+      for (int o = LPT / 2; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+      const float rstd = rsqrtf(q * (1.0f / C) + 1e-5f);
+      if (ok[u]) {
+        float o8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o8[i] = (v[u][i] - mean) * rstd * wv[i] + bv[i];
+        store8(out + static_cast<size_t>(r0 + u * TPB) * C + c0, o8);
+      }
+    }
   }
 }
 
