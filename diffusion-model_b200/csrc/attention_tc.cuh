@@ -93,7 +93,7 @@ attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bf
         kv[u] = zero; vv[u] = zero;
         if (idx < total && key[u] < L) {
           const __nv_bfloat16* rp =
-              qkv + static_cast<size_t>(geo_row(g, b, key[u] / g.W, key[u] % g.W)) * ld + h * D + 8 * c[u];
+              qkv + static_cast<size_t>(geo_row_of_pixel(g, b, key[u])) * ld + h * D + 8 * c[u];
           kv[u] = *reinterpret_cast<const uint4*>(rp + E);
           vv[u] = *reinterpret_cast<const uint4*>(rp + 2 * E);
         }
@@ -126,7 +126,7 @@ attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bf
     // ---- stage this block's queries
     const int qi = qb * kAttnQ + tid;
     const bool q_valid = qi < L;
-    const int qrow = q_valid ? geo_row(g, b, qi / g.W, qi % g.W) : 0;
+    const int qrow = q_valid ? geo_row_of_pixel(g, b, qi) : 0;
     {
       const uint4 zero = make_uint4(0, 0, 0, 0);
       const __nv_bfloat16* qp = qkv + static_cast<size_t>(qrow) * ld + h * D;
@@ -174,9 +174,15 @@ attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bf
         for (int i = 0; i < kAttnK; ++i)
           if (kbase + i >= L) s[i] = -INFINITY;
       }
-      float bm = s[0];
+      float bm;
+      {  // four independent chains: a serial max over 64 values would expose 64 x 4 cycles
+        float m0 = s[0], m1 = s[1], m2 = s[2], m3 = s[3];
 #pragma unroll
-      for (int i = 1; i < kAttnK; ++i) bm = fmaxf(bm, s[i]);
+        for (int i = 4; i < kAttnK; i += 4) {
+          m0 = fmaxf(m0, s[i]); m1 = fmaxf(m1, s[i + 1]); m2 = fmaxf(m2, s[i + 2]); m3 = fmaxf(m3, s[i + 3]);
+        }
+        bm = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+      }
       if (j == 0) {
         m_run = bm;
       } else {
@@ -205,10 +211,17 @@ attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bf
         }
       }
       const float mc = m_run * c2;
+      {
+        float r0 = 0.f, r1 = 0.f, r2 = 0.f, r3 = 0.f;
 #pragma unroll
-      for (int i = 0; i < kAttnK; ++i) {
-        s[i] = ex2_approx(fmaf(s[i], c2, -mc));   // exp2(-inf) = 0 for masked keys
-        rowsum += s[i];
+        for (int i = 0; i < kAttnK; i += 4) {
+          s[i] = ex2_approx(fmaf(s[i], c2, -mc));   // exp2(-inf) = 0 for masked keys
+          s[i + 1] = ex2_approx(fmaf(s[i + 1], c2, -mc));
+          s[i + 2] = ex2_approx(fmaf(s[i + 2], c2, -mc));
+          s[i + 3] = ex2_approx(fmaf(s[i + 3], c2, -mc));
+          r0 += s[i]; r1 += s[i + 1]; r2 += s[i + 2]; r3 += s[i + 3];
+        }
+        rowsum += (r0 + r1) + (r2 + r3);
       }
       // P buffer `buf` was last read by the P V MMA of block G-2
       if (G >= 2) {

@@ -711,7 +711,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       ops.push_back([this, in, out, wv, bv, C](cudaStream_t s) {
         // C/8 lanes per token; each block walks rows with a grid stride
         const int tpb = 256 / (C / 8);
-        const int grid = std::max(1, std::min(cdiv(in.g.rows_valid, tpb * 2), num_sms_ * 8));
+        const int grid = std::max(1, std::min(cdiv(in.g.rows_valid, tpb * 8), num_sms_ * 8));
         if (C == 64) layernorm_kernel<T, 8><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
         else if (C == 128) layernorm_kernel<T, 16><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
         else layernorm_kernel<T, 32><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);

@@ -221,7 +221,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
             if (p.act == 1) {
 #pragma unroll
-              for (int j = 0; j < kHalf; ++j) v[j] = gelu_erf(v[j]);
+              for (int j = 0; j < kHalf; ++j) v[j] = gelu_for<T>(v[j]);
             }
             if (residual) {
               const T* rp = residual + static_cast<size_t>(r) * p.ldc + col0;
@@ -314,7 +314,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
             if (p.act == 1) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+              for (int j = 0; j < 32; ++j) v[j] = gelu_for<T>(v[j]);
             }
             if (residual) {
               const T* rp = residual + static_cast<size_t>(r) * p.ldc + col0;

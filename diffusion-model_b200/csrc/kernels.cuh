@@ -145,7 +145,7 @@ enum GnMode : int { GN_NONE = 0, GN_GELU = 1, GN_RES_GELU = 2, GN_ADD_EMB = 3 };
 // register count low enough for 4 CTAs per SM (the erf GELU makes this kernel issue-bound
 // as much as HBM-bound).
 template <typename T, int MODE>
-__global__ void __launch_bounds__(256, 4)
+__global__ void __launch_bounds__(256, 3)
 gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats, int n_stat_tiles, int rows_alloc,
                  const float* __restrict__ gamma, const float* __restrict__ beta,
                  const T* __restrict__ residual, const float* __restrict__ embproj,
@@ -165,7 +165,7 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
     double s1 = 0.0, s2 = 0.0;
     const size_t sbase = static_cast<size_t>(b) * g.S;
     for (int rr = g.Wp + tid; rr < g.S; rr += 256) {
-      if (rr % g.Wp == g.W) continue;
+      if (!geo_is_pixel(g, rr)) continue;
       float a1 = 0.f, a2 = 0.f;
       for (int tn = 0; tn < n_stat_tiles; ++tn) {
         const float2 v = rowstats[static_cast<size_t>(tn) * rows_alloc + sbase + rr];
@@ -217,35 +217,54 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   const int r_begin = g.Wp + blockIdx.x * per;
   const int r_end = min(g.S, r_begin + per);
   const size_t base = static_cast<size_t>(b) * g.S;
-  constexpr int U = 2;  // rows in flight per thread
-  for (int rr0 = r_begin + tid / vpr; rr0 < r_end; rr0 += U * rows_per_iter) {
-    float xv[U][8], rv[U][8];
+  constexpr int U = (MODE == GN_RES_GELU) ? 4 : 8;  // 16-byte loads in flight per thread and stream
+  // Incremental addressing: the row advances by rows_per_iter per load, its column inside the
+  // padded image row (x) is tracked modulo Wp, so the loop has no division and no 64-bit
+  // multiply.
+  int rr = r_begin + tid / vpr;
+  int x = rr - fdiv(rr, g.mWp, g.Wp) * g.Wp;
+  const int xstep = rows_per_iter - fdiv(rows_per_iter, g.mWp, g.Wp) * g.Wp;  // rows_per_iter mod Wp
+  const size_t first = (base + rr) * C + c0;
+  const T* rp = raw + first;
+  const T* sp = (MODE == GN_RES_GELU) ? residual + first : nullptr;
+  T* op = out + first;
+  const int stride = rows_per_iter * C;
+  while (rr < r_end) {
+    Raw8<T> xr[U], rs[U];
     bool ok[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int rr = rr0 + u * rows_per_iter;
-      ok[u] = rr < r_end && (rr % g.Wp != g.W);
+      ok[u] = (rr + u * rows_per_iter < r_end) && (x != g.W);
       if (ok[u]) {
-        const size_t off = (base + rr) * C + c0;
-        load8(raw + off, xv[u]);
-        if (MODE == GN_RES_GELU) load8(residual + off, rv[u]);
+        xr[u].load(rp + u * stride);
+        if (MODE == GN_RES_GELU) rs[u].load(sp + u * stride);
       }
+      x += xstep;
+      if (x >= g.Wp) x -= g.Wp;
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      if (!ok[u]) continue;
-      const size_t off = (base + rr0 + u * rows_per_iter) * C + c0;
+      if (ok[u]) {
+        float xv[8];
+        xr[u].unpack(xv);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) xv[u][i] = fmaf(xv[u][i], sc[i], sh[i]);
-      if (MODE == GN_GELU) {
+        for (int i = 0; i < 8; ++i) xv[i] = fmaf(xv[i], sc[i], sh[i]);
+        if (MODE == GN_GELU) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) xv[u][i] = gelu_erf(xv[u][i]);
-      } else if (MODE == GN_RES_GELU) {
+          for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>(xv[i]);
+        } else if (MODE == GN_RES_GELU) {
+          float rv[8];
+          rs[u].unpack(rv);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) xv[u][i] = gelu_erf(rv[u][i] + xv[u][i]);
+          for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>(rv[i] + xv[i]);
+        }
+        store8(op + u * stride, xv);
       }
-      store8(out + off, xv[u]);
     }
+    rr += U * rows_per_iter;
+    rp += U * stride;
+    if (MODE == GN_RES_GELU) sp += U * stride;
+    op += U * stride;
   }
 }
 
@@ -325,7 +344,7 @@ __global__ void upcat_kernel(const T* __restrict__ skip, int Cs, const T* __rest
 // 16 bytes per lane; the PM rows are streamed contiguously and pad rows are skipped (they
 // stay zero in `out`).  models/unet_cond.py:37, 39, 48.
 template <typename T, int LPT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 layernorm_kernel(const T* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
                  Geo g, T* __restrict__ out) {
   constexpr int C = LPT * 8;
@@ -339,44 +358,42 @@ layernorm_kernel(const T* __restrict__ in, const float* __restrict__ w, const fl
     wv[0] = wa.x; wv[1] = wa.y; wv[2] = wa.z; wv[3] = wa.w; wv[4] = wb.x; wv[5] = wb.y; wv[6] = wb.z; wv[7] = wb.w;
     bv[0] = ba.x; bv[1] = ba.y; bv[2] = ba.z; bv[3] = ba.w; bv[4] = bb.x; bv[5] = bb.y; bv[6] = bb.z; bv[7] = bb.w;
   }
-  constexpr int U = 2;
-  for (long long r0 = static_cast<long long>(blockIdx.x) * TPB * U + threadIdx.x / LPT; r0 < g.rows_valid;
-       r0 += static_cast<long long>(gridDim.x) * TPB * U) {
-    float v[U][8];
+  constexpr int U = 8;
+  for (int r0 = blockIdx.x * TPB * U + threadIdx.x / LPT; r0 < g.rows_valid; r0 += gridDim.x * TPB * U) {
+    Raw8<T> xr[U];
     bool ok[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const long long r = r0 + u * TPB;
+      const int r = r0 + u * TPB;
       ok[u] = false;
-      if (r < g.rows_valid) {
-        const int rr = static_cast<int>(r % g.S);
-        ok[u] = rr >= g.Wp && (rr % g.Wp) != g.W;
-      }
-      if (ok[u]) load8(in + static_cast<size_t>(r) * C + c0, v[u]);
-      else {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) v[u][i] = 0.f;
-      }
+      if (r < g.rows_valid) ok[u] = geo_is_pixel(g, r - fdiv(r, g.mS, g.S) * g.S);
+      if (ok[u]) xr[u].load(in + static_cast<size_t>(r) * C + c0);
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       // all lanes take part in the shuffles; pad rows just do not store
+      float v[8];
+      if (ok[u]) xr[u].unpack(v);
+      else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = 0.f;
+      }
       float s = 0.f;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) s += v[u][i];
+      for (int i = 0; i < 8; ++i) s += v[i];
 #pragma unroll
       for (int o = LPT / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
       const float mean = s * (1.0f / C);
       float q = 0.f;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) { const float d = v[u][i] - mean; q += d * d; }
+      for (int i = 0; i < 8; ++i) { const float d = v[i] - mean; q += d * d; }
 #pragma unroll
       for (int o = LPT / 2; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
       const float rstd = rsqrtf(q * (1.0f / C) + 1e-5f);
       if (ok[u]) {
         float o8[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) o8[i] = (v[u][i] - mean) * rstd * wv[i] + bv[i];
+        for (int i = 0; i < 8; ++i) o8[i] = (v[i] - mean) * rstd * wv[i] + bv[i];
         store8(out + static_cast<size_t>(r0 + u * TPB) * C + c0, o8);
       }
     }
@@ -399,7 +416,7 @@ attention_kernel(const T* __restrict__ qkv, Geo g, int E, T* __restrict__ out) {
   constexpr int VPT = D / 8;
   for (int idx = threadIdx.x; idx < L * VPT; idx += blockDim.x) {
     const int pix = idx / VPT, dv = (idx % VPT) * 8;
-    const size_t ro = static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * ld + h * D + dv;
+    const size_t ro = static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * ld + h * D + dv;
     load8(qkv + ro + E, Ks + pix * D + dv);
     load8(qkv + ro + 2 * E, Vs + pix * D + dv);
   }
@@ -570,7 +587,7 @@ out_conv_kernel(const T* __restrict__ feat, Geo g, const float* __restrict__ w_o
   float e[kLatC];
 #pragma unroll
   for (int c = 0; c < kLatC; ++c) e[c] = b_out[c];
-  const T* f = feat + static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * 64;
+  const T* f = feat + static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * 64;
 #pragma unroll
   for (int k0 = 0; k0 < 64; k0 += 8) {
     float v[8];
@@ -598,7 +615,7 @@ geom_head_kernel(const T* __restrict__ feat, Geo g, const float* __restrict__ w1
   const int HW = g.H * g.W;
   float s = 0.f;
   for (int pix = grp; pix < HW; pix += 4)
-    s += to_f32(feat[static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * 64 + c]);
+    s += to_f32(feat[static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * 64 + c]);
   part[grp][c] = s;
   __syncthreads();
   if (tid < 64) gmean[tid] = (part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid]) / static_cast<float>(HW);
@@ -656,7 +673,7 @@ gn8_stats_kernel(const T* __restrict__ raw, Geo g, int C, double2* __restrict__ 
   for (int v = begin + tid; v < end; v += 256) {
     const int pix = v / vpr, c0 = (v % vpr) * 8;
     float xv[8];
-    load8(raw + static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * C + c0, xv);
+    load8(raw + static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * C + c0, xv);
 #pragma unroll
     for (int i = 0; i < 8; ++i) { s += xv[i]; ss += xv[i] * xv[i]; }
   }
@@ -704,11 +721,11 @@ gn8_apply_gelu_kernel(const T* __restrict__ raw, const double2* __restrict__ par
     const int pix = v / vpr, vc = v % vpr, c0 = vc * 8;
     const int grp = vc / vpg;
     const float mean = s_mean[grp], rstd = s_rstd[grp];
-    const size_t off = static_cast<size_t>(geo_row(g, b, pix / g.W, pix % g.W)) * C + c0;
+    const size_t off = static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * C + c0;
     float xv[8];
     load8(raw + off, xv);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) xv[i] = gelu_erf((xv[i] - mean) * rstd * gamma[c0 + i] + beta[c0 + i]);
+    for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>((xv[i] - mean) * rstd * gamma[c0 + i] + beta[c0 + i]);
     store8(out + off, xv);
   }
 }
