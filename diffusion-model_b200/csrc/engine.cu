@@ -152,7 +152,8 @@ template <typename T>
 struct GemmW {  // a repacked weight: [ntaps * rows_per_tap, K] K-major, plus its TMA descriptor
   T* w = nullptr;
   int K = 0, N = 0, rows_per_tap = 0, ntaps = 0, bn = 0;
-  CUtensorMap tmap;
+  CUtensorMap tmap;       // box = bn rows
+  CUtensorMap tmap_half;  // box = bn / 2 rows (CTA-pair kernel: each CTA loads half of the tile)
   const float* bias = nullptr;
 };
 
@@ -221,7 +222,10 @@ class Engine : public IEngine {
     DMB_CUDA(cudaGetDeviceProperties(&prop, device));
     if (prop.major != 10) fail(4, "this library is built for sm_100a (B200); found sm_" + std::to_string(prop.major) + std::to_string(prop.minor));
     num_sms_ = prop.multiProcessorCount;
-    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    const char* pe = getenv("DMB200_PAIRS");
+    use_pairs_ = pe ? (pe[0] - '0') : 1;
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
@@ -325,6 +329,7 @@ class Engine : public IEngine {
   long long launches_ = 0;
   bool counting_ = true;
   bool use_tc_attention_ = true;
+  int use_pairs_ = 1;   // cta_group::2 GEMM tiles: DMB200_PAIRS=0 off, 1 when there is enough work, 2 always
 
   Pool wpool_unet_, wpool_vae_;
   std::map<std::string, std::pair<const float*, int64_t>> blob_;  // name -> fp32 device copy
@@ -380,6 +385,7 @@ GemmW<T> Engine<T>::make_conv3x3_from_ptr(const float* w_dev, int Co, int Ci, Po
   repack_conv3x3_kernel<T><<<cdiv(total, 256), 256>>>(w_dev, Co, Ci, g.rows_per_tap, g.w);
   DMB_CHECK_LAUNCH();
   g.tmap = make_tmap<T>(g.w, Ci, static_cast<uint64_t>(9) * g.rows_per_tap, g.bn);
+  g.tmap_half = make_tmap<T>(g.w, Ci, static_cast<uint64_t>(9) * g.rows_per_tap, std::max(8, g.bn / 2));
   return g;
 }
 
@@ -400,6 +406,7 @@ GemmW<T> Engine<T>::make_linear_w(const std::string& wname, const std::string& b
   cast_kernel<T><<<cdiv(static_cast<long long>(N) * K, 256), 256>>>(f(wname), static_cast<long long>(N) * K, g.w);
   DMB_CHECK_LAUNCH();
   g.tmap = make_tmap<T>(g.w, K, g.rows_per_tap, g.bn);
+  g.tmap_half = make_tmap<T>(g.w, K, g.rows_per_tap, std::max(8, g.bn / 2));
   if (!bname.empty()) {
     DMB_REQUIRE(numel(bname) == N, "unexpected size of " + bname);
     g.bias = f(bname);
@@ -419,6 +426,7 @@ GemmW<T> Engine<T>::make_convT_w(const std::string& wname, const std::string& bn
   repack_convT_kernel<T><<<cdiv(16LL * Co * Ci, 256), 256>>>(f(wname), Ci, Co, g.w);
   DMB_CHECK_LAUNCH();
   g.tmap = make_tmap<T>(g.w, Ci, 16ull * Co, g.bn);
+  g.tmap_half = make_tmap<T>(g.w, Ci, 16ull * Co, std::max(8, g.bn / 2));
   if (!bname.empty()) g.bias = f(bname);
   return g;
 }
@@ -580,22 +588,47 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   p.k_chunks = w.K / ElemTraits<T>::kChunkK;
   p.block_n = w.bn;
   p.n_tiles = w.rows_per_tap / w.bn;
-  p.m_tiles = cdiv(a.g.rows_valid, kTileM);
+  {
+    static const char* de = getenv("DMB200_GEMM_DBG");  // timing experiments only (results are garbage)
+    p.dbg = de ? atoi(de) : 0;
+  }
+  // CTA pairs (256-row tiles) when there is enough work to keep every pair busy
+  const int m_tiles1 = cdiv(a.g.rows_valid, kTileM);
+  // (short K loops -- the Linear layers -- are epilogue-bound and lose on the pair's cross-CTA hand-shakes)
+  const bool pair = w.bn >= 32 && ((use_pairs_ == 1 && ntaps * p.k_chunks >= 8 && (m_tiles1 / 2) * p.n_tiles >= num_sms_ / 2) ||
+                                   (use_pairs_ == 2 && m_tiles1 >= 2));
+  const int ctas = pair ? 2 : 1;
+  p.m_tiles = cdiv(a.g.rows_valid, kTileM * ctas);
   p.tma_store = (out_act && ep.epi == EPI_STORE && ep.map_mode == 0 && w.bn % ElemTraits<T>::kChunkK == 0 &&
                  out_act->C % ElemTraits<T>::kChunkK == 0 && out_act->C >= p.n_tiles * w.bn &&
                  out_act->g.rows_alloc == a.g.rows_alloc && ep.out == out_act->p && ep.ldc == out_act->C)
                     ? 1 : 0;
-  const int stage_bytes = kTileM * 128 + w.bn * 128;
+  const int stage_bytes = kTileM * 128 + (w.bn / ctas) * 128;
   const int staging = p.tma_store ? kStagingBytes : 0;
   p.stages = std::min(kMaxStages, (kGemmSmemMax - 1024 - staging) / stage_bytes);
-  p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM, w.bn);
+  p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM * ctas, w.bn);
   p.tmem_cols = tmem_cols_for(w.bn);
   p.geo = a.g;
   p.rows_alloc = a.g.rows_alloc;
   p.n_valid = w.N;
   const int smem = p.stages * stage_bytes + staging + 1024;
-  const int grid = std::min(p.m_tiles * p.n_tiles, num_sms_);
-  gemm_tc_kernel<T><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap, p.tma_store ? out_act->tmap : a.tmap, p);
+  const CUtensorMap& tout = p.tma_store ? out_act->tmap : a.tmap;
+  if (pair) {
+    const int clusters = std::min(p.m_tiles * p.n_tiles, num_sms_ / 2);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * clusters);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2>, a.tmap, w.tmap_half, tout, p));
+  } else {
+    const int grid = std::min(p.m_tiles * p.n_tiles, num_sms_);
+    gemm_tc_kernel<T, 1><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap, tout, p);
+  }
   DMB_CHECK_LAUNCH();
   count();
 }
@@ -1199,6 +1232,7 @@ void Engine<T>::op_linear(const float* x, const float* w, const float* bias, int
   cast_kernel<T><<<cdiv(static_cast<long long>(N) * K, 256), 256>>>(wd, static_cast<long long>(N) * K, gw.w);
   DMB_CHECK_LAUNCH();
   gw.tmap = make_tmap<T>(gw.w, K, gw.rows_per_tap, gw.bn);
+  gw.tmap_half = make_tmap<T>(gw.w, K, gw.rows_per_tap, std::max(8, gw.bn / 2));
   float* bd = nullptr;
   if (bias) {
     bd = pool.alloc_n<float>(gw.rows_per_tap);
@@ -1247,6 +1281,7 @@ void Engine<T>::op_convT4x4(const float* x, const float* w, const float* bias, i
   repack_convT_kernel<T><<<cdiv(16LL * Cout * Cin, 256), 256>>>(wd, Cin, Cout, gw.w);
   DMB_CHECK_LAUNCH();
   gw.tmap = make_tmap<T>(gw.w, Cin, 16ull * Cout, gw.bn);
+  gw.tmap_half = make_tmap<T>(gw.w, Cin, 16ull * Cout, std::max(8, gw.bn / 2));
   float* bd = nullptr;
   if (bias) {
     bd = pool.alloc_n<float>(Cout);

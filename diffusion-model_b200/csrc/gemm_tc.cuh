@@ -56,6 +56,7 @@ struct GemmParams {
   Geo geo_out;
   int up_a, up_b;
   int tma_store;          // 1: epilogue stores through smem + TMA (tmap_out); 0: per-thread stores
+  int dbg;                // timing experiments only: 1 = no MMAs issued, 2 = no TMA loads issued
   float* img_f32;         // EPI_IMAGE: (n, n_valid, H, W) planar fp32, sigmoid applied
   uint8_t* img_u8;        // EPI_IMAGE: same, x255 clamp truncate
 };
@@ -64,7 +65,12 @@ constexpr int kGemmThreads = 384;
 constexpr int kEpiThreads = 256;
 constexpr int kStagingBytes = 2 * kTileM * 128;  // two 128-row x 128-byte sub-tiles
 
-template <typename T>
+// kCtas == 2: launched as clusters of two CTAs (cta_group::2).  The pair owns a 256-row tile:
+// CTA rank r loads rows [m0 + 128 r, +128) of A and rows [n0 + r BLOCK_N/2, +BLOCK_N/2) of the
+// weight tile, keeps its 128 accumulator lanes in its own TMEM and runs its own epilogue;
+// rank 0 issues the M=256 MMAs and multicasts the commits.  Per SM this halves the B
+// operand's shared-memory traffic, which is what bounds the single-CTA kernel.
+template <typename T, int kCtas>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_out, const GemmParams p) {
@@ -85,8 +91,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   // 128B-swizzled operand tiles need 1024-byte alignment.
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  const uint32_t rank = (kCtas == 2) ? cluster_ctarank() : 0u;
+  const int num_cl = gridDim.x / kCtas, cl = blockIdx.x / kCtas;   // tile loop runs per cluster
   const uint32_t a_bytes = kTileM * 128;
-  const uint32_t b_bytes = static_cast<uint32_t>(p.block_n) * 128;
+  const uint32_t b_bytes = static_cast<uint32_t>(p.block_n / kCtas) * 128;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   uint8_t* staging = smem + static_cast<size_t>(p.stages) * stage_bytes;  // 1024-aligned (stage_bytes % 1024 == 0)
 
@@ -102,72 +110,95 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full_bar[a], 1);
-      mbar_init(&tmem_empty_bar[a], kEpiThreads);
+      mbar_init(&tmem_empty_bar[a], kCtas == 2 ? 16 : kEpiThreads);  // pair: one arrive per epilogue warp
     }
     fence_mbar_init();
   }
   if (warp == 2) {
-    tmem_alloc(&tmem_base_smem, p.tmem_cols);
+    if constexpr (kCtas == 2) tmem_alloc_pair(&tmem_base_smem, p.tmem_cols);
+    else tmem_alloc(&tmem_base_smem, p.tmem_cols);
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kCtas == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
 
   const int total_tiles = p.m_tiles * p.n_tiles;
   const int n_iter = p.num_taps * p.k_chunks;
 
+  // The producer and MMA warps run their loops with ALL 32 lanes (warp-uniform control flow
+  // and operands) and elect one lane only around the asynchronous instructions: ptxas then
+  // keeps descriptors, barrier and TMEM addresses in uniform registers instead of wrapping
+  // every UTMALDG / UTCHMMA in an ELECT + R2UR.BROADCAST waterfall (~60 cycles per MMA).
   if (warp == 0) {
     // ------------------------------------------------------------- TMA producer
-    if (lane == 0) {
-      uint32_t it_global = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int n_tile = tile % p.n_tiles;
-        const int m_tile = tile / p.n_tiles;
-        const int m0 = m_tile * kTileM;
-        const int n0 = n_tile * p.block_n;
-        for (int tap = 0; tap < p.num_taps; ++tap) {
-          const int a_row = m0 + p.a_shift[tap];
-          const int b_row = p.b_row[tap] + n0;
-          for (int kc = 0; kc < p.k_chunks; ++kc, ++it_global) {
-            const uint32_t s = it_global % p.stages;
-            const uint32_t ph = (it_global / p.stages) & 1;
-            mbar_wait(&empty_bar[s], ph ^ 1);
-            uint8_t* sa = smem + s * stage_bytes;
-            mbar_expect_tx(&full_bar[s], stage_bytes);
-            tma_load_2d(sa, &tmap_a, &full_bar[s], kc * Tr::kChunkK, a_row);
-            tma_load_2d(sa + a_bytes, &tmap_b, &full_bar[s], kc * Tr::kChunkK, b_row);
+    uint32_t stage = 0, phase = 0;
+    for (int tile = cl; tile < total_tiles; tile += num_cl) {
+      const int n_tile = tile % p.n_tiles;
+      const int m_tile = tile / p.n_tiles;
+      const int m0 = (m_tile * kCtas + static_cast<int>(rank)) * kTileM;
+      const int n0 = n_tile * p.block_n + static_cast<int>(rank) * (p.block_n / kCtas);
+      for (int tap = 0; tap < p.num_taps; ++tap) {
+        const int a_row = m0 + p.a_shift[tap];
+        const int b_row = p.b_row[tap] + n0;
+        for (int kc = 0; kc < p.k_chunks; ++kc) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * stage_bytes;
+          if (elect_one()) {
+            if (p.dbg == 2) {
+              if (rank == 0) mbar_arrive(&full_bar[stage]);
+            } else if constexpr (kCtas == 2) {
+              // both CTAs' bytes are accounted on the leader's barrier
+              const uint32_t lead_bar = mapa_shared(smem_u32(&full_bar[stage]), 0);
+              if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * stage_bytes);
+              tma_load_2d_pair(sa, &tmap_a, lead_bar, kc * Tr::kChunkK, a_row);
+              tma_load_2d_pair(sa + a_bytes, &tmap_b, lead_bar, kc * Tr::kChunkK, b_row);
+            } else {
+              mbar_expect_tx(&full_bar[stage], stage_bytes);
+              tma_load_2d(sa, &tmap_a, &full_bar[stage], kc * Tr::kChunkK, a_row);
+              tma_load_2d(sa + a_bytes, &tmap_b, &full_bar[stage], kc * Tr::kChunkK, b_row);
+            }
           }
+          __syncwarp();
+          if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------- MMA issuer
-    if (lane == 0) {
-      uint32_t it_global = 0;
+    if (rank == 0) {
+      uint32_t stage = 0, phase = 0;
       uint32_t tile_count = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tile_count) {
+      for (int tile = cl; tile < total_tiles; tile += num_cl, ++tile_count) {
         const uint32_t as = tile_count & 1;
         const uint32_t aph = (tile_count >> 1) & 1;
         mbar_wait(&tmem_empty_bar[as], aph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * p.block_n;
-        for (int it = 0; it < n_iter; ++it, ++it_global) {
-          const uint32_t s = it_global % p.stages;
-          const uint32_t ph = (it_global / p.stages) & 1;
-          mbar_wait(&full_bar[s], ph);
+        for (int it = 0; it < n_iter; ++it) {
+          mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + s * stage_bytes);
+          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
           const uint64_t adesc = umma_desc_sw128(sa);
           const uint64_t bdesc = umma_desc_sw128(sa + a_bytes);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            // advance 32 bytes (one MMA K step) inside the 128-byte swizzle row
-            umma_ss<Tr::kTf32>(d_tmem, adesc + (k * 2), bdesc + (k * 2), p.idesc, (it > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < 4; ++k) {
+              if (p.dbg == 1) break;
+              // advance 32 bytes (one MMA K step) inside the 128-byte swizzle row
+              if constexpr (kCtas == 2)
+                umma_ss_pair<Tr::kTf32>(d_tmem, adesc + (k * 2), bdesc + (k * 2), p.idesc, (it > 0 || k > 0) ? 1u : 0u);
+              else
+                umma_ss<Tr::kTf32>(d_tmem, adesc + (k * 2), bdesc + (k * 2), p.idesc, (it > 0 || k > 0) ? 1u : 0u);
+            }
+            if constexpr (kCtas == 2) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
+            if (it == n_iter - 1) {
+              if constexpr (kCtas == 2) umma_commit_pair(&tmem_full_bar[as]); else umma_commit(&tmem_full_bar[as]);
+            }
           }
-          umma_commit(&empty_bar[s]);
+          __syncwarp();
+          if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tmem_full_bar[as]);
       }
     }
   } else if (warp >= 4) {
@@ -180,11 +211,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const T* residual = reinterpret_cast<const T*>(p.residual);
     uint32_t tile_count = 0;
     uint32_t sub_count = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tile_count) {
+    auto release_tmem = [&](uint32_t as) {  // this thread has read all it needs of accumulator `as`
+      tc_fence_before();
+      if constexpr (kCtas == 2) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty_bar[as]), 0));
+      } else {
+        mbar_arrive(&tmem_empty_bar[as]);
+      }
+    };
+    for (int tile = cl; tile < total_tiles; tile += num_cl, ++tile_count) {
       const int n_tile = tile % p.n_tiles;
       const int m_tile = tile / p.n_tiles;
       const int n0 = n_tile * p.block_n;
-      const int m0 = m_tile * kTileM;
+      const int m0 = (m_tile * kCtas + static_cast<int>(rank)) * kTileM;
       const int r = m0 + row_in_tile;
       int b = 0, y = 0, x = 0;
       const bool valid = geo_decode(p.geo, r, b, y, x);
@@ -206,10 +246,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             tmem_ld16(t_row + k * kSubN + h * kHalf, v);
           }
           tmem_ld_wait();
-          if (k == n_sub - 1) {  // accumulator fully read: hand it back to the MMA issuer
-            tc_fence_before();
-            mbar_arrive(&tmem_empty_bar[as]);
-          }
+          if (k == n_sub - 1) release_tmem(as);  // accumulator fully read: hand it back to the MMA issuer
           const int col0 = n0 + k * kSubN + h * kHalf;
           if (valid) {
             if (p.bias) {
@@ -289,8 +326,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
           }
         }
-        tc_fence_before();
-        mbar_arrive(&tmem_empty_bar[as]);
+        release_tmem(as);
       } else {
         int out_r = r;
         if (p.map_mode == 1 && valid) out_r = geo_row(p.geo_out, b, 2 * y + p.up_a, 2 * x + p.up_b);
@@ -342,8 +378,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
           }
         }
-        tc_fence_before();
-        mbar_arrive(&tmem_empty_bar[as]);
+        release_tmem(as);
       }
       if (p.rowstats) {
         // the two column halves of a row meet in shared memory; fixed order -> deterministic
@@ -360,10 +395,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kCtas == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, p.tmem_cols);
+    if constexpr (kCtas == 2) tmem_dealloc_pair(tmem_base, p.tmem_cols);
+    else tmem_dealloc(tmem_base, p.tmem_cols);
   }
 }
 

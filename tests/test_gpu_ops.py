@@ -28,7 +28,8 @@ def _check(name, got, ref, rel_tol=4e-3):
 
 @pytest.mark.parametrize("rows,K,N,act,use_bias", [
     (300, 64, 64, 0, True), (1000, 128, 384, 0, True), (130, 256, 256, 1, True),
-    (128, 64, 192, 0, False), (5, 64, 64, 1, True), (4097, 256, 768, 0, True), (257, 512, 128, 0, True)])
+    (128, 64, 192, 0, False), (5, 64, 64, 1, True), (4097, 256, 768, 0, True), (257, 512, 128, 0, True),
+    (40000, 64, 192, 0, True), (30000, 128, 128, 1, True)])  # the last two are large enough for CTA-pair tiles
 def test_linear(ctx, rows, K, N, act, use_bias):
     g = torch.Generator().manual_seed(rows + K + N)
     x = bf16_round(torch.randn((rows, K), generator=g))
@@ -44,7 +45,8 @@ def test_linear(ctx, rows, K, N, act, use_bias):
 
 @pytest.mark.parametrize("B,Cin,Cout,H,W", [
     (2, 64, 64, 28, 28), (3, 128, 128, 14, 14), (2, 256, 512, 3, 3), (1, 512, 256, 7, 7),
-    (2, 64, 3, 12, 12), (1, 64, 128, 1, 1), (5, 128, 64, 7, 5), (16, 256, 256, 14, 14)])
+    (2, 64, 3, 12, 12), (1, 64, 128, 1, 1), (5, 128, 64, 7, 5), (16, 256, 256, 14, 14),
+    (64, 128, 128, 28, 28), (96, 64, 256, 14, 14), (40, 128, 64, 28, 28)])  # large: CTA-pair (cta_group::2) tiles
 def test_conv3x3(ctx, B, Cin, Cout, H, W):
     g = torch.Generator().manual_seed(B * 1000 + Cin + Cout + H)
     x = bf16_round(torch.randn((B, Cin, H, W), generator=g))
