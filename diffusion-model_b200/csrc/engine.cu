@@ -222,8 +222,12 @@ class Engine : public IEngine {
     DMB_CUDA(cudaGetDeviceProperties(&prop, device));
     if (prop.major != 10) fail(4, "this library is built for sm_100a (B200); found sm_" + std::to_string(prop.major) + std::to_string(prop.minor));
     num_sms_ = prop.multiProcessorCount;
-    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
-    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     const char* pe = getenv("DMB200_PAIRS");
     use_pairs_ = pe ? (pe[0] - '0') : 1;
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
@@ -588,10 +592,6 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   p.k_chunks = w.K / ElemTraits<T>::kChunkK;
   p.block_n = w.bn;
   p.n_tiles = w.rows_per_tap / w.bn;
-  {
-    static const char* de = getenv("DMB200_GEMM_DBG");  // timing experiments only (results are garbage)
-    p.dbg = de ? atoi(de) : 0;
-  }
   // CTA pairs (256-row tiles) when there is enough work to keep every pair busy
   const int m_tiles1 = cdiv(a.g.rows_valid, kTileM);
   // (short K loops -- the Linear layers -- are epilogue-bound and lose on the pair's cross-CTA hand-shakes)
@@ -603,9 +603,25 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
                  out_act->C % ElemTraits<T>::kChunkK == 0 && out_act->C >= p.n_tiles * w.bn &&
                  out_act->g.rows_alloc == a.g.rows_alloc && ep.out == out_act->p && ep.ldc == out_act->C)
                     ? 1 : 0;
-  const int stage_bytes = kTileM * 128 + (w.bn / ctas) * 128;
+  const int pair_bytes = kTileM * 128 + (w.bn / ctas) * 128;   // one (tap, K chunk) operand pair
   const int staging = p.tma_store ? kStagingBytes : 0;
-  p.stages = std::min(kMaxStages, (kGemmSmemMax - 1024 - staging) / stage_bytes);
+  const int ring = kGemmSmemMax - 1024 - staging;
+  // One barrier hand-shake costs the issuing threads ~500 cycles (measured): group enough
+  // operand pairs per stage that their MMAs (4 x bn/2 cycles per pair) cover it, while
+  // keeping at least 3 stages in flight.
+  const int n_iter = ntaps * p.k_chunks;
+  int group = std::max(1, std::min(std::min(n_iter, kMaxGroup), cdiv(256, w.bn)));
+  if (group == 3) group = 2;
+  while (group > 1 && ring / (group * pair_bytes) < 3) group >>= 1;
+  {
+    static const char* ge = getenv("DMB200_GEMM_GROUP");  // experiment override
+    if (ge) group = std::max(1, std::min(std::min(n_iter, kMaxGroup), atoi(ge)));
+    if (group == 3) group = 2;
+    while (group > 1 && ring / (group * pair_bytes) < 2) group >>= 1;
+  }
+  p.group = group;
+  const int stage_bytes = group * pair_bytes;
+  p.stages = std::min(kMaxStages, ring / stage_bytes);
   p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM * ctas, w.bn);
   p.tmem_cols = tmem_cols_for(w.bn);
   p.geo = a.g;
@@ -624,10 +640,14 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2>, a.tmap, w.tmap_half, tout, p));
+    if (group == 1) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1>, a.tmap, w.tmap_half, tout, p));
+    else if (group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2>, a.tmap, w.tmap_half, tout, p));
+    else DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 4>, a.tmap, w.tmap_half, tout, p));
   } else {
     const int grid = std::min(p.m_tiles * p.n_tiles, num_sms_);
-    gemm_tc_kernel<T, 1><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap, tout, p);
+    if (group == 1) gemm_tc_kernel<T, 1, 1><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap, tout, p);
+    else if (group == 2) gemm_tc_kernel<T, 1, 2><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap, tout, p);
+    else gemm_tc_kernel<T, 1, 4><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap, tout, p);
   }
   DMB_CHECK_LAUNCH();
   count();

@@ -30,6 +30,7 @@ namespace dmb {
 constexpr int kMaxTaps = 9;
 constexpr int kTileM = 128;
 constexpr int kMaxStages = 8;
+constexpr int kMaxGroup = 4;   // (tap, K chunk) operand pairs per pipeline stage
 
 enum EpiMode : int { EPI_STORE = 0, EPI_IMAGE = 1 };
 
@@ -39,6 +40,8 @@ struct GemmParams {
   int b_row[kMaxTaps];    // first row of the tap's [Cout, Cin] block in the weight matrix
   int k_chunks;           // Cin / chunkK
   int m_tiles, n_tiles, block_n, stages;
+  int group;              // (tap, K chunk) operand pairs per pipeline stage: one barrier hand-shake
+                          // (~500 cycles of issue-thread time) must cover >= that much MMA time
   uint32_t idesc;
   uint32_t tmem_cols;
 
@@ -56,7 +59,6 @@ struct GemmParams {
   Geo geo_out;
   int up_a, up_b;
   int tma_store;          // 1: epilogue stores through smem + TMA (tmap_out); 0: per-thread stores
-  int dbg;                // timing experiments only: 1 = no MMAs issued, 2 = no TMA loads issued
   float* img_f32;         // EPI_IMAGE: (n, n_valid, H, W) planar fp32, sigmoid applied
   uint8_t* img_u8;        // EPI_IMAGE: same, x255 clamp truncate
 };
@@ -70,7 +72,7 @@ constexpr int kStagingBytes = 2 * kTileM * 128;  // two 128-row x 128-byte sub-t
 // weight tile, keeps its 128 accumulator lanes in its own TMEM and runs its own epilogue;
 // rank 0 issues the M=256 MMAs and multicasts the commits.  Per SM this halves the B
 // operand's shared-memory traffic, which is what bounds the single-CTA kernel.
-template <typename T, int kCtas>
+template <typename T, int kCtas, int kGroup>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_out, const GemmParams p) {
@@ -95,7 +97,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const int num_cl = gridDim.x / kCtas, cl = blockIdx.x / kCtas;   // tile loop runs per cluster
   const uint32_t a_bytes = kTileM * 128;
   const uint32_t b_bytes = static_cast<uint32_t>(p.block_n / kCtas) * 128;
-  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t pair_bytes = a_bytes + b_bytes;                       // one (tap, K chunk) operand pair
+  const uint32_t stage_bytes = static_cast<uint32_t>(kGroup) * pair_bytes;
   uint8_t* staging = smem + static_cast<size_t>(p.stages) * stage_bytes;  // 1024-aligned (stage_bytes % 1024 == 0)
 
   if (warp == 0 && lane == 0) {
@@ -133,35 +136,50 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   if (warp == 0) {
     // ------------------------------------------------------------- TMA producer
     uint32_t stage = 0, phase = 0;
+    const uint32_t lead_full0 = (kCtas == 2) ? mapa_shared(smem_u32(&full_bar[0]), 0) : 0u;
     for (int tile = cl; tile < total_tiles; tile += num_cl) {
       const int n_tile = tile % p.n_tiles;
       const int m_tile = tile / p.n_tiles;
       const int m0 = (m_tile * kCtas + static_cast<int>(rank)) * kTileM;
       const int n0 = n_tile * p.block_n + static_cast<int>(rank) * (p.block_n / kCtas);
-      for (int tap = 0; tap < p.num_taps; ++tap) {
-        const int a_row = m0 + p.a_shift[tap];
-        const int b_row = p.b_row[tap] + n0;
-        for (int kc = 0; kc < p.k_chunks; ++kc) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * stage_bytes;
-          if (elect_one()) {
-            if (p.dbg == 2) {
-              if (rank == 0) mbar_arrive(&full_bar[stage]);
-            } else if constexpr (kCtas == 2) {
-              // both CTAs' bytes are accounted on the leader's barrier
-              const uint32_t lead_bar = mapa_shared(smem_u32(&full_bar[stage]), 0);
-              if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * stage_bytes);
-              tma_load_2d_pair(sa, &tmap_a, lead_bar, kc * Tr::kChunkK, a_row);
-              tma_load_2d_pair(sa + a_bytes, &tmap_b, lead_bar, kc * Tr::kChunkK, b_row);
-            } else {
-              mbar_expect_tx(&full_bar[stage], stage_bytes);
-              tma_load_2d(sa, &tmap_a, &full_bar[stage], kc * Tr::kChunkK, a_row);
-              tma_load_2d(sa + a_bytes, &tmap_b, &full_bar[stage], kc * Tr::kChunkK, b_row);
+      // (tap, K chunk) pairs are walked in order; the per-tap row offsets are looked up when
+      // the tap changes, i.e. long before the next barrier wake-up needs them
+      int tap = 0, kc = 0;
+      int a_cur = m0 + p.a_shift[0], b_cur = p.b_row[0] + n0;
+      for (int it0 = 0; it0 < n_iter; it0 += kGroup) {
+        int a_row[kGroup], b_row[kGroup], k_col[kGroup];
+#pragma unroll
+        for (int gi = 0; gi < kGroup; ++gi) {
+          a_row[gi] = a_cur; b_row[gi] = b_cur; k_col[gi] = kc * Tr::kChunkK;
+          if (it0 + gi < n_iter && ++kc == p.k_chunks) {
+            kc = 0;
+            ++tap;
+            if (tap < p.num_taps) { a_cur = m0 + p.a_shift[tap]; b_cur = p.b_row[tap] + n0; }
+          }
+        }
+        const int cnt = min(kGroup, n_iter - it0);
+        uint8_t* sa = smem + stage * stage_bytes;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one()) {
+          if (kCtas == 1 || rank == 0) mbar_expect_tx(&full_bar[stage], static_cast<uint32_t>(cnt) * pair_bytes * kCtas);
+#pragma unroll
+          for (int gi = 0; gi < kGroup; ++gi) {
+            if (gi < cnt) {
+              uint8_t* sp = sa + gi * pair_bytes;
+              if constexpr (kCtas == 2) {
+                // both CTAs' bytes are accounted on the leader's barrier
+                const uint32_t lead_bar = lead_full0 + stage * 8;
+                tma_load_2d_pair(sp, &tmap_a, lead_bar, k_col[gi], a_row[gi]);
+                tma_load_2d_pair(sp + a_bytes, &tmap_b, lead_bar, k_col[gi], b_row[gi]);
+              } else {
+                tma_load_2d(sp, &tmap_a, &full_bar[stage], k_col[gi], a_row[gi]);
+                tma_load_2d(sp + a_bytes, &tmap_b, &full_bar[stage], k_col[gi], b_row[gi]);
+              }
             }
           }
-          __syncwarp();
-          if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -175,24 +193,32 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         mbar_wait(&tmem_empty_bar[as], aph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * p.block_n;
-        for (int it = 0; it < n_iter; ++it) {
+        for (int it0 = 0; it0 < n_iter; it0 += kGroup) {
+          const int cnt = min(kGroup, n_iter - it0);
+          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+          const uint64_t adesc0 = umma_desc_sw128(sa);
+          const uint64_t bdesc0 = umma_desc_sw128(sa + a_bytes);
+          const uint64_t pstep = static_cast<uint64_t>(pair_bytes >> 4);   // start-address field is in 16-byte units
+          const bool last = it0 + cnt >= n_iter;
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
-          const uint64_t adesc = umma_desc_sw128(sa);
-          const uint64_t bdesc = umma_desc_sw128(sa + a_bytes);
           if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              if (p.dbg == 1) break;
-              // advance 32 bytes (one MMA K step) inside the 128-byte swizzle row
-              if constexpr (kCtas == 2)
-                umma_ss_pair<Tr::kTf32>(d_tmem, adesc + (k * 2), bdesc + (k * 2), p.idesc, (it > 0 || k > 0) ? 1u : 0u);
-              else
-                umma_ss<Tr::kTf32>(d_tmem, adesc + (k * 2), bdesc + (k * 2), p.idesc, (it > 0 || k > 0) ? 1u : 0u);
+            for (int gi = 0; gi < kGroup; ++gi) {
+              if (gi < cnt) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  // advance 32 bytes (one MMA K step) inside the 128-byte swizzle row
+                  const uint32_t acc = (it0 + gi > 0 || k > 0) ? 1u : 0u;
+                  if constexpr (kCtas == 2)
+                    umma_ss_pair<Tr::kTf32>(d_tmem, adesc0 + gi * pstep + (k * 2), bdesc0 + gi * pstep + (k * 2), p.idesc, acc);
+                  else
+                    umma_ss<Tr::kTf32>(d_tmem, adesc0 + gi * pstep + (k * 2), bdesc0 + gi * pstep + (k * 2), p.idesc, acc);
+                }
+              }
             }
             if constexpr (kCtas == 2) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
-            if (it == n_iter - 1) {
+            if (last) {
               if constexpr (kCtas == 2) umma_commit_pair(&tmem_full_bar[as]); else umma_commit(&tmem_full_bar[as]);
             }
           }
