@@ -78,14 +78,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                const __grid_constant__ CUtensorMap tmap_out, const GemmParams p) {
   using Tr = ElemTraits<T>;
   constexpr int kSubN = Tr::kChunkK;   // columns per 128-byte sub-tile (64 bf16 / 32 fp32)
-  constexpr int kHalf = kSubN / 2;     // columns one epilogue warp takes of a sub-tile
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_smem;
-  __shared__ float2 stat_part[kTileM];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -113,7 +111,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full_bar[a], 1);
-      mbar_init(&tmem_empty_bar[a], kCtas == 2 ? 16 : kEpiThreads);  // pair: one arrive per epilogue warp
+      mbar_init(&tmem_empty_bar[a], 4 * kCtas);  // one arrive per warp of the epilogue group (of each CTA)
     }
     fence_mbar_init();
   }
@@ -229,24 +227,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
   } else if (warp >= 4) {
     // ------------------------------------------------------------- epilogue
-    const int q = warp & 3;          // TMEM lane quadrant this warp may read
-    const int h = (warp - 4) >> 2;   // which half of the columns this warp takes
+    // Two independent warpgroups: group g drains accumulator stage g (every other tile), with
+    // its own staging buffer, named barrier and TMA-store thread, so the latency chains of
+    // two tiles (TMEM load -> math -> smem -> TMA store) overlap.
+    const int q = warp & 3;            // TMEM lane quadrant this warp may read
+    const int wg = (warp - 4) >> 2;    // epilogue warpgroup = accumulator stage it serves
     const int row_in_tile = q * 32 + lane;
-    const bool store_thread = threadIdx.x == 128;
+    const bool store_thread = (threadIdx.x & 127) == 0;
+    const int bar_id = 1 + wg;
     T* out = reinterpret_cast<T*>(p.out);
     const T* residual = reinterpret_cast<const T*>(p.residual);
-    uint32_t tile_count = 0;
-    uint32_t sub_count = 0;
-    auto release_tmem = [&](uint32_t as) {  // this thread has read all it needs of accumulator `as`
+    uint8_t* buf = staging + wg * (kTileM * 128);
+    const uint32_t as = static_cast<uint32_t>(wg);
+    auto release_tmem = [&]() {  // this warp has read all it needs of accumulator `as`
       tc_fence_before();
-      if constexpr (kCtas == 2) {
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty_bar[as]), 0));
-      } else {
-        mbar_arrive(&tmem_empty_bar[as]);
+      __syncwarp();
+      if (lane == 0) {
+        if constexpr (kCtas == 2) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty_bar[as]), 0));
+        else mbar_arrive(&tmem_empty_bar[as]);
       }
     };
+    uint32_t tile_count = 0;
     for (int tile = cl; tile < total_tiles; tile += num_cl, ++tile_count) {
+      if ((tile_count & 1) != as) continue;
       const int n_tile = tile % p.n_tiles;
       const int m_tile = tile / p.n_tiles;
       const int n0 = n_tile * p.block_n;
@@ -255,7 +258,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       int b = 0, y = 0, x = 0;
       const bool valid = geo_decode(p.geo, r, b, y, x);
 
-      const uint32_t as = tile_count & 1;
       const uint32_t aph = (tile_count >> 1) & 1;
       mbar_wait(&tmem_full_bar[as], aph);
       tc_fence_after();
@@ -265,98 +267,98 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       if (p.tma_store) {
         const int n_sub = p.block_n / kSubN;
         for (int k = 0; k < n_sub; ++k) {
-          float v[32];
-          if constexpr (kHalf == 32) {
-            tmem_ld32(t_row + k * kSubN + h * kHalf, v);
-          } else {
-            tmem_ld16(t_row + k * kSubN + h * kHalf, v);
-          }
+          float v[kSubN];
+          tmem_ld32(t_row + k * kSubN, v);
+          if constexpr (kSubN == 64) tmem_ld32(t_row + k * kSubN + 32, v + 32);
           tmem_ld_wait();
-          if (k == n_sub - 1) release_tmem(as);  // accumulator fully read: hand it back to the MMA issuer
-          const int col0 = n0 + k * kSubN + h * kHalf;
+          if (k == n_sub - 1) release_tmem();  // accumulator fully read: hand it back to the MMA issuer
+          const int col0 = n0 + k * kSubN;
           if (valid) {
             if (p.bias) {
 #pragma unroll
-              for (int j = 0; j < kHalf; j += 4) {
+              for (int j = 0; j < kSubN; j += 4) {
                 const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
                 v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
               }
             }
             if (p.act == 1) {
 #pragma unroll
-              for (int j = 0; j < kHalf; ++j) v[j] = gelu_for<T>(v[j]);
+              for (int j = 0; j < kSubN; ++j) v[j] = gelu_for<T>(v[j]);
             }
             if (residual) {
               const T* rp = residual + static_cast<size_t>(r) * p.ldc + col0;
+              Raw8<T> rr[kSubN / 8];
 #pragma unroll
-              for (int j = 0; j < kHalf; j += 8) {
+              for (int j = 0; j < kSubN / 8; ++j) rr[j].load(rp + 8 * j);
+#pragma unroll
+              for (int j = 0; j < kSubN / 8; ++j) {
                 float rv[8];
-                load8(rp + j, rv);
+                rr[j].unpack(rv);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) v[j + i] += rv[i];
+                for (int i = 0; i < 8; ++i) v[8 * j + i] += rv[i];
               }
             }
+            if (p.rowstats) {
+              float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
-            for (int j = 0; j < kHalf; ++j) {
-              sum += v[j];
-              sumsq += v[j] * v[j];
+              for (int j = 0; j < kSubN; j += 2) {
+                s0 += v[j]; q0 = fmaf(v[j], v[j], q0);
+                s1 += v[j + 1]; q1 = fmaf(v[j + 1], v[j + 1], q1);
+              }
+              sum += s0 + s1; sumsq += q0 + q1;
             }
           } else {
 #pragma unroll
-            for (int j = 0; j < kHalf; ++j) v[j] = 0.f;  // pad pixels stay zero
+            for (int j = 0; j < kSubN; ++j) v[j] = 0.f;  // pad pixels stay zero
           }
-          uint8_t* buf = staging + (sub_count & 1) * (kTileM * 128);
-          if (store_thread) tma_store_wait_read<1>();  // the store that used this buffer two sub-tiles ago
-          named_bar_sync(1, kEpiThreads);
+          if (store_thread) tma_store_wait_read<0>();  // the previous store of this group has read the buffer
+          named_bar_sync(bar_id, 128);
           {
             uint8_t* rowp = buf + row_in_tile * 128;
             const int sw = row_in_tile & 7;
             if constexpr (sizeof(T) == 2) {
 #pragma unroll
-              for (int c = 0; c < 4; ++c) {
+              for (int c = 0; c < 8; ++c) {
                 uint4 u;
                 __nv_bfloat162* hp = reinterpret_cast<__nv_bfloat162*>(&u);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) hp[i] = __floats2bfloat162_rn(v[c * 8 + 2 * i], v[c * 8 + 2 * i + 1]);
-                *reinterpret_cast<uint4*>(rowp + (((h * 4 + c) ^ sw) << 4)) = u;
+                *reinterpret_cast<uint4*>(rowp + ((c ^ sw) << 4)) = u;
               }
             } else {
 #pragma unroll
-              for (int c = 0; c < 4; ++c) {
-                *reinterpret_cast<float4*>(rowp + (((h * 4 + c) ^ sw) << 4)) =
+              for (int c = 0; c < 8; ++c) {
+                *reinterpret_cast<float4*>(rowp + ((c ^ sw) << 4)) =
                     make_float4(v[c * 4], v[c * 4 + 1], v[c * 4 + 2], v[c * 4 + 3]);
               }
             }
           }
           fence_async_proxy();
-          named_bar_sync(1, kEpiThreads);
+          named_bar_sync(bar_id, 128);
           if (store_thread) {
             tma_store_2d(&tmap_out, buf, n0 + k * kSubN, m0);
             tma_store_commit();
           }
-          ++sub_count;
         }
       } else if (p.epi == EPI_IMAGE) {
-        if (h == 0) {
-          float v[16];
-          tmem_ld16(t_row, v);
-          tmem_ld_wait();
-          if (valid) {
-            const size_t plane = static_cast<size_t>(p.geo.H) * p.geo.W;
-            for (int c = 0; c < p.n_valid; ++c) {
-              float s = v[c] + (p.bias ? __ldg(p.bias + c) : 0.f);
-              s = 1.0f / (1.0f + expf(-s));
-              const size_t o = (static_cast<size_t>(b) * p.n_valid + c) * plane + static_cast<size_t>(y) * p.geo.W + x;
-              if (p.img_f32) p.img_f32[o] = s;
-              if (p.img_u8) p.img_u8[o] = static_cast<uint8_t>(fminf(fmaxf(s * 255.0f, 0.f), 255.f));
-            }
+        float v[16];
+        tmem_ld16(t_row, v);
+        tmem_ld_wait();
+        release_tmem();
+        if (valid) {
+          const size_t plane = static_cast<size_t>(p.geo.H) * p.geo.W;
+          for (int c = 0; c < p.n_valid; ++c) {
+            float s = v[c] + (p.bias ? __ldg(p.bias + c) : 0.f);
+            s = 1.0f / (1.0f + expf(-s));
+            const size_t o = (static_cast<size_t>(b) * p.n_valid + c) * plane + static_cast<size_t>(y) * p.geo.W + x;
+            if (p.img_f32) p.img_f32[o] = s;
+            if (p.img_u8) p.img_u8[o] = static_cast<uint8_t>(fminf(fmaxf(s * 255.0f, 0.f), 255.f));
           }
         }
-        release_tmem(as);
       } else {
         int out_r = r;
         if (p.map_mode == 1 && valid) out_r = geo_row(p.geo_out, b, 2 * y + p.up_a, 2 * x + p.up_b);
-        for (int c0 = h * 32; c0 < p.block_n; c0 += 64) {
+        for (int c0 = 0; c0 < p.block_n; c0 += 32) {
           float v[32];
           if (p.block_n - c0 >= 32) {
             tmem_ld32(t_row + c0, v);
@@ -404,18 +406,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
           }
         }
-        release_tmem(as);
+        release_tmem();
       }
-      if (p.rowstats) {
-        // the two column halves of a row meet in shared memory; fixed order -> deterministic
-        if (h == 1) stat_part[row_in_tile] = make_float2(sum, sumsq);
-        named_bar_sync(1, kEpiThreads);
-        if (h == 0 && valid) {
-          const float2 o = stat_part[row_in_tile];
-          p.rowstats[static_cast<size_t>(n_tile) * p.rows_alloc + r] = make_float2(sum + o.x, sumsq + o.y);
-        }
-        named_bar_sync(1, kEpiThreads);
-      }
+      if (p.rowstats && valid) p.rowstats[static_cast<size_t>(n_tile) * p.rows_alloc + r] = make_float2(sum, sumsq);
     }
     if (store_thread) tma_store_wait_all<0>();
   }
