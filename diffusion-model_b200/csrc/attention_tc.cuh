@@ -1,20 +1,24 @@
 // Fused attention core on tcgen05: softmax(Q K^T / sqrt(D)) V.
 // models/unet_cond.py:36, 49 (nn.MultiheadAttention, 4 heads, batch_first).
 //
-// One CTA (128 threads) owns one (sample, head) and a range of 128-query blocks.  The head's
+// One CTA (320 threads) owns one (sample, head) and a range of 128-query blocks.  The head's
 // K and V^T are staged ONCE in shared memory in the UMMA "no-swizzle, K-major" canonical
 // layout (8-row x 16-byte core matrices; LBO = 128 B between core matrices along K, SBO
-// between 8-row groups), written by the CTA's own threads; each query block then stages Q.
-// Scores S = Q K_j^T for 64-key blocks go to TMEM (fp32, lane = query); the 128 threads read
-// their own row with tcgen05.ld, so the softmax needs no shuffles.  ONE pass with an online
-// softmax: a running row maximum that is only raised when a block exceeds it by more than
-// 2^8 (then O, which lives in TMEM, is rescaled by the warp with tcgen05.ld / .st); P =
-// exp2(..) goes to shared memory as bf16 and O += P V_j accumulates in TMEM.
-// Pipeline: S is double-buffered in TMEM (S_{j+2} is issued as soon as S_j has been read) and
-// P is double-buffered in shared memory (P V_j runs while P_{j+1} is produced), so the
-// tensor-pipe latency is hidden behind the exp work, which is what bounds this kernel
-// (MUFU / issue bound, not tensor bound: d_head is 16..64).
-// 192 TMEM columns (256 allocated) and <= 90 KB shared memory: two CTAs per SM.
+// between 8-row groups), written by the CTA's own threads.
+// Two independent CHAINS run in the CTA; each is one softmax warpgroup (4 warps, thread =
+// query row) plus its own MMA-issuing warp, and works through every second query block:
+//   MMA warp : S_j = Q K_j^T (64 keys) -> TMEM;  O += P_j V_j and R += P_j 1 -> TMEM
+//   softmax  : tcgen05.ld of the own row of S_j (no shuffles) -> release S -> online max with
+//              lazy rescale of O/R in TMEM (only when a block exceeds the running maximum by
+//              more than 2^8) -> P = exp2(..) as bf16 into shared memory -> signal the MMA warp
+// All hand-offs are mbarriers (s_bar, sfree_bar, p_bar, pv_bar); there is no CTA-wide barrier
+// in the key loop and no softmax thread ever issues an MMA.  S_{j+1} is issued as soon as S_j
+// has been read, so one S buffer per chain is enough.  The row sum comes from the tensor core
+// too (R = P x ones), from exactly the bf16 P that enters P V; P is rounded by truncation (a
+// byte permute per pair instead of an F2FP per pair, which shares the MUFU pipe) and the
+// truncation bias cancels in O / R.
+// The kernel is bound by MUFU.EX2 (one per score): two CTAs per SM give 4 softmax warps per
+// scheduler to keep that pipe fed.  TMEM: 2 x (64 + D + 16) columns.
 #pragma once
 
 #include "common.cuh"
@@ -37,21 +41,43 @@ __device__ __forceinline__ uint64_t umma_desc_noswz(uint32_t smem_addr, uint32_t
   return d;
 }
 
-inline size_t attention_tc_smem_bytes(int L, int D) {
-  const int lpad = (L + kAttnK - 1) / kAttnK * kAttnK;
-  return static_cast<size_t>(kAttnQ) * D * 2 + 2ull * lpad * D * 2 + 2ull * kAttnQ * kAttnK * 2 + 128;
+// exp2 on the FMA pipe for a share of the scores (the MUFU pipe bounds this kernel): round to
+// the nearest integer with the 1.5 * 2^23 trick, cubic minimax polynomial for 2^f on
+// [-0.5, 0.5] (relative error 7.5e-5, below the bf16 rounding of P), exponent added as an integer.
+#ifndef DMB_ATTN_POLY_MASK
+#define DMB_ATTN_POLY_MASK 3   // scores with (i & 3) == MASK take the FMA-pipe exp2; -1 disables
+#endif
+constexpr bool kPolyExp = DMB_ATTN_POLY_MASK >= 0;
+__device__ __forceinline__ float ex2_poly(float x) {
+  x = fmaxf(x, -120.0f);
+  const float t = x + 12582912.0f;
+  const float f = x - (t - 12582912.0f);
+  float p = fmaf(f, 0.05517145f, 0.24261062f);
+  p = fmaf(p, f, 0.69326097f);
+  p = fmaf(p, f, 0.9999281f);
+  return __uint_as_float(__float_as_uint(p) + (__float_as_uint(t) << 23));
 }
 
+
+inline size_t attention_tc_smem_bytes(int L, int D) {
+  const int lpad = (L + kAttnK - 1) / kAttnK * kAttnK;
+  return 2ull * kAttnQ * D * 2 + 2ull * lpad * D * 2 + 2ull * kAttnQ * kAttnK * 2 + 16 * kAttnK * 2 + 128;
+}
+
+constexpr int kAttnThreads = 320;   // 2 chains x (4 softmax warps + 1 MMA warp)
+
 template <int D>
-__global__ void __launch_bounds__(128, 2)
+__global__ void __launch_bounds__(kAttnThreads, 2)
 attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bfloat16* __restrict__ out,
                     int qblocks_per_cta) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t s_bar[2];    // S buffer b holds fresh scores
-  __shared__ __align__(8) uint64_t pv_bar[2];   // the P V MMA that read P buffer b has retired
+  __shared__ __align__(8) uint64_t s_bar[2];      // chain c: S holds fresh scores        (MMA -> softmax)
+  __shared__ __align__(8) uint64_t sfree_bar[2];  // chain c: S has been read             (softmax -> MMA)
+  __shared__ __align__(8) uint64_t p_bar[2];      // chain c: P is in shared memory       (softmax -> MMA)
+  __shared__ __align__(8) uint64_t pv_bar[2];     // chain c: the P V MMA has retired     (MMA -> softmax)
   __shared__ uint32_t tmem_base_smem;
 
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int L = g.H * g.W;
   const int nkb = (L + kAttnK - 1) / kAttnK;
   const int lpad = nkb * kAttnK;
@@ -60,34 +86,50 @@ attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bf
   const int qb_begin = blockIdx.x * qblocks_per_cta;
   const int qb_end = min(nqb, qb_begin + qblocks_per_cta);
   const int ld = 3 * E;
+  constexpr uint32_t kQBytes = kAttnQ * D * 2;
+  constexpr uint32_t kPBytes = kAttnQ * kAttnK * 2;
+  constexpr uint32_t kChainCols = kAttnK + D + 16;   // TMEM per chain: S | O | R
+  // d_head 64 (7x7 maps: a single query block) runs one chain, so that 256 columns and two
+  // CTAs per SM are enough there as well
+  constexpr int kChains = 2 * kChainCols <= 256 ? 2 : 1;
+  constexpr uint32_t kTmemCols = 256;
+  static_assert(kChains * kChainCols <= kTmemCols, "TMEM budget");
 
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((128u - (raw & 127u)) & 127u);
-  uint8_t* Qs = smem;
-  uint8_t* Ks = Qs + kAttnQ * D * 2;
+  uint8_t* Qs = smem;                                        // one Q tile per chain
+  uint8_t* Ks = Qs + 2 * kQBytes;
   uint8_t* Vt = Ks + static_cast<size_t>(lpad) * D * 2;
-  uint8_t* Ps = Vt + static_cast<size_t>(lpad) * D * 2;   // two buffers of kAttnQ x kAttnK bf16
+  uint8_t* Ps = Vt + static_cast<size_t>(lpad) * D * 2;      // one P tile per chain
+  uint8_t* Ones = Ps + 2 * kPBytes;                          // B operand [16 x kAttnK]: row 0 = 1, rest 0
 
   if (tid == 0) {
-    mbar_init(&s_bar[0], 1);
-    mbar_init(&s_bar[1], 1);
-    mbar_init(&pv_bar[0], 1);
-    mbar_init(&pv_bar[1], 1);
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      mbar_init(&s_bar[c], 1);
+      mbar_init(&sfree_bar[c], 4);
+      mbar_init(&p_bar[c], 4);
+      mbar_init(&pv_bar[c], 1);
+    }
     fence_mbar_init();
   }
-  if (warp == 0) tmem_alloc(&tmem_base_smem, 256);
+  if (warp == 8) tmem_alloc(&tmem_base_smem, kTmemCols);
+  for (int i = tid; i < 16 * kAttnK; i += kAttnThreads) {
+    const int n = i / kAttnK, k = i % kAttnK;
+    *reinterpret_cast<__nv_bfloat16*>(Ones + cm_off(n, k, kAttnK)) = __float2bfloat16_rn(n == 0 ? 1.0f : 0.0f);
+  }
 
   // ---- stage K and V^T of the head (once per CTA); 4 keys in flight per thread
   {
     const uint4 zero = make_uint4(0, 0, 0, 0);
     constexpr int VPK = D / 8;  // 16-byte vectors per key
     const int total = lpad * VPK;
-    for (int i0 = tid; i0 < total; i0 += 128 * 4) {
+    for (int i0 = tid; i0 < total; i0 += kAttnThreads * 4) {
       uint4 kv[4], vv[4];
       int key[4], c[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const int idx = i0 + u * 128;
+        const int idx = i0 + u * kAttnThreads;
         c[u] = idx / lpad;
         key[u] = idx - c[u] * lpad;
         kv[u] = zero; vv[u] = zero;
@@ -100,7 +142,7 @@ attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bf
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        if (i0 + u * 128 < total) {
+        if (i0 + u * kAttnThreads < total) {
           *reinterpret_cast<uint4*>(Ks + cm_off(key[u], 8 * c[u], D)) = kv[u];
           const __nv_bfloat16* ve = reinterpret_cast<const __nv_bfloat16*>(&vv[u]);
 #pragma unroll
@@ -110,177 +152,216 @@ attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bf
       }
     }
   }
+  fence_async_proxy();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_base_smem;
 
-  const uint32_t q_addr = smem_u32(Qs), k_addr = smem_u32(Ks), v_addr = smem_u32(Vt), p_addr = smem_u32(Ps);
   const uint32_t sbo_qk = (D / 8) * 128, sbo_v = (lpad / 8) * 128, sbo_p = (kAttnK / 8) * 128;
-  const uint32_t idesc_s = umma_idesc(1, kAttnQ, kAttnK);
-  const uint32_t idesc_o = umma_idesc(1, kAttnQ, D);
   const float c2 = rsqrtf(static_cast<float>(D)) * 1.4426950408889634f;  // 1/sqrt(D) * log2(e)
-  constexpr uint32_t kColO = 2 * kAttnK;                                   // TMEM: S0 | S1 | O
-  constexpr uint32_t kPBytes = kAttnQ * kAttnK * 2;
 
-  uint32_t gi = 0;       // key blocks processed so far by this CTA (drives buffer / phase choice)
-  uint32_t tmem = 0, t_lane = 0;
-
-  for (int qb = qb_begin; qb < qb_end; ++qb) {
-    // ---- stage this block's queries
-    const int qi = qb * kAttnQ + tid;
-    const bool q_valid = qi < L;
-    const int qrow = q_valid ? geo_row_of_pixel(g, b, qi) : 0;
-    {
-      const uint4 zero = make_uint4(0, 0, 0, 0);
-      const __nv_bfloat16* qp = qkv + static_cast<size_t>(qrow) * ld + h * D;
-#pragma unroll
-      for (int c = 0; c < D / 8; ++c) {
-        const uint4 v = q_valid ? *reinterpret_cast<const uint4*>(qp + 8 * c) : zero;
-        *reinterpret_cast<uint4*>(Qs + cm_off(tid, 8 * c, D)) = v;
-      }
-    }
-    fence_async_proxy();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
-    tc_fence_before();
-    __syncthreads();      // also: every thread has finished reading O of the previous block
-    tc_fence_after();
-    tmem = tmem_base_smem;
-    t_lane = tmem + (static_cast<uint32_t>(warp * 32) << 16);
-
-    auto issue_scores = [&](int j, uint32_t buf) {  // S_j = Q K_j^T -> TMEM columns [buf*64, buf*64+64)
-#pragma unroll
-      for (int kk = 0; kk < D / 16; ++kk) {
-        const uint64_t ad = umma_desc_noswz(q_addr + kk * 256, sbo_qk);
-        const uint64_t bd = umma_desc_noswz(k_addr + j * (kAttnK / 8) * sbo_qk + kk * 256, sbo_qk);
-        umma_ss<false>(tmem + buf * kAttnK, ad, bd, idesc_s, kk > 0 ? 1u : 0u);
-      }
-      umma_commit(&s_bar[buf]);
-    };
-    if (tid == 0) {
-      issue_scores(0, gi & 1);
-      if (nkb > 1) issue_scores(1, (gi + 1) & 1);
-    }
-
-    float m_run = -INFINITY, rowsum = 0.f;
-    for (int j = 0; j < nkb; ++j) {
-      const uint32_t G = gi + j;
-      const uint32_t buf = G & 1, ph = (G >> 1) & 1;
-      mbar_wait(&s_bar[buf], ph);
-      __syncwarp();
+  if (warp >= 8) {
+    // =================== MMA warp of chain c (warp-uniform; one elected lane issues) ===================
+    const int c = warp - 8;
+    const uint32_t q_addr = smem_u32(Qs) + c * kQBytes, k_addr = smem_u32(Ks), v_addr = smem_u32(Vt);
+    const uint32_t p_addr = smem_u32(Ps) + c * kPBytes, ones_addr = smem_u32(Ones);
+    const uint32_t idesc_s = umma_idesc(1, kAttnQ, kAttnK);
+    const uint32_t idesc_o = umma_idesc(1, kAttnQ, D);
+    const uint32_t idesc_r = umma_idesc(1, kAttnQ, 16);
+    const uint32_t col_s = tmem + c * kChainCols, col_o = col_s + kAttnK, col_r = col_o + D;
+    uint32_t G = 0;
+    for (int qb = qb_begin + c; qb < qb_end && c < kChains; qb += kChains) {
+      named_bar_sync(1 + c, 160);   // Q of this block is staged; O / S of the previous one are read
       tc_fence_after();
-      float s[kAttnK];
-      tmem_ld32(t_lane + buf * kAttnK, s);
-      tmem_ld32(t_lane + buf * kAttnK + 32, s + 32);
-      tmem_ld_wait();
-      const int kbase = j * kAttnK;
-      if (kbase + kAttnK > L) {
+      if (elect_one()) {
 #pragma unroll
-        for (int i = 0; i < kAttnK; ++i)
-          if (kbase + i >= L) s[i] = -INFINITY;
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_ss<false>(col_s, umma_desc_noswz(q_addr + kk * 256, sbo_qk),
+                         umma_desc_noswz(k_addr + kk * 256, sbo_qk), idesc_s, kk > 0 ? 1u : 0u);
+        umma_commit(&s_bar[c]);
       }
-      float bm;
-      {  // four independent chains: a serial max over 64 values would expose 64 x 4 cycles
-        float m0 = s[0], m1 = s[1], m2 = s[2], m3 = s[3];
+      __syncwarp();
+      for (int j = 0; j < nkb; ++j, ++G) {
+        mbar_wait(&sfree_bar[c], G & 1);
+        tc_fence_after();
+        if (j + 1 < nkb && elect_one()) {
 #pragma unroll
-        for (int i = 4; i < kAttnK; i += 4) {
-          m0 = fmaxf(m0, s[i]); m1 = fmaxf(m1, s[i + 1]); m2 = fmaxf(m2, s[i + 2]); m3 = fmaxf(m3, s[i + 3]);
+          for (int kk = 0; kk < D / 16; ++kk)
+            umma_ss<false>(col_s, umma_desc_noswz(q_addr + kk * 256, sbo_qk),
+                           umma_desc_noswz(k_addr + (j + 1) * (kAttnK / 8) * sbo_qk + kk * 256, sbo_qk), idesc_s,
+                           kk > 0 ? 1u : 0u);
+          umma_commit(&s_bar[c]);
         }
-        bm = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
-      }
-      if (j == 0) {
-        m_run = bm;
-      } else {
-        const bool need = (bm - m_run) * c2 > 8.0f;
-        if (__any_sync(0xffffffffu, need)) {
-          // raise the running maximum: O (TMEM) and the row sum are rescaled.  All P V MMAs
-          // issued so far must have retired before O is touched.
-          const uint32_t Gp = G - 1;
-          mbar_wait(&pv_bar[Gp & 1], (Gp >> 1) & 1);
-          __syncwarp();
-          tc_fence_after();
-          const float m_new = need ? bm : m_run;
-          const float f = ex2_approx((m_run - m_new) * c2);
-          rowsum *= f;
-          m_run = m_new;
+        __syncwarp();
+        mbar_wait(&p_bar[c], G & 1);
+        tc_fence_after();
+        if (elect_one()) {
 #pragma unroll
-          for (int c0 = 0; c0 < D; c0 += 16) {
-            float o[16];
-            tmem_ld16(t_lane + kColO + c0, o);
-            tmem_ld_wait();
+          for (int kk = 0; kk < kAttnK / 16; ++kk)
+            umma_ss<false>(col_o, umma_desc_noswz(p_addr + kk * 256, sbo_p),
+                           umma_desc_noswz(v_addr + (j * (kAttnK / 8) + kk * 2) * 128, sbo_v), idesc_o,
+                           (j > 0 || kk > 0) ? 1u : 0u);
 #pragma unroll
-            for (int i = 0; i < 16; ++i) o[i] *= f;
-            tmem_st16(t_lane + kColO + c0, o);
-          }
-          tmem_st_wait();
+          for (int kk = 0; kk < kAttnK / 16; ++kk)
+            umma_ss<false>(col_r, umma_desc_noswz(p_addr + kk * 256, sbo_p),
+                           umma_desc_noswz(ones_addr + kk * 256, sbo_p), idesc_r, (j > 0 || kk > 0) ? 1u : 0u);
+          umma_commit(&pv_bar[c]);
         }
-      }
-      const float mc = m_run * c2;
-      {
-        float r0 = 0.f, r1 = 0.f, r2 = 0.f, r3 = 0.f;
-#pragma unroll
-        for (int i = 0; i < kAttnK; i += 4) {
-          s[i] = ex2_approx(fmaf(s[i], c2, -mc));   // exp2(-inf) = 0 for masked keys
-          s[i + 1] = ex2_approx(fmaf(s[i + 1], c2, -mc));
-          s[i + 2] = ex2_approx(fmaf(s[i + 2], c2, -mc));
-          s[i + 3] = ex2_approx(fmaf(s[i + 3], c2, -mc));
-          r0 += s[i]; r1 += s[i + 1]; r2 += s[i + 2]; r3 += s[i + 3];
-        }
-        rowsum += (r0 + r1) + (r2 + r3);
-      }
-      // P buffer `buf` was last read by the P V MMA of block G-2
-      if (G >= 2) {
-        mbar_wait(&pv_bar[buf], ph ^ 1);
         __syncwarp();
       }
-      uint8_t* Pb = Ps + buf * kPBytes;
+    }
+  } else {
+    // =================== softmax warpgroup of chain c: thread = query row ===================
+    const int c = warp >> 2;
+    const int row = tid & 127;
+    uint8_t* Qc = Qs + c * kQBytes;
+    uint8_t* Pc = Ps + c * kPBytes;
+    const uint32_t t_lane = tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16) + c * kChainCols;
+    constexpr uint32_t kColO = kAttnK;
+    uint32_t G = 0;
+    for (int qb = qb_begin + c; qb < qb_end && c < kChains; qb += kChains) {
+      const int qi = qb * kAttnQ + row;
+      const bool q_valid = qi < L;
+      const int qrow = q_valid ? geo_row_of_pixel(g, b, qi) : 0;
+      {
+        const uint4 zero = make_uint4(0, 0, 0, 0);
+        const __nv_bfloat16* qp = qkv + static_cast<size_t>(qrow) * ld + h * D;
 #pragma unroll
-      for (int gq = 0; gq < kAttnK / 8; ++gq) {
-        uint4 u;
-        __nv_bfloat162* hp = reinterpret_cast<__nv_bfloat162*>(&u);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) hp[i] = __floats2bfloat162_rn(s[gq * 8 + 2 * i], s[gq * 8 + 2 * i + 1]);
-        *reinterpret_cast<uint4*>(Pb + cm_off(tid, gq * 8, kAttnK)) = u;
+        for (int cc = 0; cc < D / 8; ++cc) {
+          const uint4 v = q_valid ? *reinterpret_cast<const uint4*>(qp + 8 * cc) : zero;
+          *reinterpret_cast<uint4*>(Qc + cm_off(row, 8 * cc, D)) = v;
+        }
       }
       fence_async_proxy();
       tc_fence_before();
-      __syncthreads();
-      if (tid == 0) {
+      named_bar_sync(1 + c, 160);
+
+      if (qb * kAttnQ + (row & ~31) >= L) {
+        // every query row of this warp is padding (tail block): keep the hand-shakes in step
+        // and skip the arithmetic.  The P rows stay whatever they were; their O rows are never read.
+        for (int j = 0; j < nkb; ++j, ++G) {
+          mbar_wait(&s_bar[c], G & 1);
+          if (lane == 0) mbar_arrive(&sfree_bar[c]);
+          // S_G can be ready before the other warps have delivered P_{G-1}: an arrival now would
+          // be counted in that earlier phase
+          mbar_wait(&p_bar[c], (G - 1) & 1);
+          if (lane == 0) mbar_arrive(&p_bar[c]);
+          __syncwarp();
+        }
+        continue;
+      }
+
+      float m_run = -INFINITY;
+      for (int j = 0; j < nkb; ++j, ++G) {
+        mbar_wait(&s_bar[c], G & 1);
         tc_fence_after();
+        float s[kAttnK];
+        tmem_ld32(t_lane, s);
+        tmem_ld32(t_lane + 32, s + 32);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sfree_bar[c]);   // the MMA warp may overwrite S with the next block
+        const int kbase = j * kAttnK;
+        if (kbase + kAttnK > L) {
 #pragma unroll
-        for (int kk = 0; kk < kAttnK / 16; ++kk) {
-          const uint64_t ad = umma_desc_noswz(p_addr + buf * kPBytes + kk * 256, sbo_p);
-          const uint64_t bd = umma_desc_noswz(v_addr + (j * (kAttnK / 8) + kk * 2) * 128, sbo_v);
-          umma_ss<false>(tmem + kColO, ad, bd, idesc_o, (j > 0 || kk > 0) ? 1u : 0u);
+          for (int i = 0; i < kAttnK; ++i)
+            if (kbase + i >= L) s[i] = -INFINITY;
         }
-        umma_commit(&pv_bar[buf]);
-        if (j + 2 < nkb) issue_scores(j + 2, buf);
+        float bm;
+        {  // four independent chains: a serial max over 64 values would expose 64 x 4 cycles
+          float m0 = s[0], m1 = s[1], m2 = s[2], m3 = s[3];
+#pragma unroll
+          for (int i = 4; i < kAttnK; i += 4) {
+            m0 = fmaxf(m0, s[i]); m1 = fmaxf(m1, s[i + 1]); m2 = fmaxf(m2, s[i + 2]); m3 = fmaxf(m3, s[i + 3]);
+          }
+          bm = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+        }
+        bool pv_done = (j == 0);   // O / R / P of this chain are not in use by the tensor core
+        if (j == 0) {
+          m_run = bm;
+        } else {
+          const bool need = (bm - m_run) * c2 > 8.0f;
+          if (__any_sync(0xffffffffu, need)) {
+            // raise the running maximum: O and R (TMEM) are rescaled once the P V MMAs issued
+            // so far have retired
+            mbar_wait(&pv_bar[c], (G - 1) & 1);
+            tc_fence_after();
+            pv_done = true;
+            const float m_new = need ? bm : m_run;
+            const float f = ex2_approx((m_run - m_new) * c2);
+            m_run = m_new;
+#pragma unroll
+            for (int c0 = 0; c0 < D + 16; c0 += 16) {
+              float o[16];
+              tmem_ld16(t_lane + kColO + c0, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 16; ++i) o[i] *= f;
+              tmem_st16(t_lane + kColO + c0, o);
+            }
+            tmem_st_wait();
+          }
+        }
+        const float mc = m_run * c2;
+        const int nval = L - kbase;   // valid keys of this block; whole groups of 16 padding keys cost nothing
+#pragma unroll
+        for (int g16 = 0; g16 < kAttnK / 16; ++g16) {
+          if (g16 * 16 < nval) {
+#pragma unroll
+            for (int i = g16 * 16; i < g16 * 16 + 16; ++i) {
+              const float x = fmaf(s[i], c2, -mc);
+              s[i] = (kPolyExp && (DMB_ATTN_POLY_MASK >= 4 ? (i & 1) == 1 : (i & 3) == DMB_ATTN_POLY_MASK)) ? ex2_poly(x) : ex2_approx(x);   // exp2(-inf) = 0 for masked keys
+            }
+          } else {
+#pragma unroll
+            for (int i = g16 * 16; i < g16 * 16 + 16; ++i) s[i] = 0.f;
+          }
+        }
+        if (!pv_done) mbar_wait(&pv_bar[c], (G - 1) & 1);   // P was last read by the P V MMA of block G-1
+#pragma unroll
+        for (int gq = 0; gq < kAttnK / 8; ++gq) {
+          uint4 u;
+          u.x = __byte_perm(__float_as_uint(s[gq * 8 + 0]), __float_as_uint(s[gq * 8 + 1]), 0x7632);
+          u.y = __byte_perm(__float_as_uint(s[gq * 8 + 2]), __float_as_uint(s[gq * 8 + 3]), 0x7632);
+          u.z = __byte_perm(__float_as_uint(s[gq * 8 + 4]), __float_as_uint(s[gq * 8 + 5]), 0x7632);
+          u.w = __byte_perm(__float_as_uint(s[gq * 8 + 6]), __float_as_uint(s[gq * 8 + 7]), 0x7632);
+          *reinterpret_cast<uint4*>(Pc + cm_off(row, gq * 8, kAttnK)) = u;
+        }
+        fence_async_proxy();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_bar[c]);
+      }
+      // ---- epilogue of the query block: O / R -> out
+      if (nkb > 0) {
+        mbar_wait(&pv_bar[c], (G - 1) & 1);
+        tc_fence_after();
+        float o[D + 16];
+#pragma unroll
+        for (int c0 = 0; c0 < D + 16; c0 += 16) tmem_ld16(t_lane + kColO + c0, o + c0);
+        tmem_ld_wait();
+        tc_fence_before();
+        if (q_valid) {
+          const float inv = 1.0f / o[D];   // column 0 of R = sum of the row's P
+          __nv_bfloat16* op = out + static_cast<size_t>(qrow) * E + h * D;
+#pragma unroll
+          for (int c0 = 0; c0 < D; c0 += 8) {
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = o[c0 + i] * inv;
+            store8(op + c0, v);
+          }
+        }
       }
     }
-    // ---- epilogue of the query block: O / rowsum -> out
-    {
-      const uint32_t Gl = gi + nkb - 1;
-      mbar_wait(&pv_bar[Gl & 1], (Gl >> 1) & 1);
-      __syncwarp();
-      tc_fence_after();
-      float o[D];
-#pragma unroll
-      for (int c0 = 0; c0 < D; c0 += 16) tmem_ld16(t_lane + kColO + c0, o + c0);
-      tmem_ld_wait();
-      if (q_valid) {
-        const float inv = 1.0f / rowsum;
-        __nv_bfloat16* op = out + static_cast<size_t>(qrow) * E + h * D;
-#pragma unroll
-        for (int c0 = 0; c0 < D; c0 += 8) {
-          float v[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = o[c0 + i] * inv;
-          store8(op + c0, v);
-        }
-      }
-    }
-    gi += nkb;
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) {
+  if (warp == 8) {
     tc_fence_after();
-    tmem_dealloc(tmem_base_smem, 256);
+    tmem_dealloc(tmem, kTmemCols);
   }
 }
 

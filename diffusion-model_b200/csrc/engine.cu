@@ -715,20 +715,23 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     });
   }
 
-  auto gn = [&](const Act<T>& raw, const std::string& gname, int mode, const Act<T>* residual, int emb_off) {
-    Act<T> out = new_act(pool, raw.g.n, raw.g.H, raw.g.W, raw.C, false);
+  auto gn = [&](const Act<T>& raw, const std::string& gname, int mode, const Act<T>* residual, int emb_off,
+                int n_out = 0) {
+    if (n_out == 0) n_out = raw.g.n;
+    Act<T> out = new_act(pool, n_out, raw.g.H, raw.g.W, raw.C, false);
     const float* gamma = f(gname + ".weight");
     const float* beta = f(gname + ".bias");
     const T* res = residual ? residual->p : nullptr;
     const float* embproj = P.embproj;
     const int total_vec = raw.g.H * raw.g.W * raw.C / 8;
     // enough CTAs to fill the chip at small batch, whole samples per CTA at large batch
-    const int want = (8 * num_sms_ + raw.g.n - 1) / raw.g.n;
+    const int want = (8 * num_sms_ + n_out - 1) / n_out;
     const int splits = std::max(1, std::min(std::min(want, 16), total_vec / 512));
-    ops.tag("gn1_apply", 0, static_cast<double>(raw.g.n) * total_vec * 8 * sizeof(T) * (residual ? 3 : 2));
+    ops.tag("gn1_apply " + std::to_string(raw.C) + " @" + std::to_string(raw.g.H) + " m" + std::to_string(mode), 0,
+            static_cast<double>(n_out) * total_vec * 8 * sizeof(T) * (residual ? 3 : 2));
     ops.push_back([this, raw, out, gamma, beta, mode, res, embproj, emb_off, splits](cudaStream_t s) {
-      const dim3 grid(splits, raw.g.n);
-#define DMB_GN_ARGS raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc, gamma, beta, res, embproj, emb_off, raw.g, raw.C, out.p
+      const dim3 grid(splits, out.g.n);
+#define DMB_GN_ARGS raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc, gamma, beta, res, embproj, emb_off, out.g, raw.C, out.p, raw.g.n
       if (mode == GN_GELU) gn1_apply_kernel<T, GN_GELU><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
       else if (mode == GN_RES_GELU) gn1_apply_kernel<T, GN_RES_GELU><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
       else if (mode == GN_ADD_EMB) gn1_apply_kernel<T, GN_ADD_EMB><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
@@ -748,11 +751,12 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     return out;
   };
   // ResBlock (models/unet_cond.py:10-30); last_mode is what follows the second GroupNorm.
-  auto resblock = [&](const Act<T>& in, const std::string& p, bool residual, int last_mode, int emb_off) {
+  auto resblock = [&](const Act<T>& in, const std::string& p, bool residual, int last_mode, int emb_off,
+                      int n_out = 0) {
     Act<T> r1 = conv(in, p + ".double_conv.0.weight");
     Act<T> h = gn(r1, p + ".double_conv.1", GN_GELU, nullptr, 0);
     Act<T> r2 = conv(h, p + ".double_conv.3.weight");
-    return gn(r2, p + ".double_conv.4", residual ? GN_RES_GELU : last_mode, residual ? &in : nullptr, emb_off);
+    return gn(r2, p + ".double_conv.4", residual ? GN_RES_GELU : last_mode, residual ? &in : nullptr, emb_off, n_out);
   };
   auto attention = [&](const Act<T>& x, const std::string& p) {
     const int C = x.C, H = x.g.H, W = x.g.W, nn = x.g.n;
@@ -786,17 +790,18 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.push_back([this, qkv, av, C](cudaStream_t s) {
       const int L = qkv.g.H * qkv.g.W, D = C / 4;
       if constexpr (std::is_same<T, __nv_bfloat16>::value) {
-        if (use_tc_attention_) {
+        if (use_tc_attention_ && L > 16) {   // tiny maps (3x3): a 128-row MMA tile would be > 90 % padding
           // whole (sample, head) per CTA when there are enough of them to fill the chip twice
           // over; otherwise the query blocks are spread over more CTAs
           const int nqb = cdiv(L, kAttnQ);
-          const int qsplit = std::max(1, std::min(nqb, cdiv(4 * num_sms_, 4 * qkv.g.n)));
+          // (d_head 16 / 32 run two chains per CTA: at least two query blocks each)
+          const int qsplit = std::max(1, std::min(D <= 32 ? cdiv(nqb, 2) : nqb, cdiv(4 * num_sms_, 4 * qkv.g.n)));
           const int qpc = cdiv(nqb, qsplit);
           const dim3 grid(cdiv(nqb, qpc), 4, qkv.g.n);
           const size_t smem = attention_tc_smem_bytes(L, D);
-          if (D == 16) attention_tc_kernel<16><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
-          else if (D == 32) attention_tc_kernel<32><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
-          else attention_tc_kernel<64><<<grid, 128, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
+          if (D == 16) attention_tc_kernel<16><<<grid, kAttnThreads, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
+          else if (D == 32) attention_tc_kernel<32><<<grid, kAttnThreads, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
+          else attention_tc_kernel<64><<<grid, kAttnThreads, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
           DMB_CHECK_LAUNCH();
           count();
           return;
@@ -823,7 +828,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.push_back(op_lin(f1, gw_.at(p + ".ff2"), out, 0, &o));
     return out;
   };
-  auto down = [&](const Act<T>& x, const std::string& p, int emb_off) {
+  auto down = [&](const Act<T>& x, const std::string& p, int emb_off, int n_out = 0) {
     Act<T> pooled = new_act(pool, x.g.n, x.g.H / 2, x.g.W / 2, x.C, false);
     ops.tag("maxpool", 0, 1.25 * pooled.g.n * x.g.H * x.g.W * x.C * sizeof(T));
     ops.push_back([this, x, pooled](cudaStream_t s) {
@@ -833,14 +838,14 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       count();
     });
     Act<T> a = resblock(pooled, p + ".maxpool_conv.1", true, GN_NONE, 0);
-    return resblock(a, p + ".maxpool_conv.2", false, GN_ADD_EMB, emb_off);
+    return resblock(a, p + ".maxpool_conv.2", false, GN_ADD_EMB, emb_off, n_out);
   };
   auto up = [&](const Act<T>& x, const Act<T>& skip, const std::string& p, int emb_off) {
-    Act<T> cat = new_act(pool, skip.g.n, skip.g.H, skip.g.W, skip.C + x.C, false);
+    Act<T> cat = new_act(pool, x.g.n, skip.g.H, skip.g.W, skip.C + x.C, false);
     ops.tag("upcat", 0, 2.0 * cat.g.n * cat.g.H * cat.g.W * cat.C * sizeof(T));
     ops.push_back([this, x, skip, cat](cudaStream_t s) {
       const long long total = static_cast<long long>(cat.g.n) * cat.g.H * cat.g.W * (cat.C / 8);
-      upcat_kernel<T><<<cdiv(total, 256), 256, 0, s>>>(skip.p, skip.C, x.p, x.g, x.C, cat.g, cat.p);
+      upcat_kernel<T><<<cdiv(total, 256), 256, 0, s>>>(skip.p, skip.C, skip.g.n, x.p, x.g, x.C, cat.g, cat.p);
       DMB_CHECK_LAUNCH();
       count();
     });
@@ -848,15 +853,25 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     return resblock(a, p + ".conv.1", false, GN_ADD_EMB, emb_off);
   };
 
+  // Classifier-free guidance runs the conditional and the unconditional sample of a pair
+  // through the same weights from the same x_t; they differ only through the embedding, which
+  // first enters at the end of down1 (unet_cond.py:71-74: x = maxpool_conv(x); x + emb).  inc and
+  // down1's convolutions are therefore evaluated ONCE per pair (n0 = B samples) and fan out to
+  // 2B at down1's embedding add; up3 reads the shared inc output as its skip tensor.
+  const int n0 = B;
   // inc: the 4->64 conv runs on CUDA cores straight from the fp32 latent.
-  Act<T> r0 = new_act(pool, n, kLatH, kLatW, 64, true, 1);
+  Act<T> r0 = new_act(pool, n0, kLatH, kLatW, 64, true, 1);
   {
     const float* w0 = f("inc.double_conv.0.weight");
     Plan<T>* pp = &P;
-    ops.tag("conv_in 4->64 @28", 2.0 * n * kLatH * kLatW * 36.0 * 64);
+    ops.tag("conv_in 4->64 @28", 2.0 * n0 * kLatH * kLatW * 36.0 * 64);
     ops.push_back([this, r0, w0, pp, B](cudaStream_t s) {
-      conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), r0.g.n, 1), 128, 0, s>>>(pp->x_state, B, w0, nullptr, 1.0f,
-                                                                                  r0.g, 64, r0.p, r0.stats);
+      if constexpr (std::is_same<T, __nv_bfloat16>::value)
+        conv_in_mma_kernel<<<dim3(r0.g.n, 1), kConvInThreads, 0, s>>>(pp->x_state, B, w0, nullptr, 1.0f, r0.g, 64,
+                                                                      r0.p, r0.stats);
+      else
+        conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), r0.g.n, 1), 128, 0, s>>>(pp->x_state, B, w0, nullptr, 1.0f,
+                                                                                    r0.g, 64, r0.p, r0.stats);
       DMB_CHECK_LAUNCH();
       count();
     });
@@ -865,7 +880,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   Act<T> r1 = conv(h0, "inc.double_conv.3.weight");
   Act<T> x1 = gn(r1, "inc.double_conv.4", GN_NONE, nullptr, 0);
   P.taps["inc"] = x1;
-  Act<T> x2 = down(x1, "down1", 0);       P.taps["down1"] = x2;
+  Act<T> x2 = down(x1, "down1", 0, n);    P.taps["down1"] = x2;
   x2 = attention(x2, "sa1");              P.taps["sa1"] = x2;
   Act<T> x3 = down(x2, "down2", 128);     P.taps["down2"] = x3;
   x3 = attention(x3, "sa2");              P.taps["sa2"] = x3;
@@ -1123,8 +1138,11 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
     const float* b0 = f("vae.dec.0.bias");
     ops.tag("vae conv_in 4->256 @28", 2.0 * n * kLatH * kLatW * 36.0 * 256);
     ops.push_back([this, r0, w0, b0, pp, n](cudaStream_t s) {
-      conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), n, 4), 128, 0, s>>>(pp->z, n, w0, b0, 0.18215f, r0.g, 256,
-                                                                             r0.p, nullptr);
+      if constexpr (std::is_same<T, __nv_bfloat16>::value)
+        conv_in_mma_kernel<<<dim3(n, 4), kConvInThreads, 0, s>>>(pp->z, n, w0, b0, 0.18215f, r0.g, 256, r0.p, nullptr);
+      else
+        conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), n, 4), 128, 0, s>>>(pp->z, n, w0, b0, 0.18215f, r0.g, 256,
+                                                                               r0.p, nullptr);
       DMB_CHECK_LAUNCH();
       count();
     });

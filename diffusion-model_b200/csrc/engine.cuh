@@ -14,7 +14,6 @@
 
 namespace dmb {
 
-constexpr int kLatH = 28, kLatW = 28;
 
 struct TensorRef {  // a named fp32 tensor handed over the ABI (host or device memory)
   const void* ptr;

@@ -13,6 +13,7 @@ constexpr int kEmbDim = 256;
 constexpr int kCondDim = 12;
 constexpr int kProjCols = 896;  // 128 + 256 + 256 + 128 + 64 + 64 emb_layer outputs
 constexpr int kLatC = 4;
+constexpr int kLatH = 28, kLatW = 28;   // latent map (diff.py:9, img_size 28)
 
 // ---------------------------------------------------------------------------
 // Embedding: pos_encoding(t) + class_emb[y] + cond_mlp([vals|mask]) and the six
@@ -132,6 +133,125 @@ conv_in_kernel(const float* __restrict__ x, int B_src, const float* __restrict__
 }
 
 // ---------------------------------------------------------------------------
+// The same convolution for the bf16 mode, on the warp-level tensor-core path (mma.sync
+// m16n8k16, bf16 in / fp32 accumulate): K = 4 channels x 9 taps = 36, padded to 48, is far too
+// short for a tcgen05 pipeline, and the CUDA-core version above is bound by FFMA issue (15
+// TFLOP/s).  One CTA = one sample x 64 output channels: the zero-bordered 4 x 30 x 30 latent and
+// the weights sit in shared memory, every thread keeps its B fragments (48 registers) for the
+// whole image, and each warp walks 16-pixel tiles, gathering the im2col A fragments straight
+// from the staged latent.  Row statistics for the following GroupNorm are reduced in the quad.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ void mma_bf16_16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+constexpr int kConvInThreads = 256;
+static __global__ void __launch_bounds__(kConvInThreads)
+conv_in_mma_kernel(const float* __restrict__ x, int B_src, const float* __restrict__ w_oihw,
+                   const float* __restrict__ bias, float in_div, Geo g, int cout,
+                   __nv_bfloat16* __restrict__ out, float2* __restrict__ rowstats) {
+  constexpr int PW = kLatW + 2, PH = kLatH + 2, PLANE = PW * PH;   // zero-bordered latent plane
+  __shared__ float img[kLatC * PLANE];
+  __shared__ float ws[64 * 36];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int be = blockIdx.x, co0 = blockIdx.y * 64;
+  const float inv_div = 1.0f / in_div;
+  const float* xs = x + static_cast<size_t>(be % B_src) * kLatC * kLatH * kLatW;
+  for (int i = tid; i < kLatC * PLANE; i += kConvInThreads) {
+    const int ci = i / PLANE, rem = i - ci * PLANE, py = rem / PW, px = rem - py * PW;
+    float v = 0.f;
+    if (py >= 1 && py <= kLatH && px >= 1 && px <= kLatW) v = xs[(ci * kLatH + py - 1) * kLatW + px - 1] * inv_div;
+    img[i] = v;
+  }
+  for (int i = tid; i < 64 * 36; i += kConvInThreads) ws[i] = w_oihw[static_cast<size_t>(co0) * 36 + i];
+  __syncthreads();
+
+  const int gq = lane >> 2, tq = lane & 3;
+  // this thread's K indices: kstep ks -> k = ks*16 + 2*tq + {0, 1, 8, 9}; k = ci*9 + ky*3 + kx
+  int koff[3][4];
+  uint32_t bfrag[8][3][2];
+#pragma unroll
+  for (int ks = 0; ks < 3; ++ks) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = ks * 16 + 2 * tq + (e & 1) + (e >> 1) * 8;
+      const int ci = k / 9, ky = (k - ci * 9) / 3, kx = k - ci * 9 - ky * 3;
+      koff[ks][e] = k < 36 ? ci * PLANE + ky * PW + kx : 0;
+    }
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      float wv[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int k = ks * 16 + 2 * tq + (e & 1) + (e >> 1) * 8;
+        wv[e] = k < 36 ? ws[(nt * 8 + gq) * 36 + k] : 0.f;
+      }
+      bfrag[nt][ks][0] = pack_bf16x2(wv[0], wv[1]);
+      bfrag[nt][ks][1] = pack_bf16x2(wv[2], wv[3]);
+    }
+  }
+  float bv[8][2];
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+    bv[nt][0] = bias ? bias[co0 + nt * 8 + 2 * tq] : 0.f;
+    bv[nt][1] = bias ? bias[co0 + nt * 8 + 2 * tq + 1] : 0.f;
+  }
+
+  constexpr int NPIX = kLatH * kLatW;
+  for (int mt = warp; mt * 16 < NPIX; mt += kConvInThreads / 32) {
+    const int p0 = mt * 16 + gq, p1 = p0 + 8;
+    const bool v0 = p0 < NPIX, v1 = p1 < NPIX;
+    const int y0 = v0 ? p0 / kLatW : 0, x0 = v0 ? p0 - y0 * kLatW : 0;
+    const int y1 = v1 ? p1 / kLatW : 0, x1 = v1 ? p1 - y1 * kLatW : 0;
+    const float* i0 = img + y0 * PW + x0;   // top-left of the 3x3 window in the bordered plane
+    const float* i1 = img + y1 * PW + x1;
+    float acc[8][4];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) { acc[nt][0] = bv[nt][0]; acc[nt][1] = bv[nt][1]; acc[nt][2] = bv[nt][0]; acc[nt][3] = bv[nt][1]; }
+#pragma unroll
+    for (int ks = 0; ks < 3; ++ks) {
+      uint32_t a[4];
+      a[0] = pack_bf16x2(i0[koff[ks][0]], i0[koff[ks][1]]);
+      a[1] = pack_bf16x2(i1[koff[ks][0]], i1[koff[ks][1]]);
+      a[2] = pack_bf16x2(i0[koff[ks][2]], i0[koff[ks][3]]);
+      a[3] = pack_bf16x2(i1[koff[ks][2]], i1[koff[ks][3]]);
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) mma_bf16_16816(acc[nt], a, bfrag[nt][ks][0], bfrag[nt][ks][1]);
+    }
+    // rows p0 (acc[.][0..1]) and p1 (acc[.][2..3]); channels co0 + nt*8 + 2*tq + {0, 1}
+    float s0 = 0.f, q0 = 0.f, s1 = 0.f, q1 = 0.f;
+    const int r0 = geo_row(g, be, y0, x0), r1 = geo_row(g, be, y1, x1);
+    __nv_bfloat16* o0 = out + static_cast<size_t>(r0) * cout + co0 + 2 * tq;
+    __nv_bfloat16* o1 = out + static_cast<size_t>(r1) * cout + co0 + 2 * tq;
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      s0 += acc[nt][0] + acc[nt][1]; q0 = fmaf(acc[nt][0], acc[nt][0], fmaf(acc[nt][1], acc[nt][1], q0));
+      s1 += acc[nt][2] + acc[nt][3]; q1 = fmaf(acc[nt][2], acc[nt][2], fmaf(acc[nt][3], acc[nt][3], q1));
+      if (v0) *reinterpret_cast<uint32_t*>(o0 + nt * 8) = pack_bf16x2(acc[nt][0], acc[nt][1]);
+      if (v1) *reinterpret_cast<uint32_t*>(o1 + nt * 8) = pack_bf16x2(acc[nt][2], acc[nt][3]);
+    }
+    if (rowstats) {
+#pragma unroll
+      for (int o = 1; o <= 2; o <<= 1) {
+        s0 += __shfl_xor_sync(0xffffffffu, s0, o); q0 += __shfl_xor_sync(0xffffffffu, q0, o);
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o); q1 += __shfl_xor_sync(0xffffffffu, q1, o);
+      }
+      if (tq == 0) {
+        if (v0) rowstats[r0] = make_float2(s0, q0);
+        if (v1) rowstats[r1] = make_float2(s1, q1);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // GroupNorm(1, C) application.  The producing conv left per-row (sum, sumsq) partials;
 // each CTA first reduces its sample's partials in a fixed order (double), then normalises
 // its slice.  mode: 0 affine only, 1 GELU, 2 GELU(residual + .), 3 + emb[b, c].
@@ -149,8 +269,12 @@ __global__ void __launch_bounds__(256, 3)
 gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats, int n_stat_tiles, int rows_alloc,
                  const float* __restrict__ gamma, const float* __restrict__ beta,
                  const T* __restrict__ residual, const float* __restrict__ embproj,
-                 int emb_off, Geo g, int C, T* __restrict__ out) {
+                 int emb_off, Geo g, int C, T* __restrict__ out, int n_src) {
+  // `raw` holds n_src samples; output sample b reads raw sample b mod n_src (n_src < gridDim.y
+  // only where the classifier-free-guidance pair still shares its activations, see
+  // build_unet_plan).
   const int b = blockIdx.y;
+  const int b_src = b >= n_src ? b - n_src : b;
   const int tid = threadIdx.x;
   const int vpr = C >> 3;                  // vectors per row: 8, 16, 32 or 64
   const int rows_per_iter = 256 / vpr;
@@ -163,7 +287,7 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   __shared__ float s_mean, s_rstd;
   {
     double s1 = 0.0, s2 = 0.0;
-    const size_t sbase = static_cast<size_t>(b) * g.S;
+    const size_t sbase = static_cast<size_t>(b_src) * g.S;
     for (int rr = g.Wp + tid; rr < g.S; rr += 256) {
       if (!geo_is_pixel(g, rr)) continue;
       float a1 = 0.f, a2 = 0.f;
@@ -225,7 +349,7 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   int x = rr - fdiv(rr, g.mWp, g.Wp) * g.Wp;
   const int xstep = rows_per_iter - fdiv(rows_per_iter, g.mWp, g.Wp) * g.Wp;  // rows_per_iter mod Wp
   const size_t first = (base + rr) * C + c0;
-  const T* rp = raw + first;
+  const T* rp = raw + (static_cast<size_t>(b_src) * g.S + rr) * C + c0;
   const T* sp = (MODE == GN_RES_GELU) ? residual + first : nullptr;
   T* op = out + first;
   const int stride = rows_per_iter * C;
@@ -297,8 +421,8 @@ __global__ void maxpool2_kernel(const T* __restrict__ in, Geo gi, Geo go, int C,
 // Up-stage input: cat([skip, pad(bilinear_x2_align_corners(x))], channel).
 // models/unet_cond.py:76, 87-97.  Output geometry = skip geometry.
 template <typename T>
-__global__ void upcat_kernel(const T* __restrict__ skip, int Cs, const T* __restrict__ xin, Geo gx, int Cx,
-                             Geo go, T* __restrict__ out) {
+__global__ void upcat_kernel(const T* __restrict__ skip, int Cs, int n_skip, const T* __restrict__ xin, Geo gx,
+                             int Cx, Geo go, T* __restrict__ out) {
   const int C = Cs + Cx;
   const int vpr = C / 8;
   const long long total = static_cast<long long>(go.n) * go.H * go.W * vpr;
@@ -312,7 +436,9 @@ __global__ void upcat_kernel(const T* __restrict__ skip, int Cs, const T* __rest
   const int r = geo_row(go, b, y, x);
   float o[8];
   if (c0 < Cs) {
-    load8(skip + static_cast<size_t>(r) * Cs + c0, o);
+    // the skip tensor may hold only the shared half of a guidance pair (n_skip = go.n / 2)
+    const int rs = b >= n_skip ? r - n_skip * go.S : r;
+    load8(skip + static_cast<size_t>(rs) * Cs + c0, o);
   } else {
     const int cx = c0 - Cs;
     const int Hu = 2 * gx.H, Wu = 2 * gx.W;
