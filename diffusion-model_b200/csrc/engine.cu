@@ -152,8 +152,13 @@ template <typename T>
 struct GemmW {  // a repacked weight: [ntaps * rows_per_tap, K] K-major, plus its TMA descriptor
   T* w = nullptr;
   int K = 0, N = 0, rows_per_tap = 0, ntaps = 0, bn = 0;
-  CUtensorMap tmap;       // box = bn rows
-  CUtensorMap tmap_half;  // box = bn / 2 rows (CTA-pair kernel: each CTA loads half of the tile)
+  CUtensorMap tmap_bn[6];  // box = 8 << i rows (8 .. 256): the N tile is narrowed when a launch has
+                           // too few tiles to fill the chip; the CTA-pair kernel loads half tiles
+  const CUtensorMap& tmap_for(int box_rows) const {
+    int i = 0;
+    while ((8 << i) < box_rows) ++i;
+    return tmap_bn[i];
+  }
   const float* bias = nullptr;
 };
 
@@ -230,6 +235,8 @@ class Engine : public IEngine {
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     const char* pe = getenv("DMB200_PAIRS");
     use_pairs_ = pe ? (pe[0] - '0') : 1;
+    const char* ne = getenv("DMB200_NARROW_TILES");
+    narrow_tiles_ = ne ? (ne[0] != '0') : true;
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
@@ -296,6 +303,15 @@ class Engine : public IEngine {
 
   // ---- launch helpers
   Act<T> new_act(Pool& pool, int n, int H, int W, int C, bool with_stats, int stat_tiles = 0);
+  // N tile of a launch: the weight's own tile, halved (down to 32) while the launch would leave
+  // SMs without a tile -- at small batch the GEMMs are bound by streaming the weights, and more,
+  // narrower tiles spread that stream over more SMs.
+  int effective_bn(const GemmW<T>& w, int rows_valid) const {
+    int bn = w.bn;
+    const int m_tiles = cdiv(rows_valid, kTileM);
+    while (narrow_tiles_ && bn > 32 && m_tiles * (w.rows_per_tap / bn) < num_sms_) bn >>= 1;
+    return bn;
+  }
   void gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* shifts, int ntaps, GemmParams ep,
             cudaStream_t s, const Act<T>* out_act = nullptr);
   Op op_conv(const Act<T>& in, const GemmW<T>& w, const Act<T>& out);
@@ -333,6 +349,7 @@ class Engine : public IEngine {
   long long launches_ = 0;
   bool counting_ = true;
   bool use_tc_attention_ = true;
+  bool narrow_tiles_ = true;   // DMB200_NARROW_TILES=0: always the weight's own N tile
   int use_pairs_ = 1;   // cta_group::2 GEMM tiles: DMB200_PAIRS=0 off, 1 when there is enough work, 2 always
 
   Pool wpool_unet_, wpool_vae_;
@@ -388,8 +405,7 @@ GemmW<T> Engine<T>::make_conv3x3_from_ptr(const float* w_dev, int Co, int Ci, Po
   const long long total = 9LL * Co * Ci;
   repack_conv3x3_kernel<T><<<cdiv(total, 256), 256>>>(w_dev, Co, Ci, g.rows_per_tap, g.w);
   DMB_CHECK_LAUNCH();
-  g.tmap = make_tmap<T>(g.w, Ci, static_cast<uint64_t>(9) * g.rows_per_tap, g.bn);
-  g.tmap_half = make_tmap<T>(g.w, Ci, static_cast<uint64_t>(9) * g.rows_per_tap, std::max(8, g.bn / 2));
+  for (int i = 0; i < 6; ++i) g.tmap_bn[i] = make_tmap<T>(g.w, Ci, static_cast<uint64_t>(9) * g.rows_per_tap, 8 << i);
   return g;
 }
 
@@ -409,8 +425,7 @@ GemmW<T> Engine<T>::make_linear_w(const std::string& wname, const std::string& b
   g.w = pool.alloc_n<T>(static_cast<size_t>(g.rows_per_tap) * K);
   cast_kernel<T><<<cdiv(static_cast<long long>(N) * K, 256), 256>>>(f(wname), static_cast<long long>(N) * K, g.w);
   DMB_CHECK_LAUNCH();
-  g.tmap = make_tmap<T>(g.w, K, g.rows_per_tap, g.bn);
-  g.tmap_half = make_tmap<T>(g.w, K, g.rows_per_tap, std::max(8, g.bn / 2));
+  for (int i = 0; i < 6; ++i) g.tmap_bn[i] = make_tmap<T>(g.w, K, g.rows_per_tap, 8 << i);
   if (!bname.empty()) {
     DMB_REQUIRE(numel(bname) == N, "unexpected size of " + bname);
     g.bias = f(bname);
@@ -429,8 +444,7 @@ GemmW<T> Engine<T>::make_convT_w(const std::string& wname, const std::string& bn
   g.w = pool.alloc_n<T>(16ull * Co * Ci);
   repack_convT_kernel<T><<<cdiv(16LL * Co * Ci, 256), 256>>>(f(wname), Ci, Co, g.w);
   DMB_CHECK_LAUNCH();
-  g.tmap = make_tmap<T>(g.w, Ci, 16ull * Co, g.bn);
-  g.tmap_half = make_tmap<T>(g.w, Ci, 16ull * Co, std::max(8, g.bn / 2));
+  for (int i = 0; i < 6; ++i) g.tmap_bn[i] = make_tmap<T>(g.w, Ci, 16ull * Co, 8 << i);
   if (!bname.empty()) g.bias = f(bname);
   return g;
 }
@@ -590,27 +604,28 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     p.b_row[i] = (phase * ntaps + i) * w.rows_per_tap;
   }
   p.k_chunks = w.K / ElemTraits<T>::kChunkK;
-  p.block_n = w.bn;
-  p.n_tiles = w.rows_per_tap / w.bn;
+  const int bn = effective_bn(w, a.g.rows_valid);
+  p.block_n = bn;
+  p.n_tiles = w.rows_per_tap / bn;
   // CTA pairs (256-row tiles) when there is enough work to keep every pair busy
   const int m_tiles1 = cdiv(a.g.rows_valid, kTileM);
   // (short K loops -- the Linear layers -- are epilogue-bound and lose on the pair's cross-CTA hand-shakes)
-  const bool pair = w.bn >= 32 && ((use_pairs_ == 1 && ntaps * p.k_chunks >= 8 && (m_tiles1 / 2) * p.n_tiles >= num_sms_ / 2) ||
+  const bool pair = bn >= 32 && ((use_pairs_ == 1 && ntaps * p.k_chunks >= 8 && (m_tiles1 / 2) * p.n_tiles >= num_sms_ / 2) ||
                                    (use_pairs_ == 2 && m_tiles1 >= 2));
   const int ctas = pair ? 2 : 1;
   p.m_tiles = cdiv(a.g.rows_valid, kTileM * ctas);
-  p.tma_store = (out_act && ep.epi == EPI_STORE && ep.map_mode == 0 && w.bn % ElemTraits<T>::kChunkK == 0 &&
-                 out_act->C % ElemTraits<T>::kChunkK == 0 && out_act->C >= p.n_tiles * w.bn &&
+  p.tma_store = (out_act && ep.epi == EPI_STORE && ep.map_mode == 0 && bn % ElemTraits<T>::kChunkK == 0 &&
+                 out_act->C % ElemTraits<T>::kChunkK == 0 && out_act->C >= p.n_tiles * bn &&
                  out_act->g.rows_alloc == a.g.rows_alloc && ep.out == out_act->p && ep.ldc == out_act->C)
                     ? 1 : 0;
-  const int pair_bytes = kTileM * 128 + (w.bn / ctas) * 128;   // one (tap, K chunk) operand pair
+  const int pair_bytes = kTileM * 128 + (bn / ctas) * 128;   // one (tap, K chunk) operand pair
   const int staging = p.tma_store ? kStagingBytes : 0;
   const int ring = kGemmSmemMax - 1024 - staging;
   // One barrier hand-shake costs the issuing threads ~500 cycles (measured): group enough
   // operand pairs per stage that their MMAs (4 x bn/2 cycles per pair) cover it, while
   // keeping at least 3 stages in flight.
   const int n_iter = ntaps * p.k_chunks;
-  int group = std::max(1, std::min(std::min(n_iter, kMaxGroup), cdiv(256, w.bn)));
+  int group = std::max(1, std::min(std::min(n_iter, kMaxGroup), cdiv(256, bn)));
   if (group == 3) group = 2;
   while (group > 1 && ring / (group * pair_bytes) < 3) group >>= 1;
   {
@@ -622,8 +637,8 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   p.group = group;
   const int stage_bytes = group * pair_bytes;
   p.stages = std::min(kMaxStages, ring / stage_bytes);
-  p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM * ctas, w.bn);
-  p.tmem_cols = tmem_cols_for(w.bn);
+  p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM * ctas, bn);
+  p.tmem_cols = tmem_cols_for(bn);
   p.geo = a.g;
   p.rows_alloc = a.g.rows_alloc;
   p.n_valid = w.N;
@@ -640,14 +655,14 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    if (group == 1) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1>, a.tmap, w.tmap_half, tout, p));
-    else if (group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2>, a.tmap, w.tmap_half, tout, p));
-    else DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 4>, a.tmap, w.tmap_half, tout, p));
+    if (group == 1) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1>, a.tmap, w.tmap_for(bn / 2), tout, p));
+    else if (group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2>, a.tmap, w.tmap_for(bn / 2), tout, p));
+    else DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 4>, a.tmap, w.tmap_for(bn / 2), tout, p));
   } else {
     const int grid = std::min(p.m_tiles * p.n_tiles, num_sms_);
-    if (group == 1) gemm_tc_kernel<T, 1, 1><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap, tout, p);
-    else if (group == 2) gemm_tc_kernel<T, 1, 2><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap, tout, p);
-    else gemm_tc_kernel<T, 1, 4><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap, tout, p);
+    if (group == 1) gemm_tc_kernel<T, 1, 1><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
+    else if (group == 2) gemm_tc_kernel<T, 1, 2><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
+    else gemm_tc_kernel<T, 1, 4><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
   }
   DMB_CHECK_LAUNCH();
   count();
@@ -744,7 +759,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   };
   auto conv = [&](const Act<T>& in, const std::string& wname) {
     const GemmW<T>& w = gw_.at(wname);
-    Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, true, w.rows_per_tap / w.bn);
+    Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, true, w.rows_per_tap / effective_bn(w, in.g.rows_valid));
     ops.tag("conv3x3 " + std::to_string(w.K) + "->" + std::to_string(w.N) + " @" + std::to_string(in.g.H),
             2.0 * in.g.n * in.g.H * in.g.W * 9.0 * w.K * w.N);
     ops.push_back(op_conv(in, w, out));
@@ -1241,7 +1256,7 @@ void Engine<T>::op_conv3x3(const float* x, const float* w, int B, int Cin, int C
   GemmW<T> gw = make_conv3x3_from_ptr(wd, Cout, Cin, pool);
   Act<T> in = new_act(pool, B, H, W, Cin, false);
   const int cpad = gw.rows_per_tap;
-  Act<T> o = new_act(pool, B, H, W, cpad, true, gw.rows_per_tap / gw.bn);
+  Act<T> o = new_act(pool, B, H, W, cpad, true, gw.rows_per_tap / effective_bn(gw, make_geo(B, H, W).rows_valid));
   DMB_CUDA(cudaDeviceSynchronize());
   const long long tin = static_cast<long long>(B) * Cin * H * W;
   nchw_to_pm_kernel<T><<<cdiv(tin, 256), 256, 0, s>>>(x, in.g, Cin, in.p);
@@ -1269,8 +1284,7 @@ void Engine<T>::op_linear(const float* x, const float* w, const float* bias, int
   gw.w = pool.alloc_n<T>(static_cast<size_t>(gw.rows_per_tap) * K);
   cast_kernel<T><<<cdiv(static_cast<long long>(N) * K, 256), 256>>>(wd, static_cast<long long>(N) * K, gw.w);
   DMB_CHECK_LAUNCH();
-  gw.tmap = make_tmap<T>(gw.w, K, gw.rows_per_tap, gw.bn);
-  gw.tmap_half = make_tmap<T>(gw.w, K, gw.rows_per_tap, std::max(8, gw.bn / 2));
+  for (int i = 0; i < 6; ++i) gw.tmap_bn[i] = make_tmap<T>(gw.w, K, gw.rows_per_tap, 8 << i);
   float* bd = nullptr;
   if (bias) {
     bd = pool.alloc_n<float>(gw.rows_per_tap);
@@ -1318,8 +1332,7 @@ void Engine<T>::op_convT4x4(const float* x, const float* w, const float* bias, i
   gw.w = pool.alloc_n<T>(16ull * Cout * Cin);
   repack_convT_kernel<T><<<cdiv(16LL * Cout * Cin, 256), 256>>>(wd, Cin, Cout, gw.w);
   DMB_CHECK_LAUNCH();
-  gw.tmap = make_tmap<T>(gw.w, Cin, 16ull * Cout, gw.bn);
-  gw.tmap_half = make_tmap<T>(gw.w, Cin, 16ull * Cout, std::max(8, gw.bn / 2));
+  for (int i = 0; i < 6; ++i) gw.tmap_bn[i] = make_tmap<T>(gw.w, Cin, 16ull * Cout, 8 << i);
   float* bd = nullptr;
   if (bias) {
     bd = pool.alloc_n<float>(Cout);
