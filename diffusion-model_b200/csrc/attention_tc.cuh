@@ -45,7 +45,7 @@ __device__ __forceinline__ uint64_t umma_desc_noswz(uint32_t smem_addr, uint32_t
 // the nearest integer with the 1.5 * 2^23 trick, cubic minimax polynomial for 2^f on
 // [-0.5, 0.5] (relative error 7.5e-5, below the bf16 rounding of P), exponent added as an integer.
 #ifndef DMB_ATTN_POLY_MASK
-#define DMB_ATTN_POLY_MASK 3   // scores with (i & 3) == MASK take the FMA-pipe exp2; -1 disables
+#define DMB_ATTN_POLY_MASK -1   // scores with (i & 3) == MASK take the FMA-pipe exp2; -1 disables
 #endif
 constexpr bool kPolyExp = DMB_ATTN_POLY_MASK >= 0;
 __device__ __forceinline__ float ex2_poly(float x) {

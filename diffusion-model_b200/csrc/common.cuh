@@ -173,6 +173,53 @@ template <> struct Raw8<float> {
 };
 
 // Exact (erf) GELU, as nn.GELU() / F.gelu default.
+// ---------------------------------------------------------------------------
+// GroupNorm statistics are summed in ONE association order whatever N tile a launch uses (the
+// tile is narrowed at small batch), so a sample's result does not depend on the batch it is in
+// or on how the batch is sharded: the unit is an aligned group of 16 columns (even and odd
+// columns as two sequential chains), units combine as an aligned binary tree (a binary counter:
+// level l holds a finished subtree of 2^l units), and left-over subtrees combine from the
+// largest to the smallest.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float2 stat_unit16(const float* v) {
+  float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < 16; j += 2) {
+    s0 += v[j]; q0 = fmaf(v[j], v[j], q0);
+    s1 += v[j + 1]; q1 = fmaf(v[j + 1], v[j + 1], q1);
+  }
+  return make_float2(s0 + s1, q0 + q1);
+}
+struct StatTree {
+  float2 l0, l1, l2, l3, l4, l5;
+  uint32_t n = 0;
+  __device__ __forceinline__ static float2 join(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+  __device__ __forceinline__ void add(float2 x) {
+    const uint32_t c = n++;
+    if (!(c & 1)) { l0 = x; return; }
+    x = join(l0, x);
+    if (!(c & 2)) { l1 = x; return; }
+    x = join(l1, x);
+    if (!(c & 4)) { l2 = x; return; }
+    x = join(l2, x);
+    if (!(c & 8)) { l3 = x; return; }
+    x = join(l3, x);
+    if (!(c & 16)) { l4 = x; return; }
+    l5 = join(l4, x);
+  }
+  __device__ __forceinline__ float2 total() const {   // n <= 63
+    float2 r = make_float2(0.f, 0.f);
+    bool has = false;
+    if (n & 32) { r = l5; has = true; }
+    if (n & 16) { r = has ? join(r, l4) : l4; has = true; }
+    if (n & 8) { r = has ? join(r, l3) : l3; has = true; }
+    if (n & 4) { r = has ? join(r, l2) : l2; has = true; }
+    if (n & 2) { r = has ? join(r, l1) : l1; has = true; }
+    if (n & 1) { r = has ? join(r, l0) : l0; }
+    return r;
+  }
+};
+
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 // GELU for bf16 storage: x * sigmoid(u(x)) with u = logit(Phi(x)) fitted by an odd polynomial
 // (x * P4(x^2), coefficients pre-multiplied by -log2 e) -- 6 FMA-pipe ops and 2 MUFU ops

@@ -237,11 +237,12 @@ class Engine : public IEngine {
     use_pairs_ = pe ? (pe[0] - '0') : 1;
     const char* ne = getenv("DMB200_NARROW_TILES");
     narrow_tiles_ = ne ? (ne[0] != '0') : true;
+    if (ne && atoi(ne) >= 16) min_bn_ = atoi(ne);
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     DMB_CUDA(cudaFuncSetAttribute(attention_kernel<T, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     if constexpr (std::is_same<T, __nv_bfloat16>::value) {
-      DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+      DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
       DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
     }
@@ -309,7 +310,7 @@ class Engine : public IEngine {
   int effective_bn(const GemmW<T>& w, int rows_valid) const {
     int bn = w.bn;
     const int m_tiles = cdiv(rows_valid, kTileM);
-    while (narrow_tiles_ && bn > 32 && m_tiles * (w.rows_per_tap / bn) < num_sms_) bn >>= 1;
+    while (narrow_tiles_ && bn > min_bn_ && m_tiles * (w.rows_per_tap / bn) < num_sms_) bn >>= 1;
     return bn;
   }
   void gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* shifts, int ntaps, GemmParams ep,
@@ -349,6 +350,7 @@ class Engine : public IEngine {
   long long launches_ = 0;
   bool counting_ = true;
   bool use_tc_attention_ = true;
+  int min_bn_ = 16;
   bool narrow_tiles_ = true;   // DMB200_NARROW_TILES=0: always the weight's own N tile
   int use_pairs_ = 1;   // cta_group::2 GEMM tiles: DMB200_PAIRS=0 off, 1 when there is enough work, 2 always
 
@@ -606,6 +608,7 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   p.k_chunks = w.K / ElemTraits<T>::kChunkK;
   const int bn = effective_bn(w, a.g.rows_valid);
   p.block_n = bn;
+  p.stat_cols = std::min(bn, ElemTraits<T>::kChunkK);
   p.n_tiles = w.rows_per_tap / bn;
   // CTA pairs (256-row tiles) when there is enough work to keep every pair busy
   const int m_tiles1 = cdiv(a.g.rows_valid, kTileM);
@@ -759,7 +762,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   };
   auto conv = [&](const Act<T>& in, const std::string& wname) {
     const GemmW<T>& w = gw_.at(wname);
-    Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, true, w.rows_per_tap / effective_bn(w, in.g.rows_valid));
+    Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, true, w.rows_per_tap / std::min(effective_bn(w, in.g.rows_valid), ElemTraits<T>::kChunkK));
     ops.tag("conv3x3 " + std::to_string(w.K) + "->" + std::to_string(w.N) + " @" + std::to_string(in.g.H),
             2.0 * in.g.n * in.g.H * in.g.W * 9.0 * w.K * w.N);
     ops.push_back(op_conv(in, w, out));
@@ -813,7 +816,8 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
           const int qsplit = std::max(1, std::min(D <= 32 ? cdiv(nqb, 2) : nqb, cdiv(4 * num_sms_, 4 * qkv.g.n)));
           const int qpc = cdiv(nqb, qsplit);
           const dim3 grid(cdiv(nqb, qpc), 4, qkv.g.n);
-          const size_t smem = attention_tc_smem_bytes(L, D);
+          static const char* pad_env = getenv("DMB200_ATTN_PAD_SMEM");   // experiment: force 1 CTA / SM
+          const size_t smem = attention_tc_smem_bytes(L, D) + ((pad_env && L == 784) ? atoi(pad_env) * 1024 : 0);
           if (D == 16) attention_tc_kernel<16><<<grid, kAttnThreads, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
           else if (D == 32) attention_tc_kernel<32><<<grid, kAttnThreads, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
           else attention_tc_kernel<64><<<grid, kAttnThreads, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
@@ -1256,7 +1260,7 @@ void Engine<T>::op_conv3x3(const float* x, const float* w, int B, int Cin, int C
   GemmW<T> gw = make_conv3x3_from_ptr(wd, Cout, Cin, pool);
   Act<T> in = new_act(pool, B, H, W, Cin, false);
   const int cpad = gw.rows_per_tap;
-  Act<T> o = new_act(pool, B, H, W, cpad, true, gw.rows_per_tap / effective_bn(gw, make_geo(B, H, W).rows_valid));
+  Act<T> o = new_act(pool, B, H, W, cpad, true, gw.rows_per_tap / std::min(effective_bn(gw, make_geo(B, H, W).rows_valid), ElemTraits<T>::kChunkK));
   DMB_CUDA(cudaDeviceSynchronize());
   const long long tin = static_cast<long long>(B) * Cin * H * W;
   nchw_to_pm_kernel<T><<<cdiv(tin, 256), 256, 0, s>>>(x, in.g, Cin, in.p);

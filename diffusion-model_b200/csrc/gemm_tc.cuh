@@ -53,7 +53,8 @@ struct GemmParams {
   const float* bias;      // [n_valid] or null
   int act;                // 0 none, 1 GELU(erf)
   const void* residual;   // T [rows, ldc] or null (added after the activation)
-  float2* rowstats;       // [n_tiles][rows_alloc] (sum, sum of squares) or null
+  float2* rowstats;       // [N / stat_cols][rows_alloc] (sum, sum of squares) or null
+  int stat_cols;          // columns per statistics group: min(block_n, 128-byte K chunk)
   int rows_alloc;
   int map_mode;           // 0 identity; 1 = out pixel (2y+up_a, 2x+up_b) of geo_out
   Geo geo_out;
@@ -262,7 +263,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       mbar_wait(&tmem_full_bar[as], aph);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * p.block_n;
-      float sum = 0.f, sumsq = 0.f;
+      // GroupNorm partials of this row: one (sum, sumsq) per aligned group of
+      // p.stat_cols = min(block_n, kSubN) columns, each the aligned binary tree of its 16-column
+      // units; gn1_apply joins the groups in the same tree (common.cuh, StatTree), so the
+      // statistics do not depend on the N tile of the launch.
+      float2* stat_row = p.rowstats ? p.rowstats + static_cast<size_t>(n0 / p.stat_cols) * p.rows_alloc + r : nullptr;
 
       if (p.tma_store) {
         const int n_sub = p.block_n / kSubN;
@@ -298,14 +303,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 for (int i = 0; i < 8; ++i) v[8 * j + i] += rv[i];
               }
             }
-            if (p.rowstats) {
-              float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+            if (stat_row) {   // block_n >= kSubN here: one group per sub-tile
+              float2 u[kSubN / 16];
 #pragma unroll
-              for (int j = 0; j < kSubN; j += 2) {
-                s0 += v[j]; q0 = fmaf(v[j], v[j], q0);
-                s1 += v[j + 1]; q1 = fmaf(v[j + 1], v[j + 1], q1);
-              }
-              sum += s0 + s1; sumsq += q0 + q1;
+              for (int j = 0; j < kSubN / 16; ++j) u[j] = stat_unit16(v + 16 * j);
+              if constexpr (kSubN == 64) stat_row[static_cast<size_t>(k) * p.rows_alloc] = StatTree::join(StatTree::join(u[0], u[1]), StatTree::join(u[2], u[3]));
+              else stat_row[static_cast<size_t>(k) * p.rows_alloc] = StatTree::join(u[0], u[1]);
             }
           } else {
 #pragma unroll
@@ -358,6 +361,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       } else {
         int out_r = r;
         if (p.map_mode == 1 && valid) out_r = geo_row(p.geo_out, b, 2 * y + p.up_a, 2 * x + p.up_b);
+        float2 stat_hold = make_float2(0.f, 0.f);
         for (int c0 = 0; c0 < p.block_n; c0 += 32) {
           float v[32];
           if (p.block_n - c0 >= 32) {
@@ -392,11 +396,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
               }
             }
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              if (j < ncols) {
-                sum += v[j];
-                sumsq += v[j] * v[j];
+            if (stat_row) {   // block_n is a multiple of 16: whole units only
+              float2 g32 = stat_unit16(v);
+              if (ncols > 16) g32 = StatTree::join(g32, stat_unit16(v + 16));
+              if (p.stat_cols <= 32) {
+                stat_row[static_cast<size_t>(c0 / p.stat_cols) * p.rows_alloc] = g32;
+              } else if ((c0 & 32) == 0) {   // 64-column groups: left half now, joined with the right half next
+                stat_hold = g32;
+              } else {
+                stat_row[static_cast<size_t>(c0 / 64) * p.rows_alloc] = StatTree::join(stat_hold, g32);
               }
             }
             T* op = out + static_cast<size_t>(out_r) * p.ldc + col0;
@@ -408,7 +416,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
         release_tmem();
       }
-      if (p.rowstats && valid) p.rowstats[static_cast<size_t>(n_tile) * p.rows_alloc + r] = make_float2(sum, sumsq);
     }
     if (store_thread) tma_store_wait_all<0>();
   }

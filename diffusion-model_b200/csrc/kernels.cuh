@@ -290,12 +290,11 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
     const size_t sbase = static_cast<size_t>(b_src) * g.S;
     for (int rr = g.Wp + tid; rr < g.S; rr += 256) {
       if (!geo_is_pixel(g, rr)) continue;
-      float a1 = 0.f, a2 = 0.f;
-      for (int tn = 0; tn < n_stat_tiles; ++tn) {
-        const float2 v = rowstats[static_cast<size_t>(tn) * rows_alloc + sbase + rr];
-        a1 += v.x; a2 += v.y;
-      }
-      s1 += a1; s2 += a2;
+      StatTree acc;   // the groups of a row join in the same aligned tree as the units inside a group
+      const float2* rs = rowstats + sbase + rr;
+      for (int tn = 0; tn < n_stat_tiles; ++tn) acc.add(rs[static_cast<size_t>(tn) * rows_alloc]);
+      const float2 a = acc.total();
+      s1 += a.x; s2 += a.y;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
