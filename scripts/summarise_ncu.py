@@ -15,7 +15,14 @@ KEEP = ["gpu__time_duration.sum", "sm__cycles_elapsed.avg.per_second", "dram__by
         "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "smsp__inst_executed.sum",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
         "launch__shared_mem_per_block_dynamic", "launch__grid_size", "launch__block_size",
-        "smsp__cycles_active.avg", "sm__inst_executed_pipe_tensor_subpipe_hmma.sum"]
+        "smsp__cycles_active.avg", "sm__inst_executed_pipe_tensor_subpipe_hmma.sum",
+        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "sm__inst_issued.avg.pct_of_peak_sustained_active",
+        "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+        "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio"]
 
 
 def launches(src, dst, cmd):
