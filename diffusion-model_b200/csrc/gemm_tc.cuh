@@ -8,19 +8,24 @@
 // tensor arrive as zeros.  A 1x1 conv / Linear is the one-tap case; a 4x4 stride-2
 // transposed conv is four 4-tap launches (one per output phase) with a scattering row map.
 //
-// CTA = 384 threads, one CTA per SM, persistent over 128 x BLOCK_N output tiles:
-//   warp 0    TMA producer   (one lane)  : fills the smem ring, signals full[s] via complete_tx
-//   warp 1    MMA issuer     (one lane)  : tcgen05.mma SS, commits to empty[s] / tmem_full[a]
+// CTA = 384 threads, one CTA (kCtas = 1) or one 2-CTA cluster (kCtas = 2, cta_group::2, a
+// 256 x BLOCK_N tile whose B operand is split between the pair) per SM, persistent over tiles:
+//   warp 0    TMA producer : warp-uniform loop, elect_one() around the asm only; fills the smem
+//                            ring, kGroup (tap, K chunk) operand pairs per stage, signals full[s]
+//                            (of the leader CTA for pairs) via complete_tx
+//   warp 1    MMA issuer   : tcgen05.mma SS (leader CTA only for pairs), commits to empty[s]
+//                            (multicast to both CTAs) and to tmem_full[a]
 //   warp 2    TMEM allocator
-//   warps 4-11 epilogue      (256 thr)   : two warps per TMEM lane quadrant (each takes half of
-//                                          the columns): tcgen05.ld lane==row, bias / GELU /
-//                                          residual, row statistics for GroupNorm, then the
-//                                          tile goes through a 128B-swizzled staging buffer
-//                                          and out with ONE TMA store per 128-byte column
-//                                          block (pad-pixel rows are stored as zeros).
-// Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
-// Scattering outputs (conv-transpose phases), the image epilogue and tiles narrower than
-// 128 bytes keep per-thread stores.
+//   warps 4-7 / 8-11  two epilogue warpgroups, one per TMEM accumulator stage (tile parity):
+//                            tcgen05.ld lane == row, bias / GELU / residual, GroupNorm row
+//                            statistics per aligned column group, then the tile goes through the
+//                            warpgroup's own 128B-swizzled staging buffer and out with one TMA
+//                            store per 128-byte column block (pad-pixel rows are stored as zeros).
+// Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1 and the
+// two epilogues overlap each other.  Scattering outputs (conv-transpose phases), the image
+// epilogue and tiles narrower than 128 bytes keep per-thread stores.
+// Why kGroup: one producer <-> issuer mbarrier round trip costs ~500 cycles of issue-thread
+// time whatever the payload (measured), so a stage carries >= ~512 cycles of MMA work.
 #pragma once
 
 #include "common.cuh"

@@ -124,6 +124,38 @@ def test_config2_batch16_step_eps_parity(models):
         assert r["x_max_abs"] < 2e-2 * r["x_ref_max"], (k, r)
 
 
+def test_config2_batch16_step_eps_parity_tf32_mode(models):
+    """The fp32-storage / TF32-operand mode (DMB200_PRECISION=tf32) on the same teacher-forced
+    steps.  Tolerances: eps rel-L2 <= 3e-3, max-abs <= 1.5e-2 * max|eps|; x_{t-1} max-abs <= 3e-3 * max|x|."""
+    from dmb200 import context_for
+    from diff import Diffuser
+    unet, _, sd, _ = models
+    B = 16
+    y, vals, mask = synth.line_conditions(B, seed=0)
+    d = Diffuser(num_timesteps=1000, device=DEV)
+    ctx = context_for(DEV, "tf32")
+    ctx.ensure_unet(unet)
+    _, alphas, abars = R.schedule(1000)
+    g = torch.Generator().manual_seed(99)
+    rows = {}
+    for tt, scale in ((1000, 1.0), (1, 20.0)):
+        x = torch.randn((B, 4, 28, 28), generator=g) * scale
+        nz = torch.randn((B, 4, 28, 28), generator=g)
+        t = torch.full((B,), tt, dtype=torch.long)
+        with torch.no_grad():
+            x_ref, eps_ref = R.denoise_cond(sd, x, t, y, 3.0, 0, vals, mask, nz, alphas, abars)
+        out, eps = ctx.denoise_cond_step(x.to(DEV), t.to(DEV), y.to(DEV), 0, vals.to(DEV), mask.to(DEV), 3.0,
+                                         d.step_coefficients(), noise=nz.to(DEV), want_eps=True)
+        rows[f"t{tt}"] = {"eps_rel_l2": rel_l2(eps, eps_ref), "eps_max_abs": max_abs(eps, eps_ref),
+                          "eps_ref_max": float(eps_ref.abs().max()), "x_max_abs": max_abs(out, x_ref),
+                          "x_ref_max": float(x_ref.abs().max())}
+    report("config2_b16_step_tf32", rows)
+    for k, r in rows.items():
+        assert r["eps_rel_l2"] < 3e-3, (k, r)
+        assert r["eps_max_abs"] < 1.5e-2 * r["eps_ref_max"], (k, r)
+        assert r["x_max_abs"] < 3e-3 * r["x_ref_max"], (k, r)
+
+
 def test_vae_decode_golden(golden, models):
     _, vae, _, _ = models
     z = _t(golden["D_z"]).to(DEV)
