@@ -230,6 +230,13 @@ class Engine : public IEngine {
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    {
+      const char* ae = getenv("DMB200_ACC4");
+      use_acc4_ = ae ? (ae[0] != '0') : true;
+    }
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
@@ -350,6 +357,7 @@ class Engine : public IEngine {
   long long launches_ = 0;
   bool counting_ = true;
   bool use_tc_attention_ = true;
+  bool use_acc4_ = true;   // DMB200_ACC4=0: two epilogue warpgroups for every launch
   int min_bn_ = 16;
   bool narrow_tiles_ = true;   // DMB200_NARROW_TILES=0: always the weight's own N tile
   int use_pairs_ = 1;   // cta_group::2 GEMM tiles: DMB200_PAIRS=0 off, 1 when there is enough work, 2 always
@@ -622,7 +630,10 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
                  out_act->g.rows_alloc == a.g.rows_alloc && ep.out == out_act->p && ep.ldc == out_act->C)
                     ? 1 : 0;
   const int pair_bytes = kTileM * 128 + (bn / ctas) * 128;   // one (tap, K chunk) operand pair
-  const int staging = p.tma_store ? kStagingBytes : 0;
+  // Linear layers (one tap, short K, N tile <= 128): four accumulator stages / epilogue warpgroups
+  const bool acc4 = use_acc4_ && !pair && ntaps == 1 && bn <= 128 && p.tma_store;
+  const int n_acc = acc4 ? 4 : 2;
+  const int staging = p.tma_store ? gemm_staging_bytes(n_acc) : 0;
   const int ring = kGemmSmemMax - 1024 - staging;
   // One barrier hand-shake costs the issuing threads ~500 cycles (measured): group enough
   // operand pairs per stage that their MMAs (4 x bn/2 cycles per pair) cover it, while
@@ -641,7 +652,7 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   const int stage_bytes = group * pair_bytes;
   p.stages = std::min(kMaxStages, ring / stage_bytes);
   p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM * ctas, bn);
-  p.tmem_cols = tmem_cols_for(bn);
+  p.tmem_cols = tmem_cols_for(bn * n_acc / 2);
   p.geo = a.g;
   p.rows_alloc = a.g.rows_alloc;
   p.n_valid = w.N;
@@ -663,6 +674,12 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     else DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 4>, a.tmap, w.tmap_for(bn / 2), tout, p));
   } else {
     const int grid = std::min(p.m_tiles * p.n_tiles, num_sms_);
+    if (acc4) {
+      constexpr int kT4 = gemm_threads(4);
+      if (group == 1) gemm_tc_kernel<T, 1, 1, 4><<<grid, kT4, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
+      else if (group == 2) gemm_tc_kernel<T, 1, 2, 4><<<grid, kT4, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
+      else gemm_tc_kernel<T, 1, 4, 4><<<grid, kT4, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
+    } else
     if (group == 1) gemm_tc_kernel<T, 1, 1><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
     else if (group == 2) gemm_tc_kernel<T, 1, 2><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
     else gemm_tc_kernel<T, 1, 4><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);

@@ -69,17 +69,23 @@ struct GemmParams {
   uint8_t* img_u8;        // EPI_IMAGE: same, x255 clamp truncate
 };
 
-constexpr int kGemmThreads = 384;
-constexpr int kEpiThreads = 256;
-constexpr int kStagingBytes = 2 * kTileM * 128;  // two 128-row x 128-byte sub-tiles
+constexpr int kGemmThreads = 384;                // kAcc = 2: 4 control warps + 2 epilogue warpgroups
+constexpr int kStagingBytes = 2 * kTileM * 128;  // one 128-row x 128-byte sub-tile per epilogue warpgroup
+constexpr int gemm_threads(int acc) { return 128 + 128 * acc; }
+constexpr int gemm_staging_bytes(int acc) { return acc * kTileM * 128; }
 
 // kCtas == 2: launched as clusters of two CTAs (cta_group::2).  The pair owns a 256-row tile:
 // CTA rank r loads rows [m0 + 128 r, +128) of A and rows [n0 + r BLOCK_N/2, +BLOCK_N/2) of the
 // weight tile, keeps its 128 accumulator lanes in its own TMEM and runs its own epilogue;
 // rank 0 issues the M=256 MMAs and multicasts the commits.  Per SM this halves the B
 // operand's shared-memory traffic, which is what bounds the single-CTA kernel.
-template <typename T, int kCtas, int kGroup>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+//
+// kAcc = number of TMEM accumulator stages = number of epilogue warpgroups (2 or 4).  Short-K
+// launches (the Linear layers) are bound by the epilogue's dependent instruction stream: with
+// two warpgroups an SM scheduler holds two epilogue warps and issues in 23-38 % of its cycles
+// (ncu, profiles/r1_v3_ncu_full_up_path.md); four warpgroups (N tile <= 128) double that.
+template <typename T, int kCtas, int kGroup, int kAcc = 2>
+__global__ void __launch_bounds__(gemm_threads(kAcc), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_out, const GemmParams p) {
   using Tr = ElemTraits<T>;
@@ -87,8 +93,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
-  __shared__ __align__(8) uint64_t tmem_full_bar[2];
-  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ __align__(8) uint64_t tmem_full_bar[kAcc];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[kAcc];
   __shared__ uint32_t tmem_base_smem;
 
   const int warp = threadIdx.x >> 5;
@@ -115,7 +121,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < kAcc; ++a) {
       mbar_init(&tmem_full_bar[a], 1);
       mbar_init(&tmem_empty_bar[a], 4 * kCtas);  // one arrive per warp of the epilogue group (of each CTA)
     }
@@ -192,8 +198,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       uint32_t stage = 0, phase = 0;
       uint32_t tile_count = 0;
       for (int tile = cl; tile < total_tiles; tile += num_cl, ++tile_count) {
-        const uint32_t as = tile_count & 1;
-        const uint32_t aph = (tile_count >> 1) & 1;
+        const uint32_t as = tile_count % kAcc;
+        const uint32_t aph = (tile_count / kAcc) & 1;
         mbar_wait(&tmem_empty_bar[as], aph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * p.block_n;
@@ -255,7 +261,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     };
     uint32_t tile_count = 0;
     for (int tile = cl; tile < total_tiles; tile += num_cl, ++tile_count) {
-      if ((tile_count & 1) != as) continue;
+      if ((tile_count % kAcc) != as) continue;
       const int n_tile = tile % p.n_tiles;
       const int m_tile = tile / p.n_tiles;
       const int n0 = n_tile * p.block_n;
@@ -264,7 +270,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       int b = 0, y = 0, x = 0;
       const bool valid = geo_decode(p.geo, r, b, y, x);
 
-      const uint32_t aph = (tile_count >> 1) & 1;
+      const uint32_t aph = (tile_count / kAcc) & 1;
       mbar_wait(&tmem_full_bar[as], aph);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * p.block_n;
@@ -275,69 +281,82 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       float2* stat_row = p.rowstats ? p.rowstats + static_cast<size_t>(n0 / p.stat_cols) * p.rows_alloc + r : nullptr;
 
       if (p.tma_store) {
+        // kP columns are in registers at a time: a whole 128-byte sub-tile with two epilogue
+        // warpgroups, half of one (bf16) with four, whose 640-thread CTA leaves 96 registers
+        // per thread.
+        constexpr int kP = (kAcc == 4) ? 32 : kSubN;
+        constexpr int kHalves = kSubN / kP;
+        constexpr int kVecs = kP * static_cast<int>(sizeof(T)) / 16;   // 16-byte staging chunks per step
         const int n_sub = p.block_n / kSubN;
         for (int k = 0; k < n_sub; ++k) {
-          float v[kSubN];
-          tmem_ld32(t_row + k * kSubN, v);
-          if constexpr (kSubN == 64) tmem_ld32(t_row + k * kSubN + 32, v + 32);
-          tmem_ld_wait();
-          if (k == n_sub - 1) release_tmem();  // accumulator fully read: hand it back to the MMA issuer
-          const int col0 = n0 + k * kSubN;
-          if (valid) {
-            if (p.bias) {
 #pragma unroll
-              for (int j = 0; j < kSubN; j += 4) {
-                const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-                v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
+          for (int h = 0; h < kHalves; ++h) {
+            float v[kP];
+            tmem_ld32(t_row + k * kSubN + h * kP, v);
+            if constexpr (kP == 64) tmem_ld32(t_row + k * kSubN + 32, v + 32);
+            tmem_ld_wait();
+            if (k == n_sub - 1 && h == kHalves - 1) release_tmem();  // accumulator fully read: hand it back to the MMA issuer
+            const int col0 = n0 + k * kSubN + h * kP;
+            if (valid) {
+              if (p.bias) {
+#pragma unroll
+                for (int j = 0; j < kP; j += 4) {
+                  const float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+                  v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
+                }
               }
-            }
-            if (p.act == 1) {
+              if (p.act == 1) {
 #pragma unroll
-              for (int j = 0; j < kSubN; ++j) v[j] = gelu_for<T>(v[j]);
-            }
-            if (residual) {
-              const T* rp = residual + static_cast<size_t>(r) * p.ldc + col0;
-              Raw8<T> rr[kSubN / 8];
-#pragma unroll
-              for (int j = 0; j < kSubN / 8; ++j) rr[j].load(rp + 8 * j);
-#pragma unroll
-              for (int j = 0; j < kSubN / 8; ++j) {
-                float rv[8];
-                rr[j].unpack(rv);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[8 * j + i] += rv[i];
+                for (int j = 0; j < kP; ++j) v[j] = gelu_for<T>(v[j]);
               }
-            }
-            if (stat_row) {   // block_n >= kSubN here: one group per sub-tile
-              float2 u[kSubN / 16];
+              if (residual) {
+                const T* rp = residual + static_cast<size_t>(r) * p.ldc + col0;
+                Raw8<T> rr[kP / 8];
 #pragma unroll
-              for (int j = 0; j < kSubN / 16; ++j) u[j] = stat_unit16(v + 16 * j);
-              if constexpr (kSubN == 64) stat_row[static_cast<size_t>(k) * p.rows_alloc] = StatTree::join(StatTree::join(u[0], u[1]), StatTree::join(u[2], u[3]));
-              else stat_row[static_cast<size_t>(k) * p.rows_alloc] = StatTree::join(u[0], u[1]);
-            }
-          } else {
+                for (int j = 0; j < kP / 8; ++j) rr[j].load(rp + 8 * j);
 #pragma unroll
-            for (int j = 0; j < kSubN; ++j) v[j] = 0.f;  // pad pixels stay zero
-          }
-          if (store_thread) tma_store_wait_read<0>();  // the previous store of this group has read the buffer
-          named_bar_sync(bar_id, 128);
-          {
-            uint8_t* rowp = buf + row_in_tile * 128;
-            const int sw = row_in_tile & 7;
-            if constexpr (sizeof(T) == 2) {
+                for (int j = 0; j < kP / 8; ++j) {
+                  float rv[8];
+                  rr[j].unpack(rv);
 #pragma unroll
-              for (int c = 0; c < 8; ++c) {
-                uint4 u;
-                __nv_bfloat162* hp = reinterpret_cast<__nv_bfloat162*>(&u);
+                  for (int i = 0; i < 8; ++i) v[8 * j + i] += rv[i];
+                }
+              }
+              if constexpr (kHalves == 1) {   // (launches with row statistics use two warpgroups)
+                if (stat_row) {   // block_n >= kSubN here: one group per sub-tile
+                  float2 u[kSubN / 16];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) hp[i] = __floats2bfloat162_rn(v[c * 8 + 2 * i], v[c * 8 + 2 * i + 1]);
-                *reinterpret_cast<uint4*>(rowp + ((c ^ sw) << 4)) = u;
+                  for (int j = 0; j < kSubN / 16; ++j) u[j] = stat_unit16(v + 16 * j);
+                  if constexpr (kSubN == 64) stat_row[static_cast<size_t>(k) * p.rows_alloc] = StatTree::join(StatTree::join(u[0], u[1]), StatTree::join(u[2], u[3]));
+                  else stat_row[static_cast<size_t>(k) * p.rows_alloc] = StatTree::join(u[0], u[1]);
+                }
               }
             } else {
 #pragma unroll
-              for (int c = 0; c < 8; ++c) {
-                *reinterpret_cast<float4*>(rowp + ((c ^ sw) << 4)) =
-                    make_float4(v[c * 4], v[c * 4 + 1], v[c * 4 + 2], v[c * 4 + 3]);
+              for (int j = 0; j < kP; ++j) v[j] = 0.f;  // pad pixels stay zero
+            }
+            if (h == 0) {
+              if (store_thread) tma_store_wait_read<0>();  // the previous store of this group has read the buffer
+              named_bar_sync(bar_id, 128);
+            }
+            {
+              uint8_t* rowp = buf + row_in_tile * 128;
+              const int sw = row_in_tile & 7;
+              if constexpr (sizeof(T) == 2) {
+#pragma unroll
+                for (int c = 0; c < kVecs; ++c) {
+                  uint4 u;
+                  __nv_bfloat162* hp = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) hp[i] = __floats2bfloat162_rn(v[c * 8 + 2 * i], v[c * 8 + 2 * i + 1]);
+                  *reinterpret_cast<uint4*>(rowp + (((h * kVecs + c) ^ sw) << 4)) = u;
+                }
+              } else {
+#pragma unroll
+                for (int c = 0; c < kVecs; ++c) {
+                  *reinterpret_cast<float4*>(rowp + (((h * kVecs + c) ^ sw) << 4)) =
+                      make_float4(v[c * 4], v[c * 4 + 1], v[c * 4 + 2], v[c * 4 + 3]);
+                }
               }
             }
           }
