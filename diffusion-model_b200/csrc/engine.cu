@@ -743,7 +743,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     const int doubled = P.doubled ? 1 : 0;
     ops.tag("emb");
     ops.push_back([this, ew, pp, n, B, doubled](cudaStream_t s) {
-      emb_kernel<<<n, 256, 0, s>>>(ew, pp->t_vec, pp->y, pp->dyn->flags, pp->vals, pp->mask, B, doubled, pp->emb,
+      emb_kernel<<<dim3(cdiv(B, kEmbSamples), kEmbSplit), 256, 0, s>>>(ew, pp->t_vec, pp->y, pp->dyn->flags, pp->vals, pp->mask, B, doubled, pp->emb,
                                    pp->embproj);
       DMB_CHECK_LAUNCH();
       count();

@@ -18,7 +18,7 @@ constexpr int kLatH = 28, kLatW = 28;   // latent map (diff.py:9, img_size 28)
 // ---------------------------------------------------------------------------
 // Embedding: pos_encoding(t) + class_emb[y] + cond_mlp([vals|mask]) and the six
 // Linear(SiLU(emb)) projections of Down/Up.  unet_cond.py:155-167, 62-65, 82-85;
-// unet_cond_geom.py:89-95.  One CTA (256 threads) per effective sample.
+// unet_cond_geom.py:89-95.  One CTA (256 threads) per kEmbSamples samples (both guidance halves).
 // ---------------------------------------------------------------------------
 struct EmbWeights {
   const float* class_emb;  // [4][256]
@@ -31,48 +31,96 @@ struct EmbWeights {
   const float* projb;      // [896]
 };
 
+constexpr int kEmbSamples = 2;   // samples per CTA (x 2 guidance halves): every weight is loaded once for all of them
+constexpr int kEmbSplit = 4;     // blockIdx.y: slice of the projection columns (the small embedding part is recomputed)
+static_assert(kProjCols % kEmbSplit == 0 && kProjCols / kEmbSplit <= 256, "one projection column per thread");
+
 static __global__ void __launch_bounds__(256)
 emb_kernel(EmbWeights w, const long long* __restrict__ t_vec, const long long* __restrict__ y,
            const int* __restrict__ dyn_flags /* {null_label, has_cond} */,
            const float* __restrict__ vals, const float* __restrict__ mask,
            int B, int doubled, float* __restrict__ emb_out, float* __restrict__ proj_out) {
-  __shared__ float feat[2 * kCondDim];
-  __shared__ float h1[kEmbDim];
-  __shared__ float semb[kEmbDim];
-  const int be = blockIdx.x;
-  const int b = doubled ? (be % B) : be;
-  const int half = doubled ? (be / B) : 1;
+  __shared__ float feat[kEmbSamples][2 * kCondDim];
+  __shared__ float h1[kEmbSamples][kEmbDim];
+  __shared__ float semb[2 * kEmbSamples][kEmbDim];   // [sample][half]
+  const int b0 = blockIdx.x * kEmbSamples;
+  const int nb = min(kEmbSamples, B - b0);
   const int tid = threadIdx.x;
   const int null_label = dyn_flags[0];
   const bool has_cond = dyn_flags[1] != 0;
-  long long yv = (half == 0) ? static_cast<long long>(null_label) : y[b];
 
-  float cond = 0.f;
-  if (has_cond) {
-    if (tid < kCondDim) feat[tid] = vals[b * kCondDim + tid];
-    else if (tid < 2 * kCondDim) feat[tid] = mask[b * kCondDim + tid - kCondDim];
-    __syncthreads();
-    float h = w.b1[tid];
+  // cond_mlp([vals | mask]) does not depend on the guidance half: once per sample
+  float cond[kEmbSamples];
 #pragma unroll
-    for (int i = 0; i < 2 * kCondDim; ++i) h = fmaf(feat[i], w.w1t[i * kEmbDim + tid], h);
-    h1[tid] = silu(h);
+  for (int s = 0; s < kEmbSamples; ++s) cond[s] = 0.f;
+  if (has_cond) {
+    if (tid < kEmbSamples * 2 * kCondDim) {
+      const int s = tid / (2 * kCondDim), i = tid % (2 * kCondDim);
+      float v = 0.f;
+      if (s < nb) v = (i < kCondDim) ? vals[(b0 + s) * kCondDim + i] : mask[(b0 + s) * kCondDim + i - kCondDim];
+      feat[s][i] = v;
+    }
     __syncthreads();
-    float c = w.b2[tid];
-    for (int i = 0; i < kEmbDim; ++i) c = fmaf(h1[i], w.w2t[i * kEmbDim + tid], c);
-    cond = c;
+    float h[kEmbSamples];
+#pragma unroll
+    for (int s = 0; s < kEmbSamples; ++s) h[s] = w.b1[tid];
+#pragma unroll
+    for (int i = 0; i < 2 * kCondDim; ++i) {
+      const float wv = w.w1t[i * kEmbDim + tid];
+#pragma unroll
+      for (int s = 0; s < kEmbSamples; ++s) h[s] = fmaf(feat[s][i], wv, h[s]);
+    }
+#pragma unroll
+    for (int s = 0; s < kEmbSamples; ++s) h1[s][tid] = silu(h[s]);
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < kEmbSamples; ++s) cond[s] = w.b2[tid];
+#pragma unroll 16
+    for (int i = 0; i < kEmbDim; ++i) {
+      const float wv = w.w2t[i * kEmbDim + tid];
+#pragma unroll
+      for (int s = 0; s < kEmbSamples; ++s) cond[s] = fmaf(h1[s][i], wv, cond[s]);
+    }
   }
-  const float tf = static_cast<float>(t_vec[b]);
-  const float arg = tf * w.inv_freq[tid & 127];
-  const float pe = (tid < 128) ? sinf(arg) : cosf(arg);
-  float e = pe + w.class_emb[yv * kEmbDim + tid];
-  if (has_cond) e = e + cond;
-  if (emb_out) emb_out[be * kEmbDim + tid] = e;
-  semb[tid] = silu(e);
+  const int halves = doubled ? 2 : 1;
+#pragma unroll
+  for (int s = 0; s < kEmbSamples; ++s) {
+    if (s < nb) {
+      const int b = b0 + s;
+      const float tf = static_cast<float>(t_vec[b]);
+      const float arg = tf * w.inv_freq[tid & 127];
+      const float pe = (tid < 128) ? sinf(arg) : cosf(arg);
+      for (int hf = 0; hf < halves; ++hf) {
+        // doubled: effective sample hf * B + b; half 0 carries the null label (diff.py:147-150)
+        const long long yv = (doubled && hf == 0) ? static_cast<long long>(null_label) : y[b];
+        const int be = doubled ? hf * B + b : b;
+        float e = pe + w.class_emb[yv * kEmbDim + tid];
+        if (has_cond) e = e + cond[s];
+        if (emb_out && blockIdx.y == 0) emb_out[be * kEmbDim + tid] = e;
+        semb[2 * s + hf][tid] = silu(e);
+      }
+    }
+  }
   __syncthreads();
-  for (int o = tid; o < kProjCols; o += 256) {
-    float acc = w.projb[o];
-    for (int i = 0; i < kEmbDim; ++i) acc = fmaf(semb[i], w.projt[i * kProjCols + o], acc);
-    proj_out[be * kProjCols + o] = acc;
+  if (tid < kProjCols / kEmbSplit) {
+    const int o = blockIdx.y * (kProjCols / kEmbSplit) + tid;
+    float acc[2 * kEmbSamples];
+#pragma unroll
+    for (int q = 0; q < 2 * kEmbSamples; ++q) acc[q] = w.projb[o];
+#pragma unroll 16
+    for (int i = 0; i < kEmbDim; ++i) {
+      const float wv = w.projt[i * kProjCols + o];
+#pragma unroll
+      for (int q = 0; q < 2 * kEmbSamples; ++q) acc[q] = fmaf(semb[q][i], wv, acc[q]);
+    }
+#pragma unroll
+    for (int q = 0; q < 2 * kEmbSamples; ++q) {
+      const int s = q >> 1, hf = q & 1;
+      if (s < nb && hf < halves) {
+        const int be = doubled ? hf * B + b0 + s : b0 + s;
+        proj_out[be * kProjCols + o] = acc[q];
+      }
+    }
   }
 }
 
