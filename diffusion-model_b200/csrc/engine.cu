@@ -227,6 +227,11 @@ class Engine : public IEngine {
     DMB_CUDA(cudaGetDeviceProperties(&prop, device));
     if (prop.major != 10) fail(4, "this library is built for sm_100a (B200); found sm_" + std::to_string(prop.major) + std::to_string(prop.minor));
     num_sms_ = prop.multiProcessorCount;
+    // the embedding kernel runs beside inc / down1 on a second stream (fork / join by events,
+    // also inside the captured graph)
+    DMB_CUDA(cudaStreamCreateWithFlags(&side_, cudaStreamNonBlocking));
+    DMB_CUDA(cudaEventCreateWithFlags(&ev_fork_, cudaEventDisableTiming));
+    DMB_CUDA(cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
@@ -258,7 +263,11 @@ class Engine : public IEngine {
     const char* env = getenv("DMB200_CUDA_CORE_ATTENTION");
     use_tc_attention_ = !(env && env[0] == '1');
   }
-  ~Engine() override {}
+  ~Engine() override {
+    if (ev_fork_) cudaEventDestroy(ev_fork_);
+    if (ev_join_) cudaEventDestroy(ev_join_);
+    if (side_) cudaStreamDestroy(side_);
+  }
 
   void load_unet(const TensorMapIn& w) override;
   void load_vae(const TensorMapIn& w) override;
@@ -357,6 +366,8 @@ class Engine : public IEngine {
   long long launches_ = 0;
   bool counting_ = true;
   bool use_tc_attention_ = true;
+  cudaStream_t side_ = nullptr;
+  cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
   bool use_acc4_ = true;   // DMB200_ACC4=0: two epilogue warpgroups for every launch
   int min_bn_ = 16;
   bool narrow_tiles_ = true;   // DMB200_NARROW_TILES=0: always the weight's own N tile
@@ -743,13 +754,18 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     const int doubled = P.doubled ? 1 : 0;
     ops.tag("emb");
     ops.push_back([this, ew, pp, n, B, doubled](cudaStream_t s) {
-      emb_kernel<<<dim3(cdiv(B, kEmbSamples), kEmbSplit), 256, 0, s>>>(ew, pp->t_vec, pp->y, pp->dyn->flags, pp->vals, pp->mask, B, doubled, pp->emb,
-                                   pp->embproj);
+      // nothing before down1's embedding add reads the result: fork to the side stream
+      DMB_CUDA(cudaEventRecord(ev_fork_, s));
+      DMB_CUDA(cudaStreamWaitEvent(side_, ev_fork_, 0));
+      emb_kernel<<<dim3(cdiv(B, kEmbSamples), kEmbSplit), 256, 0, side_>>>(ew, pp->t_vec, pp->y, pp->dyn->flags, pp->vals,
+                                                                          pp->mask, B, doubled, pp->emb, pp->embproj);
       DMB_CHECK_LAUNCH();
+      DMB_CUDA(cudaEventRecord(ev_join_, side_));
       count();
     });
   }
 
+  bool emb_joined = false;
   auto gn = [&](const Act<T>& raw, const std::string& gname, int mode, const Act<T>* residual, int emb_off,
                 int n_out = 0) {
     if (n_out == 0) n_out = raw.g.n;
@@ -762,6 +778,11 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     // enough CTAs to fill the chip at small batch, whole samples per CTA at large batch
     const int want = (8 * num_sms_ + n_out - 1) / n_out;
     const int splits = std::max(1, std::min(std::min(want, 16), total_vec / 512));
+    if (mode == GN_ADD_EMB && !emb_joined) {   // first consumer of the embedding projections: join the side stream
+      emb_joined = true;
+      ops.tag("emb join");
+      ops.push_back([this](cudaStream_t s) { DMB_CUDA(cudaStreamWaitEvent(s, ev_join_, 0)); });
+    }
     ops.tag("gn1_apply " + std::to_string(raw.C) + " @" + std::to_string(raw.g.H) + " m" + std::to_string(mode), 0,
             static_cast<double>(n_out) * total_vec * 8 * sizeof(T) * (residual ? 3 : 2));
     ops.push_back([this, raw, out, gamma, beta, mode, res, embproj, emb_off, splits](cudaStream_t s) {
