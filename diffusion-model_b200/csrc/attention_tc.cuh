@@ -45,7 +45,7 @@ __device__ __forceinline__ uint64_t umma_desc_noswz(uint32_t smem_addr, uint32_t
 // the nearest integer with the 1.5 * 2^23 trick, cubic minimax polynomial for 2^f on
 // [-0.5, 0.5] (relative error 7.5e-5, below the bf16 rounding of P), exponent added as an integer.
 #ifndef DMB_ATTN_POLY_MASK
-#define DMB_ATTN_POLY_MASK -1   // scores with (i & 3) == MASK take the FMA-pipe exp2; -1 disables
+#define DMB_ATTN_POLY_MASK 3   // scores with (i & 3) == MASK take the FMA-pipe exp2; -1 disables
 #endif
 constexpr bool kPolyExp = DMB_ATTN_POLY_MASK >= 0;
 __device__ __forceinline__ float ex2_poly(float x) {
@@ -77,6 +77,7 @@ attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bf
   __shared__ __align__(8) uint64_t pv_bar[2];     // chain c: the P V MMA has retired     (MMA -> softmax)
   __shared__ uint32_t tmem_base_smem;
 
+  pdl_trigger();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int L = g.H * g.W;
   const int nkb = (L + kAttnK - 1) / kAttnK;
@@ -119,6 +120,7 @@ attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bf
     *reinterpret_cast<__nv_bfloat16*>(Ones + cm_off(n, k, kAttnK)) = __float2bfloat16_rn(n == 0 ? 1.0f : 0.0f);
   }
 
+  pdl_wait();   // (barrier init, TMEM allocation and the ones tile overlap the previous kernel's tail)
   // ---- stage K and V^T of the head (once per CTA); 4 keys in flight per thread
   {
     const uint4 zero = make_uint4(0, 0, 0, 0);
@@ -306,28 +308,29 @@ attention_tc_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bf
         }
         const float mc = m_run * c2;
         const int nval = L - kbase;   // valid keys of this block; whole groups of 16 padding keys cost nothing
-#pragma unroll
-        for (int g16 = 0; g16 < kAttnK / 16; ++g16) {
-          if (g16 * 16 < nval) {
-#pragma unroll
-            for (int i = g16 * 16; i < g16 * 16 + 16; ++i) {
-              const float x = fmaf(s[i], c2, -mc);
-              s[i] = (kPolyExp && (DMB_ATTN_POLY_MASK >= 4 ? (i & 1) == 1 : (i & 3) == DMB_ATTN_POLY_MASK)) ? ex2_poly(x) : ex2_approx(x);   // exp2(-inf) = 0 for masked keys
-            }
-          } else {
-#pragma unroll
-            for (int i = g16 * 16; i < g16 * 16 + 16; ++i) s[i] = 0.f;
-          }
-        }
         if (!pv_done) mbar_wait(&pv_bar[c], (G - 1) & 1);   // P was last read by the P V MMA of block G-1
+        // exp2, bf16 truncation and the shared-memory store of P in ONE loop over 8-key chunks:
+        // a warp issues in order, so MUFU instructions that queue for the XU pipe should have
+        // independent FMA / ALU / LSU work right behind them rather than 63 more MUFUs.
+        // fp32 -> bf16 by truncation: one byte-permute per PAIR (the F2FP pack shares the MUFU pipe);
+        // the truncation bias cancels because the row sum comes from the same truncated values.
 #pragma unroll
-        for (int gq = 0; gq < kAttnK / 8; ++gq) {
-          uint4 u;
-          u.x = __byte_perm(__float_as_uint(s[gq * 8 + 0]), __float_as_uint(s[gq * 8 + 1]), 0x7632);
-          u.y = __byte_perm(__float_as_uint(s[gq * 8 + 2]), __float_as_uint(s[gq * 8 + 3]), 0x7632);
-          u.z = __byte_perm(__float_as_uint(s[gq * 8 + 4]), __float_as_uint(s[gq * 8 + 5]), 0x7632);
-          u.w = __byte_perm(__float_as_uint(s[gq * 8 + 6]), __float_as_uint(s[gq * 8 + 7]), 0x7632);
-          *reinterpret_cast<uint4*>(Pc + cm_off(row, gq * 8, kAttnK)) = u;
+        for (int ch = 0; ch < kAttnK / 8; ++ch) {
+          uint4 u = make_uint4(0u, 0u, 0u, 0u);
+          if ((ch >> 1) * 16 < nval) {
+            float e[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float x = fmaf(s[ch * 8 + i], c2, -mc);
+              e[i] = (kPolyExp && (DMB_ATTN_POLY_MASK >= 4 ? (i & 1) == 1 : (i & 3) == DMB_ATTN_POLY_MASK)) ? ex2_poly(x)
+                                                                                                            : ex2_approx(x);   // exp2(-inf) = 0 for masked keys
+            }
+            u.x = __byte_perm(__float_as_uint(e[0]), __float_as_uint(e[1]), 0x7632);
+            u.y = __byte_perm(__float_as_uint(e[2]), __float_as_uint(e[3]), 0x7632);
+            u.z = __byte_perm(__float_as_uint(e[4]), __float_as_uint(e[5]), 0x7632);
+            u.w = __byte_perm(__float_as_uint(e[6]), __float_as_uint(e[7]), 0x7632);
+          }
+          *reinterpret_cast<uint4*>(Pc + cm_off(row, ch * 8, kAttnK)) = u;
         }
         fence_async_proxy();
         tc_fence_before();

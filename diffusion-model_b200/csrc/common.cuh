@@ -247,6 +247,13 @@ __device__ __forceinline__ float silu(float x) { return x / (1.0f + expf(-x)); }
 // ---------------------------------------------------------------------------
 // PTX wrappers
 // ---------------------------------------------------------------------------
+// Programmatic dependent launch.  Every kernel of the step loop starts with pdl_trigger() (the
+// next kernel of the stream may be scheduled as soon as all CTAs of this one are resident or
+// done) and calls pdl_wait() before its first global-memory access (returns once the previous
+// kernel has completed and its writes are visible).  Without the launch attribute both are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

@@ -239,6 +239,8 @@ class Engine : public IEngine {
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     {
+      const char* pe2 = getenv("DMB200_PDL");
+      use_pdl_ = pe2 ? (pe2[0] != '0') : false;
       const char* ae = getenv("DMB200_ACC4");
       use_acc4_ = ae ? (ae[0] != '0') : true;
     }
@@ -319,6 +321,24 @@ class Engine : public IEngine {
   GemmW<T> make_conv3x3_from_ptr(const float* w_dev, int Co, int Ci, Pool& pool);
 
   // ---- launch helpers
+  // Launch of a step-loop kernel.  With programmatic dependent launch (DMB200_PDL=1) the kernel may
+  // be scheduled while the previous kernel of the stream drains; every kernel launched through
+  // here calls pdl_wait() before it touches global memory (common.cuh).  Off by default: the
+  // kernels' own latency chains, not the launch gaps, bound the small-batch step (measured).
+  template <typename... KArgs, typename... Args>
+  void launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = use_pdl_ ? 1 : 0;
+    DMB_CUDA(cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...));
+  }
   Act<T> new_act(Pool& pool, int n, int H, int W, int C, bool with_stats, int stat_tiles = 0);
   // N tile of a launch: the weight's own tile, halved (down to 32) while the launch would leave
   // SMs without a tile -- at small batch the GEMMs are bound by streaming the weights, and more,
@@ -368,6 +388,7 @@ class Engine : public IEngine {
   bool use_tc_attention_ = true;
   cudaStream_t side_ = nullptr;
   cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
+  bool use_pdl_ = false;   // DMB200_PDL=1: programmatic dependent launch (measured: no gain at batch 1, -1.6 % at 256)
   bool use_acc4_ = true;   // DMB200_ACC4=0: two epilogue warpgroups for every launch
   int min_bn_ = 16;
   bool narrow_tiles_ = true;   // DMB200_NARROW_TILES=0: always the weight's own N tile
@@ -676,10 +697,12 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     cfg.blockDim = dim3(kGemmThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = use_pdl_ ? 2 : 1;
     if (group == 1) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1>, a.tmap, w.tmap_for(bn / 2), tout, p));
     else if (group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2>, a.tmap, w.tmap_for(bn / 2), tout, p));
     else DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 4>, a.tmap, w.tmap_for(bn / 2), tout, p));
@@ -687,13 +710,13 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     const int grid = std::min(p.m_tiles * p.n_tiles, num_sms_);
     if (acc4) {
       constexpr int kT4 = gemm_threads(4);
-      if (group == 1) gemm_tc_kernel<T, 1, 1, 4><<<grid, kT4, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
-      else if (group == 2) gemm_tc_kernel<T, 1, 2, 4><<<grid, kT4, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
-      else gemm_tc_kernel<T, 1, 4, 4><<<grid, kT4, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
+      if (group == 1) launch(gemm_tc_kernel<T, 1, 1, 4>, grid, kT4, smem, s, a.tmap, w.tmap_for(bn), tout, p);
+      else if (group == 2) launch(gemm_tc_kernel<T, 1, 2, 4>, grid, kT4, smem, s, a.tmap, w.tmap_for(bn), tout, p);
+      else launch(gemm_tc_kernel<T, 1, 4, 4>, grid, kT4, smem, s, a.tmap, w.tmap_for(bn), tout, p);
     } else
-    if (group == 1) gemm_tc_kernel<T, 1, 1><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
-    else if (group == 2) gemm_tc_kernel<T, 1, 2><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
-    else gemm_tc_kernel<T, 1, 4><<<grid, kGemmThreads, smem, s>>>(a.tmap, w.tmap_for(bn), tout, p);
+    if (group == 1) launch(gemm_tc_kernel<T, 1, 1>, grid, kGemmThreads, smem, s, a.tmap, w.tmap_for(bn), tout, p);
+    else if (group == 2) launch(gemm_tc_kernel<T, 1, 2>, grid, kGemmThreads, smem, s, a.tmap, w.tmap_for(bn), tout, p);
+    else launch(gemm_tc_kernel<T, 1, 4>, grid, kGemmThreads, smem, s, a.tmap, w.tmap_for(bn), tout, p);
   }
   DMB_CHECK_LAUNCH();
   count();
@@ -788,10 +811,10 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.push_back([this, raw, out, gamma, beta, mode, res, embproj, emb_off, splits](cudaStream_t s) {
       const dim3 grid(splits, out.g.n);
 #define DMB_GN_ARGS raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc, gamma, beta, res, embproj, emb_off, out.g, raw.C, out.p, raw.g.n
-      if (mode == GN_GELU) gn1_apply_kernel<T, GN_GELU><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
-      else if (mode == GN_RES_GELU) gn1_apply_kernel<T, GN_RES_GELU><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
-      else if (mode == GN_ADD_EMB) gn1_apply_kernel<T, GN_ADD_EMB><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
-      else gn1_apply_kernel<T, GN_NONE><<<grid, 256, 0, s>>>(DMB_GN_ARGS);
+      if (mode == GN_GELU) launch(gn1_apply_kernel<T, GN_GELU>, grid, 256, 0, s, DMB_GN_ARGS);
+      else if (mode == GN_RES_GELU) launch(gn1_apply_kernel<T, GN_RES_GELU>, grid, 256, 0, s, DMB_GN_ARGS);
+      else if (mode == GN_ADD_EMB) launch(gn1_apply_kernel<T, GN_ADD_EMB>, grid, 256, 0, s, DMB_GN_ARGS);
+      else launch(gn1_apply_kernel<T, GN_NONE>, grid, 256, 0, s, DMB_GN_ARGS);
 #undef DMB_GN_ARGS
       DMB_CHECK_LAUNCH();
       count();
@@ -825,9 +848,9 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
         // C/8 lanes per token; each block walks rows with a grid stride
         const int tpb = 256 / (C / 8);
         const int grid = std::max(1, std::min(cdiv(in.g.rows_valid, tpb * 8), num_sms_ * 8));
-        if (C == 64) layernorm_kernel<T, 8><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
-        else if (C == 128) layernorm_kernel<T, 16><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
-        else layernorm_kernel<T, 32><<<grid, 256, 0, s>>>(in.p, wv, bv, in.g, out.p);
+        if (C == 64) launch(layernorm_kernel<T, 8>, grid, 256, 0, s, in.p, wv, bv, in.g, out.p);
+        else if (C == 128) launch(layernorm_kernel<T, 16>, grid, 256, 0, s, in.p, wv, bv, in.g, out.p);
+        else launch(layernorm_kernel<T, 32>, grid, 256, 0, s, in.p, wv, bv, in.g, out.p);
         DMB_CHECK_LAUNCH();
         count();
       });
@@ -856,9 +879,9 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
           const dim3 grid(cdiv(nqb, qpc), 4, qkv.g.n);
           static const char* pad_env = getenv("DMB200_ATTN_PAD_SMEM");   // experiment: force 1 CTA / SM
           const size_t smem = attention_tc_smem_bytes(L, D) + ((pad_env && L == 784) ? atoi(pad_env) * 1024 : 0);
-          if (D == 16) attention_tc_kernel<16><<<grid, kAttnThreads, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
-          else if (D == 32) attention_tc_kernel<32><<<grid, kAttnThreads, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
-          else attention_tc_kernel<64><<<grid, kAttnThreads, smem, s>>>(qkv.p, qkv.g, C, av.p, qpc);
+          if (D == 16) launch(attention_tc_kernel<16>, grid, kAttnThreads, smem, s, qkv.p, qkv.g, C, av.p, qpc);
+          else if (D == 32) launch(attention_tc_kernel<32>, grid, kAttnThreads, smem, s, qkv.p, qkv.g, C, av.p, qpc);
+          else launch(attention_tc_kernel<64>, grid, kAttnThreads, smem, s, qkv.p, qkv.g, C, av.p, qpc);
           DMB_CHECK_LAUNCH();
           count();
           return;
@@ -867,9 +890,9 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       const int threads = std::min(128, (L + 31) / 32 * 32);
       const dim3 grid(cdiv(L, threads), 4, qkv.g.n);
       const size_t smem = static_cast<size_t>(L) * D * 2 * sizeof(float);
-      if (D == 16) attention_kernel<T, 16><<<grid, threads, smem, s>>>(qkv.p, qkv.g, C, av.p);
-      else if (D == 32) attention_kernel<T, 32><<<grid, threads, smem, s>>>(qkv.p, qkv.g, C, av.p);
-      else attention_kernel<T, 64><<<grid, threads, smem, s>>>(qkv.p, qkv.g, C, av.p);
+      if (D == 16) launch(attention_kernel<T, 16>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p);
+      else if (D == 32) launch(attention_kernel<T, 32>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p);
+      else launch(attention_kernel<T, 64>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p);
       DMB_CHECK_LAUNCH();
       count();
     });
@@ -890,7 +913,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.tag("maxpool", 0, 1.25 * pooled.g.n * x.g.H * x.g.W * x.C * sizeof(T));
     ops.push_back([this, x, pooled](cudaStream_t s) {
       const long long total = static_cast<long long>(pooled.g.n) * pooled.g.H * pooled.g.W * (x.C / 8);
-      maxpool2_kernel<T><<<cdiv(total, 256), 256, 0, s>>>(x.p, x.g, pooled.g, x.C, pooled.p);
+      launch(maxpool2_kernel<T>, cdiv(total, 256), 256, 0, s, x.p, x.g, pooled.g, x.C, pooled.p);
       DMB_CHECK_LAUNCH();
       count();
     });
@@ -902,7 +925,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.tag("upcat", 0, 2.0 * cat.g.n * cat.g.H * cat.g.W * cat.C * sizeof(T));
     ops.push_back([this, x, skip, cat](cudaStream_t s) {
       const long long total = static_cast<long long>(cat.g.n) * cat.g.H * cat.g.W * (cat.C / 8);
-      upcat_kernel<T><<<cdiv(total, 256), 256, 0, s>>>(skip.p, skip.C, skip.g.n, x.p, x.g, x.C, cat.g, cat.p);
+      launch(upcat_kernel<T>, cdiv(total, 256), 256, 0, s, skip.p, skip.C, skip.g.n, x.p, x.g, x.C, cat.g, cat.p);
       DMB_CHECK_LAUNCH();
       count();
     });
@@ -924,7 +947,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.tag("conv_in 4->64 @28", 2.0 * n0 * kLatH * kLatW * 36.0 * 64);
     ops.push_back([this, r0, w0, pp, B](cudaStream_t s) {
       if constexpr (std::is_same<T, __nv_bfloat16>::value)
-        conv_in_mma_kernel<<<dim3(r0.g.n, 1), kConvInThreads, 0, s>>>(pp->x_state, B, w0, nullptr, 1.0f, r0.g, 64,
+        launch(conv_in_mma_kernel, dim3(r0.g.n, 1), kConvInThreads, 0, s, pp->x_state, B, w0, nullptr, 1.0f, r0.g, 64,
                                                                       r0.p, r0.stats);
       else
         conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), r0.g.n, 1), 128, 0, s>>>(pp->x_state, B, w0, nullptr, 1.0f,
@@ -1043,7 +1066,7 @@ void Engine<T>::cfg_step(const float* x_in, const long long* t, const long long*
   tail.tag("cfg_step (out conv + CFG + DDPM)", 0, static_cast<double>(B) * kLatH * kLatW * (2 * 64 * sizeof(T) + 4 * 4 * 3));
   Plan<T>* pp = &p;
   tail.push_back([this, pp, B](cudaStream_t cs) {
-    cfg_step_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, cs>>>(pp->feat.p, pp->feat.g, B, &pp->dyn->step);
+    launch(cfg_step_kernel<T>, dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, cs, pp->feat.p, pp->feat.g, B, &pp->dyn->step);
     DMB_CHECK_LAUNCH();
     count();
   });
@@ -1075,9 +1098,9 @@ void Engine<T>::sample_loop(float* x, const long long* y, int null_label, const 
 
   auto one_step = [&](cudaStream_t cs) {
     run_ops(p, cs);
-    cfg_step_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, cs>>>(p.feat.p, p.feat.g, B, &p.dyn->step);
+    launch(cfg_step_kernel<T>, dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, cs, p.feat.p, p.feat.g, B, &p.dyn->step);
     DMB_CHECK_LAUNCH();
-    advance_t_kernel<<<cdiv(B, 256), 256, 0, cs>>>(p.t_vec, B);
+    launch(advance_t_kernel, cdiv(B, 256), 256, 0, cs, p.t_vec, B);
     DMB_CHECK_LAUNCH();
     count(2);
   };
@@ -1196,7 +1219,7 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
     ops.tag("vae conv_in 4->256 @28", 2.0 * n * kLatH * kLatW * 36.0 * 256);
     ops.push_back([this, r0, w0, b0, pp, n](cudaStream_t s) {
       if constexpr (std::is_same<T, __nv_bfloat16>::value)
-        conv_in_mma_kernel<<<dim3(n, 4), kConvInThreads, 0, s>>>(pp->z, n, w0, b0, 0.18215f, r0.g, 256, r0.p, nullptr);
+        launch(conv_in_mma_kernel, dim3(n, 4), kConvInThreads, 0, s, pp->z, n, w0, b0, 0.18215f, r0.g, 256, r0.p, nullptr);
       else
         conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), n, 4), 128, 0, s>>>(pp->z, n, w0, b0, 0.18215f, r0.g, 256,
                                                                                r0.p, nullptr);

@@ -97,6 +97,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   __shared__ __align__(8) uint64_t tmem_empty_bar[kAcc];
   __shared__ uint32_t tmem_base_smem;
 
+  pdl_trigger();
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
@@ -135,6 +136,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   if constexpr (kCtas == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();   // barriers, TMEM and descriptors are set up; from here on global memory is touched
 
   const int total_tiles = p.m_tiles * p.n_tiles;
   const int n_iter = p.num_taps * p.k_chunks;

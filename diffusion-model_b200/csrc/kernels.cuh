@@ -205,6 +205,8 @@ static __global__ void __launch_bounds__(kConvInThreads)
 conv_in_mma_kernel(const float* __restrict__ x, int B_src, const float* __restrict__ w_oihw,
                    const float* __restrict__ bias, float in_div, Geo g, int cout,
                    __nv_bfloat16* __restrict__ out, float2* __restrict__ rowstats) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int PW = kLatW + 2, PH = kLatH + 2, PLANE = PW * PH;   // zero-bordered latent plane
   __shared__ float img[kLatC * PLANE];
   __shared__ float ws[64 * 36];
@@ -318,6 +320,8 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
                  const float* __restrict__ gamma, const float* __restrict__ beta,
                  const T* __restrict__ residual, const float* __restrict__ embproj,
                  int emb_off, Geo g, int C, T* __restrict__ out, int n_src) {
+  pdl_trigger();
+  pdl_wait();
   // `raw` holds n_src samples; output sample b reads raw sample b mod n_src (n_src < gridDim.y
   // only where the classifier-free-guidance pair still shares its activations, see
   // build_unet_plan).
@@ -442,6 +446,8 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
 // MaxPool2d(2), floor.  models/unet_cond.py:58.
 template <typename T>
 __global__ void maxpool2_kernel(const T* __restrict__ in, Geo gi, Geo go, int C, T* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   const int vpr = C / 8;
   const long long total = static_cast<long long>(go.n) * go.H * go.W * vpr;
   const long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -470,6 +476,8 @@ __global__ void maxpool2_kernel(const T* __restrict__ in, Geo gi, Geo go, int C,
 template <typename T>
 __global__ void upcat_kernel(const T* __restrict__ skip, int Cs, int n_skip, const T* __restrict__ xin, Geo gx,
                              int Cx, Geo go, T* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   const int C = Cs + Cx;
   const int vpr = C / 8;
   const long long total = static_cast<long long>(go.n) * go.H * go.W * vpr;
@@ -520,6 +528,8 @@ template <typename T, int LPT>
 __global__ void __launch_bounds__(256, 3)
 layernorm_kernel(const T* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
                  Geo g, T* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int C = LPT * 8;
   constexpr int TPB = 256 / LPT;  // tokens (PM rows) per block iteration
   const int sub = threadIdx.x % LPT;
@@ -580,6 +590,8 @@ layernorm_kernel(const T* __restrict__ in, const float* __restrict__ w, const fl
 template <typename T, int D>
 __global__ void __launch_bounds__(128)
 attention_kernel(const T* __restrict__ qkv, Geo g, int E, T* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float kv[];
   const int L = g.H * g.W;
   float* Ks = kv;
@@ -691,6 +703,8 @@ struct StepParams {
 template <typename T>
 __global__ void __launch_bounds__(128)
 cfg_step_kernel(const T* __restrict__ feat, Geo g, int B, const StepParams* __restrict__ pp) {
+  pdl_trigger();
+  pdl_wait();
   const StepParams p = *pp;
   __shared__ float ws[kLatC * 64];
   __shared__ float bs[kLatC];
@@ -806,6 +820,8 @@ geom_head_kernel(const T* __restrict__ feat, Geo g, const float* __restrict__ w1
 
 // t_vec[b] -= 1 (end of a captured step).
 static __global__ void advance_t_kernel(long long* t_vec, int B) {
+  pdl_trigger();
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B) t_vec[i] -= 1;
 }
