@@ -120,8 +120,21 @@ int dmb_sample_loop(dmb_ctx* ctx, float* x, const int64_t* y, int null_label, co
     DMB_REQUIRE(ctx && x && y && coef, "ctx, x, y and coef are required");
     DMB_REQUIRE((vals == nullptr) == (mask == nullptr), "cond_vals and cond_mask must be given together");
     DMB_REQUIRE(null_label >= 0 && null_label <= 3, "null_label must index class_emb (0..3)");
-    ctx->eng->sample_loop(x, ll(y), null_label, vals, mask, guidance_scale, coef, T, t_start, n_steps, noise, seed,
+    ctx->eng->sample_loop(x, ll(y), null_label, vals, mask, guidance_scale, coef, T, t_start, 1, n_steps, noise, seed,
                           sample_offset, x_dump, eps_dump, B, st(stream));
+  });
+}
+
+int dmb_sample_loop_strided(dmb_ctx* ctx, float* x, const int64_t* y, int null_label, const float* vals,
+                            const float* mask, float guidance_scale, const float* coef, int T, int t_start,
+                            int t_stride, int n_steps, const float* noise, uint64_t seed, uint64_t sample_offset,
+                            float* x_dump, float* eps_dump, int B, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && x && y && coef, "ctx, x, y and coef are required");
+    DMB_REQUIRE((vals == nullptr) == (mask == nullptr), "cond_vals and cond_mask must be given together");
+    DMB_REQUIRE(null_label >= 0 && null_label <= 3, "null_label must index class_emb (0..3)");
+    ctx->eng->sample_loop(x, ll(y), null_label, vals, mask, guidance_scale, coef, T, t_start, t_stride, n_steps, noise,
+                          seed, sample_offset, x_dump, eps_dump, B, st(stream));
   });
 }
 

@@ -280,9 +280,9 @@ class Engine : public IEngine {
                 unsigned long long seed, unsigned long long sample_offset, float* x_out, float* eps_out, int B,
                 cudaStream_t s) override;
   void sample_loop(float* x, const long long* y, int null_label, const float* vals, const float* mask,
-                   float guidance, const float* coef, int T_steps, int t_start, int n_steps, const float* noise,
-                   unsigned long long seed, unsigned long long sample_offset, float* x_dump, float* eps_dump,
-                   int B, cudaStream_t s) override;
+                   float guidance, const float* coef, int T_steps, int t_start, int t_stride, int n_steps,
+                   const float* noise, unsigned long long seed, unsigned long long sample_offset, float* x_dump,
+                   float* eps_dump, int B, cudaStream_t s) override;
   void vae_decode(const float* z, int B, float* img_f32, uint8_t* img_u8, cudaStream_t s) override;
   void get_tap(const char* name, float* out, int64_t capacity, int64_t* shape4, cudaStream_t s) override;
   void op_conv3x3(const float* x, const float* w, int B, int Cin, int Cout, int H, int W, float* out,
@@ -1057,6 +1057,7 @@ void Engine<T>::cfg_step(const float* x_in, const long long* t, const long long*
   bind_inputs(p, x_in, t, y, vals, mask, null_label, s);
   StepParams sp{};
   sp.x_in = p.x_state; sp.x_out = x_out; sp.t_vec = p.t_vec; sp.coef = coef; sp.T = T_steps; sp.slot_t0 = 0;
+  sp.t_stride = 1;
   sp.guidance = guidance; sp.noise = noise; sp.noise_step_stride = 0; sp.seed = seed;
   sp.sample_offset = sample_offset; sp.eps_out = eps_out; sp.x_dump = nullptr; sp.dump_step_stride = 0;
   sp.w_out = f("out.weight"); sp.b_out = f("out.bias");
@@ -1078,12 +1079,14 @@ void Engine<T>::cfg_step(const float* x_in, const long long* t, const long long*
 // between calls is read from device memory, so the graph is captured once per batch size.
 template <typename T>
 void Engine<T>::sample_loop(float* x, const long long* y, int null_label, const float* vals, const float* mask,
-                            float guidance, const float* coef, int T_steps, int t_start, int n_steps,
+                            float guidance, const float* coef, int T_steps, int t_start, int t_stride, int n_steps,
                             const float* noise, unsigned long long seed, unsigned long long sample_offset,
                             float* x_dump, float* eps_dump, int B, cudaStream_t s) {
   DMB_CUDA(cudaSetDevice(device_));
   DMB_REQUIRE(t_start >= 1 && t_start <= T_steps, "t_start must be in [1, T]");
-  DMB_REQUIRE(n_steps >= 1 && n_steps <= t_start, "n_steps must be in [1, t_start]");
+  DMB_REQUIRE(t_stride >= 1, "t_stride must be >= 1");
+  DMB_REQUIRE(n_steps >= 1 && static_cast<long long>(n_steps - 1) * t_stride < t_start,
+              "the visited timesteps t_start - k * t_stride must stay >= 1");
   Plan<T>& p = get_plan(B, true);
   bind_inputs(p, x, nullptr, y, vals, mask, null_label, s);
   fill_t_kernel<<<cdiv(B, 256), 256, 0, s>>>(p.t_vec, B, t_start);
@@ -1091,7 +1094,7 @@ void Engine<T>::sample_loop(float* x, const long long* y, int null_label, const 
   const long long lat = static_cast<long long>(B) * kLatC * kLatH * kLatW;
   StepParams sp{};
   sp.x_in = p.x_state; sp.x_out = p.x_state; sp.t_vec = p.t_vec; sp.coef = coef; sp.T = T_steps;
-  sp.slot_t0 = t_start; sp.guidance = guidance; sp.noise = noise; sp.noise_step_stride = lat; sp.seed = seed;
+  sp.slot_t0 = t_start; sp.t_stride = t_stride; sp.guidance = guidance; sp.noise = noise; sp.noise_step_stride = lat; sp.seed = seed;
   sp.sample_offset = sample_offset; sp.eps_out = eps_dump; sp.x_dump = x_dump; sp.dump_step_stride = lat;
   sp.w_out = f("out.weight"); sp.b_out = f("out.bias");
   DMB_CUDA(cudaMemcpyAsync(&p.dyn->step, &sp, sizeof(sp), cudaMemcpyHostToDevice, s));
@@ -1100,7 +1103,7 @@ void Engine<T>::sample_loop(float* x, const long long* y, int null_label, const 
     run_ops(p, cs);
     launch(cfg_step_kernel<T>, dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, cs, p.feat.p, p.feat.g, B, &p.dyn->step);
     DMB_CHECK_LAUNCH();
-    launch(advance_t_kernel, cdiv(B, 256), 256, 0, cs, p.t_vec, B);
+    launch(advance_t_kernel, cdiv(B, 256), 256, 0, cs, p.t_vec, B, &p.dyn->step);
     DMB_CHECK_LAUNCH();
     count(2);
   };

@@ -40,7 +40,7 @@ class IEngine {
                         const float* noise, unsigned long long seed, unsigned long long sample_offset,
                         float* x_out, float* eps_out, int B, cudaStream_t s) = 0;
   virtual void sample_loop(float* x, const long long* y, int null_label, const float* vals, const float* mask,
-                           float guidance, const float* coef, int T, int t_start, int n_steps,
+                           float guidance, const float* coef, int T, int t_start, int t_stride, int n_steps,
                            const float* noise, unsigned long long seed, unsigned long long sample_offset,
                            float* x_dump, float* eps_dump, int B, cudaStream_t s) = 0;
   virtual void vae_decode(const float* z, int B, float* img_f32, uint8_t* img_u8, cudaStream_t s) = 0;

@@ -687,7 +687,8 @@ struct StepParams {
   const long long* t_vec;  // (B,) current timestep per sample, 1..T
   const float* coef;       // (T,3): (1-a)/sqrt(1-abar), sqrt(a), sigma
   int T;
-  int slot_t0;             // noise / dump slot of a step = slot_t0 - t
+  int slot_t0;             // noise / dump slot of a step = (slot_t0 - t) / t_stride
+  int t_stride;            // timesteps per loop iteration (1 = the reference's schedule)
   float guidance;
   const float* noise;       // injected noise or null (then Philox)
   long long noise_step_stride;  // elements between consecutive steps' noise (0: single step)
@@ -735,7 +736,7 @@ cfg_step_kernel(const T* __restrict__ feat, Geo g, int B, const StepParams* __re
       }
   }
   const long long t = p.t_vec[b];
-  const int slot = p.slot_t0 - static_cast<int>(t);
+  const int slot = (p.slot_t0 - static_cast<int>(t)) / p.t_stride;
   const float c1 = p.coef[(t - 1) * 3 + 0], sqrt_a = p.coef[(t - 1) * 3 + 1], sigma = p.coef[(t - 1) * 3 + 2];
   float nz[kLatC] = {0.f, 0.f, 0.f, 0.f};
   if (t != 1) {
@@ -818,12 +819,12 @@ geom_head_kernel(const T* __restrict__ feat, Geo g, const float* __restrict__ w1
   }
 }
 
-// t_vec[b] -= 1 (end of a captured step).
-static __global__ void advance_t_kernel(long long* t_vec, int B) {
+// t_vec[b] -= t_stride (end of a captured step).
+static __global__ void advance_t_kernel(long long* t_vec, int B, const StepParams* __restrict__ pp) {
   pdl_trigger();
   pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < B) t_vec[i] -= 1;
+  if (i < B) t_vec[i] -= pp->t_stride;
 }
 static __global__ void fill_t_kernel(long long* t_vec, int B, long long t) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -54,6 +54,31 @@ class Diffuser:
             self._coef = torch.stack([c1, sq, sigma], dim=1).contiguous().float()
         return self._coef
 
+    def strided_coefficients(self, sample_steps: int):
+        """EXTENSION (not in the reference): constants of a deterministic
+        DDIM (eta = 0) pass over the sub-sampled schedule t_k = T - k * (T // sample_steps).
+
+        The DDIM update  x' = sqrt(ab') * (x - sqrt(1-ab) eps) / sqrt(ab) + sqrt(1-ab') eps  is
+        x' = a x + b eps with a = sqrt(ab'/ab), b = sqrt(1-ab') - a sqrt(1-ab); written in the form the
+        step kernel evaluates, x' = (x - c0 eps) / c1 + c2 z, that is c0 = -b/a, c1 = 1/a, c2 = 0
+        (ab' = alpha_bar of the NEXT visited timestep, 1 after the last).  Returns (coef (T,3), stride)."""
+        T = self.num_timesteps
+        if sample_steps < 1 or T % sample_steps != 0:
+            raise ValueError(f"sample_steps must divide num_timesteps={T}, got {sample_steps}")
+        stride = T // sample_steps
+        ab = self.alpha_bars.double()
+        t = torch.arange(T, 0, -stride, device=ab.device)            # visited timesteps T, T-s, ..., s
+        t_prev = t - stride                                           # >= 0
+        ab_t = ab[t - 1]
+        ab_p = torch.where(t_prev >= 1, ab[torch.clamp(t_prev - 1, min=0)], torch.ones_like(ab_t))
+        a = torch.sqrt(ab_p / ab_t)
+        b = torch.sqrt(1 - ab_p) - a * torch.sqrt(1 - ab_t)
+        coef = torch.zeros((T, 3), dtype=torch.float64, device=ab.device)
+        coef[:, 1] = 1.0
+        coef[t - 1, 0] = -b / a
+        coef[t - 1, 1] = 1.0 / a
+        return coef.float().contiguous(), stride
+
     def _ctx(self, model):
         from dmb200 import context_for
         dev = torch.device(self.device)
@@ -98,7 +123,19 @@ class Diffuser:
 
     # ------------------------------------------------------------------ loops
     def _run_loop(self, ctx, x, y, vals, msk, guidance_scale, null_label, progress, noise, seed, sample_offset,
-                  latent_dump, desc):
+                  latent_dump, desc, sample_steps=None):
+        if sample_steps is not None:
+            # extension: strided deterministic schedule (see strided_coefficients)
+            coef, stride = self.strided_coefficients(int(sample_steps))
+            if noise is not None:
+                raise ValueError("the strided (eta = 0) schedule draws no noise")
+            B = x.shape[0]
+            dump = None
+            if latent_dump:
+                dump = torch.empty((int(sample_steps),) + tuple(x.shape), device=x.device, dtype=torch.float32)
+            ctx.sample_loop(x, y, null_label, vals, msk, guidance_scale, coef, self.num_timesteps, int(sample_steps),
+                            seed=seed, sample_offset=sample_offset, x_dump=dump, t_stride=stride)
+            return x, dump
         T = self.num_timesteps
         coef = self.step_coefficients()
         B = x.shape[0]
@@ -160,8 +197,13 @@ class Diffuser:
         sample_offset: int = 0,
         latent_dump: bool = False,
         return_u8: bool = False,
+        sample_steps: Optional[int] = None,
     ):
         """Class + numeric-condition CFG sampling (diff.py:174-369).
+
+        ``sample_steps`` (keyword-only EXTENSION, default None = the reference's full T-step
+        ancestral DDPM loop, unchanged): run a deterministic DDIM pass over ``sample_steps``
+        evenly strided timesteps instead (must divide T).
 
         Returns what the reference returns: the latent if ``vae is None``, a (B,3,224,224)
         tensor if ``to_pil=False``, else a list of PIL images.  With ``latent_dump=True`` a
@@ -205,7 +247,7 @@ class Diffuser:
         if seed is None:
             seed = int(torch.randint(0, 2 ** 62, (1,)).item())
         x, dump = self._run_loop(ctx, x, y, vals, msk, guidance_scale, null_label, progress, noise, seed,
-                                 sample_offset, latent_dump, "Sampling (cond+numeric)")
+                                 sample_offset, latent_dump, "Sampling (cond+numeric)", sample_steps=sample_steps)
 
         def ret(v):
             return (v, dump) if latent_dump else v

@@ -40,6 +40,8 @@ _SIGNATURES = {
                                         C.c_uint64, _P, _P, C.c_int, _P]),
     "dmb_sample_loop": (C.c_int, [_P, _P, _P, C.c_int, _P, _P, C.c_float, _P, C.c_int, C.c_int, C.c_int, _P,
                                   C.c_uint64, C.c_uint64, _P, _P, C.c_int, _P]),
+    "dmb_sample_loop_strided": (C.c_int, [_P, _P, _P, C.c_int, _P, _P, C.c_float, _P, C.c_int, C.c_int, C.c_int,
+                                          C.c_int, _P, C.c_uint64, C.c_uint64, _P, _P, C.c_int, _P]),
     "dmb_vae_decode": (C.c_int, [_P, _P, C.c_int, _P, _P, _P]),
     "dmb_philox_normal": (C.c_int, [_P, _P, C.c_int, C.c_uint64, C.c_uint64, C.c_int, _P]),
     "dmb_launch_count": (C.c_int64, [_P]),
@@ -201,8 +203,8 @@ class Context:
         return (out, eps) if want_eps else out
 
     def sample_loop(self, x, y, null_label, vals, mask, guidance, coef, t_start, n_steps, noise=None, seed=0,
-                    sample_offset=0, x_dump=None, eps_dump=None):
-        """In place on x (B,4,28,28)."""
+                    sample_offset=0, x_dump=None, eps_dump=None, t_stride=1):
+        """In place on x (B,4,28,28).  t_stride > 1: iteration k runs at t = t_start - k * t_stride."""
         B = x.shape[0]
         _check_dev(x, self.device, torch.float32, "x")
         coef = _check_dev(coef, self.device, torch.float32, "coef")
@@ -213,9 +215,14 @@ class Context:
         y = y.to(torch.long).contiguous()
         vals = None if vals is None else vals.to(torch.float32).contiguous()
         mask = None if mask is None else mask.to(torch.float32).contiguous()
-        self._call("dmb_sample_loop", self._h, _ptr(x), _ptr(y), int(null_label), _ptr(vals), _ptr(mask),
-                   float(guidance), _ptr(coef), coef.shape[0], int(t_start), int(n_steps), _ptr(noise), int(seed),
-                   int(sample_offset), _ptr(x_dump), _ptr(eps_dump), B, self._stream())
+        if int(t_stride) == 1:
+            self._call("dmb_sample_loop", self._h, _ptr(x), _ptr(y), int(null_label), _ptr(vals), _ptr(mask),
+                       float(guidance), _ptr(coef), coef.shape[0], int(t_start), int(n_steps), _ptr(noise), int(seed),
+                       int(sample_offset), _ptr(x_dump), _ptr(eps_dump), B, self._stream())
+        else:
+            self._call("dmb_sample_loop_strided", self._h, _ptr(x), _ptr(y), int(null_label), _ptr(vals), _ptr(mask),
+                       float(guidance), _ptr(coef), coef.shape[0], int(t_start), int(t_stride), int(n_steps),
+                       _ptr(noise), int(seed), int(sample_offset), _ptr(x_dump), _ptr(eps_dump), B, self._stream())
         return x
 
     def vae_decode(self, z, want_f32=True, want_u8=False):

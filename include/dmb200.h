@@ -83,6 +83,17 @@ int dmb_sample_loop(dmb_ctx* ctx, float* x, const int64_t* y, int null_label, co
                     const float* noise, uint64_t seed, uint64_t sample_offset, float* x_dump, float* eps_dump,
                     int B, void* stream);
 
+/* Extension (NOT in the reference): the same loop over a strided
+ * schedule.  Iteration k runs at t = t_start - k * t_stride (all >= 1) and reads its constants
+ * from row t-1 of coef like dmb_sample_loop; the caller fills those rows with the update it
+ * wants, e.g. deterministic DDIM (eta = 0) written in the posterior-step form
+ * x' = (x - c0 * eps) / c1 + c2 * z  (Diffuser.strided_coefficients).  noise / x_dump / eps_dump
+ * are indexed by iteration.  t_stride = 1 is exactly dmb_sample_loop. */
+int dmb_sample_loop_strided(dmb_ctx* ctx, float* x, const int64_t* y, int null_label, const float* vals,
+                            const float* mask, float guidance_scale, const float* coef, int T, int t_start,
+                            int t_stride, int n_steps, const float* noise, uint64_t seed, uint64_t sample_offset,
+                            float* x_dump, float* eps_dump, int B, void* stream);
+
 /* VAE.decode (models/vae.py:64-69) + Diffuser.reverse_to_img's x*255 / clamp / uint8 truncation
  * (diff.py:58-61).  z (B,4,28,28) [dev]; img_f32 (B,3,224,224) [dev] in [0,1] or NULL;
  * img_u8 (B,3,224,224) [dev] or NULL. */

@@ -214,6 +214,35 @@ def sample_latent(sd: SD, x_T: torch.Tensor, y: torch.Tensor, cond_vals, cond_ma
     return x
 
 
+def ddim_update(x: torch.Tensor, eps: torch.Tensor, t: int, t_prev: int, alpha_bars: torch.Tensor) -> torch.Tensor:
+    """EXTENSION, not in the reference: deterministic DDIM step (Song et al.
+    2021, eq. 12 with sigma = 0) from timestep t to t_prev (0 = the clean sample), in float64:
+    x0 = (x - sqrt(1-ab_t) eps) / sqrt(ab_t);  x' = sqrt(ab_prev) x0 + sqrt(1-ab_prev) eps."""
+    ab = alpha_bars.double()
+    ab_t = ab[t - 1]
+    ab_p = ab[t_prev - 1] if t_prev >= 1 else torch.tensor(1.0, dtype=torch.float64)
+    x0 = (x.double() - torch.sqrt(1 - ab_t) * eps.double()) / torch.sqrt(ab_t)
+    return (torch.sqrt(ab_p) * x0 + torch.sqrt(1 - ab_p) * eps.double()).float()
+
+
+def sample_latent_strided(sd: SD, x_T: torch.Tensor, y: torch.Tensor, cond_vals, cond_mask, sample_steps: int,
+                          num_timesteps: int = 1000, guidance_scale: float = 3.0, null_label: int = 0,
+                          record: Optional[list] = None) -> torch.Tensor:
+    """EXTENSION: the CFG loop over T, T-s, ..., s (s = T / sample_steps) with ddim_update."""
+    _, _, alpha_bars = schedule(num_timesteps)
+    assert num_timesteps % sample_steps == 0
+    s = num_timesteps // sample_steps
+    x = x_T
+    B = x.shape[0]
+    for i in range(num_timesteps, 0, -s):
+        t = torch.full((B,), i, dtype=torch.long)
+        eps, _, _ = cfg_eps(sd, x, t, y, guidance_scale, null_label, cond_vals, cond_mask)
+        x = ddim_update(x, eps, i, i - s, alpha_bars)
+        if record is not None:
+            record.append((i, eps, x))
+    return x
+
+
 # --------------------------------------------------------------------------
 # VAE decoder and image conversion
 # --------------------------------------------------------------------------

@@ -245,3 +245,28 @@ def test_launches_are_counted(models):
     x = torch.randn((1, 4, 28, 28), generator=g).to(DEV)
     unet(x, torch.tensor([5], device=DEV), torch.tensor([1], device=DEV))
     assert ctx.launch_count() > 100
+
+
+def test_strided_ddim_extension_matches_oracle(models):
+    """Extension N1 (not in the reference): 10 evenly strided deterministic DDIM steps through the
+    CUDA-graph loop vs the oracle's restatement of the same update.  Tolerance: latent rel-L2 <= 3e-2;
+    the dump holds x_t before each visited step."""
+    from diff import Diffuser
+    unet, _, sd, _ = models
+    B, K = 3, 10
+    y, vals, mask, _ = synth.mixed_conditions(B, seed=4)
+    g = torch.Generator().manual_seed(11)
+    x_T = torch.randn((B, 4, 28, 28), generator=g)
+    with torch.no_grad():
+        ref = R.sample_latent_strided(sd, x_T, y, vals, mask, K)
+    d = Diffuser(num_timesteps=1000, device=DEV)
+    cc = {int(c): int((y == c).sum()) for c in sorted(set(y.tolist()))}
+    order = torch.argsort(y, stable=True)   # sample_latent_cond lays classes out in blocks
+    got, dump = d.sample_latent_cond(unet, cc, z_shape=(4, 28, 28), vae=None, progress=False, guidance_scale=3.0,
+                                     cond=vals[order].to(DEV), cond_mask=mask[order].to(DEV), x_T=x_T[order].to(DEV),
+                                     seed=1, latent_dump=True, sample_steps=K)
+    assert tuple(dump.shape) == (K, B, 4, 28, 28)
+    assert torch.equal(dump[0].cpu(), x_T[order])
+    r = rel_l2(got, ref[order])
+    report("strided_ddim_K10", {"latent_rel_l2": r})
+    assert r < 3e-2

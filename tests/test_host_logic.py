@@ -169,3 +169,28 @@ def test_reverse_to_img_truncates():
     img = Diffuser().reverse_to_img(x)
     assert img.mode == "RGB" and img.size == (7, 1)
     assert list(np.array(img)[0, :, 0]) == [0, 0, 1, 127, 255, 255, 0]
+
+
+def test_strided_coefficients_match_ddim_formula():
+    """Extension N1: the (c0, c1, 0) rows reproduce the DDIM eta=0 update of the oracle."""
+    import sys, os
+    from oracle import ref_torch as R
+    from diff import Diffuser
+    d = Diffuser(num_timesteps=1000, device="cpu")
+    coef, stride = d.strided_coefficients(20)
+    assert stride == 50 and tuple(coef.shape) == (1000, 3)
+    _, _, abars = R.schedule(1000)
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn((2, 4, 28, 28), generator=g)
+    eps = torch.randn((2, 4, 28, 28), generator=g)
+    for t in (1000, 550, 50):
+        c0, c1, c2 = (float(v) for v in coef[t - 1])
+        assert c2 == 0.0
+        got = (x - c0 * eps) / c1
+        want = R.ddim_update(x, eps, t, t - stride, abars)
+        assert float((got - want).abs().max()) < 2e-5 * float(want.abs().max())
+    # rows that are never visited are harmless (divide by one)
+    assert float(coef[998, 1]) == 1.0 and float(coef[998, 0]) == 0.0
+    import pytest
+    with pytest.raises(ValueError):
+        d.strided_coefficients(7)
