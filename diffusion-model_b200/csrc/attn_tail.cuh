@@ -1,0 +1,306 @@
+// Tail of the attention block as ONE kernel (models/unet_cond.py:36-50, after the MHA core):
+//
+//   o   = av Wp^T + bp + x_ln                (out_proj + the residual of the block)
+//   h   = LayerNorm(o)                       (ff_self.0)
+//   f1  = GELU(h W1^T + b1)                  (ff_self.1, ff_self.2)
+//   out = f1 W2^T + b2 + o                   (ff_self.3 + residual)
+//
+// Every step is local to a token (a PM row) and K = N = C <= 128, so a 128-row tile runs the
+// whole chain on chip: the three weight matrices stay resident in shared memory for the
+// lifetime of the (persistent) CTA, av / x_ln arrive by TMA, the three GEMMs are tcgen05 MMAs
+// into one TMEM accumulator, and the intermediate activations (o, h, f1) only ever exist as
+// bf16 tiles in shared memory.  HBM traffic per token: 2 C reads + C writes (bf16) instead of
+// the 11 C of the four separate launches (three Linear GEMMs + LayerNorm).
+//
+// The chain of one tile is strictly sequential (MMA -> epilogue -> MMA ...), so a CTA runs
+// kChains independent chains.  A chain is C / 32 warpgroups: a thread owns 32 columns of one row
+// for the epilogues (TMEM lane = row; warps with the same warp % 4 may read the same lanes, so
+// the columns of a row are split over warpgroups and the row's LayerNorm sums are exchanged
+// through shared memory); the chain's first warp issues its TMA loads and MMAs (warp-uniform
+// code, elect_one() around the asm only).  32 warps per SM keep the short dependent epilogue
+// sequences of several tiles in flight.  Buffers per chain: A (av -> h -> f1 -> out, each the
+// K-major 128B-swizzled operand of the next MMA / source of the TMA store) and R (x_ln -> o).
+// Rounding points are those of the separate launches (o, h, f1 and out are rounded to bf16);
+// the LayerNorm variance is the one-pass E[o^2] - mean^2 in fp32.
+#pragma once
+
+#include "common.cuh"
+
+namespace dmb {
+
+struct TailParams {
+  Geo geo;
+  int m_tiles;
+  const float* bp;     // out_proj bias
+  const float* ln_w;   // ff_self.0 weight / bias
+  const float* ln_b;
+  const float* b1;     // ff_self.1 bias
+  const float* b2;     // ff_self.3 bias
+};
+
+constexpr int kTailCols = 32;        // accumulator columns per thread
+constexpr int kTailThreads = 1024;   // kChains * (C / kTailCols) * 128 for both instantiations
+
+template <int C, int kChains>
+constexpr int attn_tail_smem_bytes() {
+  return 3 * C * C * 2 + kChains * 2 * (C / 64) * (128 * 128) + 1024;
+}
+
+template <int C, int kChains>
+__global__ void __launch_bounds__(kTailThreads, 1)
+attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_constant__ CUtensorMap tmap_xl,
+                 const __grid_constant__ CUtensorMap tmap_wp, const __grid_constant__ CUtensorMap tmap_w1,
+                 const __grid_constant__ CUtensorMap tmap_w2, const __grid_constant__ CUtensorMap tmap_out,
+                 const TailParams p) {
+  static_assert(C == 64 || C == 128, "weights of wider blocks do not fit in shared memory");
+  constexpr int kSplit = C / kTailCols;       // warpgroups sharing the columns of one tile
+  constexpr int kChainThreads = 128 * kSplit;
+  static_assert(kChains * kChainThreads == kTailThreads, "thread layout");
+  constexpr int kKC = C / 64;                 // 128-byte K chunks (= 64-column output blocks)
+  constexpr uint32_t kChunkBytes = 128 * 128; // one 128-row x 128-byte sub-tile
+  constexpr uint32_t kWChunkBytes = C * 128;  // one K chunk of a weight: C rows x 128 bytes
+  constexpr uint32_t kTmemCols = kChains * C; // 256
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t w_bar;
+  __shared__ __align__(8) uint64_t ld_bar[kChains];
+  __shared__ __align__(8) uint64_t mma_bar[kChains];
+  __shared__ uint32_t tmem_base_smem;
+
+  pdl_trigger();
+  const int warp = threadIdx.x >> 5;
+  const int chain = warp / (4 * kSplit);
+  const int split = (warp >> 2) % kSplit;       // which 32 columns of the row this thread owns
+  const int q = warp & 3;                       // TMEM lane quadrant of this warp
+  const bool lead = (warp % (4 * kSplit)) == 0; // the chain's first warp issues its TMA and MMAs
+  const int t = q * 32 + (threadIdx.x & 31);    // row of the tile
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  uint8_t* wsm = smem;                                         // [3][kKC][C rows][128 B]
+  uint8_t* bufA = smem + 3 * kKC * kWChunkBytes + chain * (2 * kKC * kChunkBytes);
+  uint8_t* bufR = bufA + kKC * kChunkBytes;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmap_av); tma_prefetch_desc(&tmap_xl); tma_prefetch_desc(&tmap_out);
+    tma_prefetch_desc(&tmap_wp); tma_prefetch_desc(&tmap_w1); tma_prefetch_desc(&tmap_w2);
+    mbar_init(&w_bar, 1);
+    for (int i = 0; i < kChains; ++i) { mbar_init(&ld_bar[i], 1); mbar_init(&mma_bar[i], 1); }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(&tmem_base_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();
+
+  if (threadIdx.x == 0) {   // the three weight matrices, once per CTA
+    mbar_expect_tx(&w_bar, 3 * kKC * kWChunkBytes);
+    for (int kc = 0; kc < kKC; ++kc) {
+      tma_load_2d(wsm + (0 * kKC + kc) * kWChunkBytes, &tmap_wp, &w_bar, kc * 64, 0);
+      tma_load_2d(wsm + (1 * kKC + kc) * kWChunkBytes, &tmap_w1, &w_bar, kc * 64, 0);
+      tma_load_2d(wsm + (2 * kKC + kc) * kWChunkBytes, &tmap_w2, &w_bar, kc * 64, 0);
+    }
+  }
+
+  const uint32_t idesc = umma_idesc(1u, 128, C);
+  const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(chain * C);
+  const int col0 = split * kTailCols;           // first column of this thread
+  const uint32_t t_row = d_tmem + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(col0);
+  const uint32_t a_addr = smem_u32(bufA);
+  const uint32_t w_addr = smem_u32(wsm);
+  const int bar_id = 1 + chain;
+  const int sw = t & 7;
+  // this thread's four 16-byte vectors of a row: chunk (col0 / 64), vectors j0 .. j0 + 3 of its 128 bytes
+  const uint32_t row_off = (col0 >> 6) * kChunkBytes + t * 128;
+  const int j0 = (col0 & 63) >> 3;
+  uint8_t* rowA = bufA + row_off;
+  uint8_t* rowR = bufR + row_off;
+  // LayerNorm partials of the row's column groups are exchanged through the (then idle) A buffer
+  float2* scratch = reinterpret_cast<float2*>(bufA);
+  uint32_t ph_ld = 0, ph_mma = 0;
+  bool w_ready = false;
+
+  // one GEMM of the chain: D = A(bufA) * W[which]^T, issued by the chain's first warp
+  auto issue_gemm = [&](int which) {
+    if (lead) {
+      tc_fence_after();
+      if (elect_one()) {
+#pragma unroll
+        for (int kc = 0; kc < kKC; ++kc) {
+          const uint64_t ad = umma_desc_sw128(a_addr + kc * kChunkBytes);
+          const uint64_t bd = umma_desc_sw128(w_addr + (which * kKC + kc) * kWChunkBytes);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_ss<false>(d_tmem, ad + (k * 2), bd + (k * 2), idesc, (kc > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&mma_bar[chain]);
+      }
+      __syncwarp();
+    }
+  };
+  auto wait_gemm = [&]() {
+    mbar_wait(&mma_bar[chain], ph_mma);
+    ph_mma ^= 1;
+    tc_fence_after();
+  };
+  auto load_vec8 = [&](const float* src, float* dst) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(src + 4));
+    dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; dst[3] = a.w; dst[4] = b.x; dst[5] = b.y; dst[6] = b.z; dst[7] = b.w;
+  };
+
+  // consecutive tiles go to different CTAs first, so a small launch still spreads over the chip
+  for (int tile = blockIdx.x + gridDim.x * chain; tile < p.m_tiles; tile += gridDim.x * kChains) {
+    const int m0 = tile * 128;
+    int b = 0, y = 0, x = 0;
+    const bool valid = geo_decode(p.geo, m0 + t, b, y, x);
+
+    if (lead) {
+      if (elect_one()) {
+        tma_store_wait_read<0>();   // the previous tile's store has read bufA
+        mbar_expect_tx(&ld_bar[chain], 2 * kKC * kChunkBytes);
+#pragma unroll
+        for (int kc = 0; kc < kKC; ++kc) {
+          tma_load_2d(bufA + kc * kChunkBytes, &tmap_av, &ld_bar[chain], kc * 64, m0);
+          tma_load_2d(bufR + kc * kChunkBytes, &tmap_xl, &ld_bar[chain], kc * 64, m0);
+        }
+      }
+      __syncwarp();
+    }
+    if (!w_ready) { mbar_wait(&w_bar, 0); w_ready = true; }
+    mbar_wait(&ld_bar[chain], ph_ld);
+    ph_ld ^= 1;
+    issue_gemm(0);
+    wait_gemm();
+
+    // ---- o = acc + bp + x_ln (kept in R as bf16); h = LayerNorm(o) -> A
+    {
+      float o[kTailCols];
+      tmem_ld32(t_row, o);
+      tmem_ld_wait();
+      float s = 0.f, ss = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint4* rp = reinterpret_cast<uint4*>(rowR + (((j0 + j) ^ sw) << 4));
+        const uint4 u = *rp;
+        const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&u);
+        float bv[8];
+        load_vec8(p.bp + col0 + 8 * j, bv);
+        uint4 w4;
+        __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 xr = __bfloat1622float2(hp[i]);
+          const __nv_bfloat162 ob = __floats2bfloat162_rn(o[8 * j + 2 * i] + bv[2 * i] + xr.x,
+                                                          o[8 * j + 2 * i + 1] + bv[2 * i + 1] + xr.y);
+          wp[i] = ob;
+          const float2 of = __bfloat1622float2(ob);   // LayerNorm sees the rounded o, as it would from HBM
+          o[8 * j + 2 * i] = of.x; o[8 * j + 2 * i + 1] = of.y;
+          s += of.x + of.y;
+          ss = fmaf(of.x, of.x, fmaf(of.y, of.y, ss));
+        }
+        *rp = w4;
+      }
+      scratch[split * 128 + t] = make_float2(s, ss);
+      named_bar_sync(bar_id, kChainThreads);
+      float ts = 0.f, tss = 0.f;
+#pragma unroll
+      for (int g = 0; g < kSplit; ++g) {   // the same order in every thread of the row
+        const float2 v = scratch[g * 128 + t];
+        ts += v.x; tss += v.y;
+      }
+      const float mean = ts * (1.0f / C);
+      const float rstd = rsqrtf(fmaxf(tss * (1.0f / C) - mean * mean, 0.f) + 1e-5f);
+      named_bar_sync(bar_id, kChainThreads);   // the partials are read: A may be overwritten
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float wv[8], bv[8];
+        load_vec8(p.ln_w + col0 + 8 * j, wv);
+        load_vec8(p.ln_b + col0 + 8 * j, bv);
+        uint4 w4;
+        __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          wp[i] = __floats2bfloat162_rn((o[8 * j + 2 * i] - mean) * rstd * wv[2 * i] + bv[2 * i],
+                                        (o[8 * j + 2 * i + 1] - mean) * rstd * wv[2 * i + 1] + bv[2 * i + 1]);
+        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
+      }
+    }
+    fence_async_proxy();
+    tc_fence_before();
+    named_bar_sync(bar_id, kChainThreads);
+    issue_gemm(1);
+    wait_gemm();
+
+    // ---- f1 = GELU(acc + b1) -> A
+    {
+      float v[kTailCols];
+      tmem_ld32(t_row, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float bv[8];
+        load_vec8(p.b1 + col0 + 8 * j, bv);
+        uint4 w4;
+        __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          wp[i] = __floats2bfloat162_rn(gelu_fast(v[8 * j + 2 * i] + bv[2 * i]), gelu_fast(v[8 * j + 2 * i + 1] + bv[2 * i + 1]));
+        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
+      }
+    }
+    fence_async_proxy();
+    tc_fence_before();
+    named_bar_sync(bar_id, kChainThreads);
+    issue_gemm(2);
+    wait_gemm();
+
+    // ---- out = acc + b2 + o -> A -> TMA store (pad pixels are stored as zeros)
+    {
+      float v[kTailCols];
+      tmem_ld32(t_row, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t off = ((j0 + j) ^ sw) << 4;
+        uint4 w4 = make_uint4(0u, 0u, 0u, 0u);
+        if (valid) {
+          const uint4 u = *reinterpret_cast<const uint4*>(rowR + off);
+          const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&u);
+          float bv[8];
+          load_vec8(p.b2 + col0 + 8 * j, bv);
+          __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 of = __bfloat1622float2(hp[i]);
+            wp[i] = __floats2bfloat162_rn(v[8 * j + 2 * i] + bv[2 * i] + of.x, v[8 * j + 2 * i + 1] + bv[2 * i + 1] + of.y);
+          }
+        }
+        *reinterpret_cast<uint4*>(rowA + off) = w4;
+      }
+    }
+    fence_async_proxy();
+    tc_fence_before();
+    named_bar_sync(bar_id, kChainThreads);
+    if (lead) {
+      if (elect_one()) {
+#pragma unroll
+        for (int kc = 0; kc < kKC; ++kc) tma_store_2d(&tmap_out, bufA + kc * kChunkBytes, kc * 64, m0);
+        tma_store_commit();
+      }
+      __syncwarp();
+    }
+  }
+  // a bulk-store group belongs to the thread that committed it; elect_one() picks the same lane
+  // every time in converged code, and waiting in every lane of the issuing warps is harmless
+  if (lead) tma_store_wait_all<0>();
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+}  // namespace dmb

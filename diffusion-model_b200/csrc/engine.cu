@@ -3,6 +3,7 @@
 //   T = float         : fp32 activations / weights, tcgen05 kind::tf32, fp32 accumulate
 #include "engine.cuh"
 #include "attention_tc.cuh"
+#include "attn_tail.cuh"
 
 #include <type_traits>
 
@@ -259,7 +260,11 @@ class Engine : public IEngine {
       DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
       DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+      DMB_CUDA(cudaFuncSetAttribute(attn_tail_kernel<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail_smem_bytes<64, 4>()));
+      DMB_CUDA(cudaFuncSetAttribute(attn_tail_kernel<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail_smem_bytes<128, 2>()));
     }
+    const char* fe = getenv("DMB200_FUSED_TAIL");
+    use_fused_tail_ = !(fe && fe[0] == '0');
     const char* bn = getenv("DMB200_BN256");
     g_allow_bn256 = !(bn && bn[0] == '0');
     const char* env = getenv("DMB200_CUDA_CORE_ATTENTION");
@@ -389,6 +394,7 @@ class Engine : public IEngine {
   cudaStream_t side_ = nullptr;
   cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
   bool use_pdl_ = false;   // DMB200_PDL=1: programmatic dependent launch (measured: no gain at batch 1, -1.6 % at 256)
+  bool use_fused_tail_ = true;   // DMB200_FUSED_TAIL=0: out_proj / LayerNorm / ff1 / ff2 as four launches
   bool use_acc4_ = true;   // DMB200_ACC4=0: two epilogue warpgroups for every launch
   int min_bn_ = 16;
   bool narrow_tiles_ = true;   // DMB200_NARROW_TILES=0: always the weight's own N tile
@@ -896,6 +902,33 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       DMB_CHECK_LAUNCH();
       count();
     });
+    if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+      if (use_fused_tail_ && (C == 64 || C == 128)) {
+        // out_proj + residual, LayerNorm, ff1 + GELU, ff2 + residual on chip (attn_tail.cuh)
+        Act<T> out = new_act(pool, nn, H, W, C, false);
+        const GemmW<T>&wp = gw_.at(p + ".proj"), &w1 = gw_.at(p + ".ff1"), &w2 = gw_.at(p + ".ff2");
+        TailParams tp{};
+        tp.geo = av.g;
+        tp.m_tiles = cdiv(av.g.rows_valid, kTileM);
+        tp.bp = wp.bias; tp.b1 = w1.bias; tp.b2 = w2.bias;
+        tp.ln_w = f(p + ".ff_self.0.weight");
+        tp.ln_b = f(p + ".ff_self.0.bias");
+        DMB_REQUIRE(tp.bp && tp.b1 && tp.b2, "attention-block linears carry biases");
+        ops.tag("attn_tail " + std::to_string(C) + " @" + std::to_string(H), 6.0 * tok * C * C, 3.0 * tok * C * sizeof(T));
+        ops.push_back([this, av, xl, out, wp, w1, w2, tp, C](cudaStream_t s) {
+          const int grid = std::min(tp.m_tiles, num_sms_);
+          if (C == 64)
+            launch(attn_tail_kernel<64, 4>, grid, kTailThreads, attn_tail_smem_bytes<64, 4>(), s, av.tmap, xl.tmap, wp.tmap_for(64),
+                   w1.tmap_for(64), w2.tmap_for(64), out.tmap, tp);
+          else
+            launch(attn_tail_kernel<128, 2>, grid, kTailThreads, attn_tail_smem_bytes<128, 2>(), s, av.tmap, xl.tmap, wp.tmap_for(128),
+                   w1.tmap_for(128), w2.tmap_for(128), out.tmap, tp);
+          DMB_CHECK_LAUNCH();
+          count();
+        });
+        return out;
+      }
+    }
     Act<T> o = new_act(pool, nn, H, W, C, false);
     lin_tag(C, C);
     ops.push_back(op_lin(av, gw_.at(p + ".proj"), o, 0, &xl));
