@@ -816,7 +816,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
             static_cast<double>(n_out) * total_vec * 8 * sizeof(T) * (residual ? 3 : 2));
     ops.push_back([this, raw, out, gamma, beta, mode, res, embproj, emb_off, splits](cudaStream_t s) {
       const dim3 grid(splits, out.g.n);
-#define DMB_GN_ARGS raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc, gamma, beta, res, embproj, emb_off, out.g, raw.C, out.p, raw.g.n
+#define DMB_GN_ARGS raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc, gamma, beta, res, embproj, emb_off, out.g, raw.C, out.p, raw.g.n, 1.0 / (static_cast<double>(raw.g.H) * raw.g.W * raw.C)
       if (mode == GN_GELU) launch(gn1_apply_kernel<T, GN_GELU>, grid, 256, 0, s, DMB_GN_ARGS);
       else if (mode == GN_RES_GELU) launch(gn1_apply_kernel<T, GN_RES_GELU>, grid, 256, 0, s, DMB_GN_ARGS);
       else if (mode == GN_ADD_EMB) launch(gn1_apply_kernel<T, GN_ADD_EMB>, grid, 256, 0, s, DMB_GN_ARGS);
@@ -957,8 +957,10 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     Act<T> cat = new_act(pool, x.g.n, skip.g.H, skip.g.W, skip.C + x.C, false);
     ops.tag("upcat", 0, 2.0 * cat.g.n * cat.g.H * cat.g.W * cat.C * sizeof(T));
     ops.push_back([this, x, skip, cat](cudaStream_t s) {
-      const long long total = static_cast<long long>(cat.g.n) * cat.g.H * cat.g.W * (cat.C / 8);
-      launch(upcat_kernel<T>, cdiv(total, 256), 256, 0, s, skip.p, skip.C, skip.g.n, x.p, x.g, x.C, cat.g, cat.p);
+      const int vpr = cat.C / 8;
+      const int quarter = cdiv(cdiv(static_cast<long long>(cat.g.H) * cat.g.W * vpr, kUpcatU), vpr) * vpr;
+      launch(upcat_kernel<T>, dim3(cdiv(quarter, 256), cat.g.n), 256, 0, s, skip.p, skip.C, skip.g.n, x.p, x.g, x.C, cat.g,
+             cat.p, quarter);
       DMB_CHECK_LAUNCH();
       count();
     });

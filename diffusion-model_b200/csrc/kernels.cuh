@@ -319,7 +319,7 @@ __global__ void __launch_bounds__(256, 3)
 gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats, int n_stat_tiles, int rows_alloc,
                  const float* __restrict__ gamma, const float* __restrict__ beta,
                  const T* __restrict__ residual, const float* __restrict__ embproj,
-                 int emb_off, Geo g, int C, T* __restrict__ out, int n_src) {
+                 int emb_off, Geo g, int C, T* __restrict__ out, int n_src, double inv_cnt) {
   pdl_trigger();
   pdl_wait();
   // `raw` holds n_src samples; output sample b reads raw sample b mod n_src (n_src < gridDim.y
@@ -336,17 +336,44 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   // sample reduces them in the same fixed order (double), so the result does not depend on
   // the sample's position in the batch nor on how the batch is sharded.
   __shared__ double red[2][8];
-  __shared__ float s_mean, s_rstd;
+  float mean, rstd;
   {
     double s1 = 0.0, s2 = 0.0;
     const size_t sbase = static_cast<size_t>(b_src) * g.S;
-    for (int rr = g.Wp + tid; rr < g.S; rr += 256) {
-      if (!geo_is_pixel(g, rr)) continue;
+    const int rows_iter = (g.S - g.Wp + 255) >> 8;   // rows per thread
+    if (rows_iter * n_stat_tiles <= 8) {
+      // all partials of the thread are loaded before any is used: one memory latency instead of
+      // one per row (this phase is a fixed cost in front of every CTA's streaming loop)
+      float2 v[8];
+      bool okv[8];
+      int it = 0, tn = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int sr = g.Wp + tid + (it << 8);
+        okv[k] = it < rows_iter && sr < g.S && geo_is_pixel(g, sr);
+        if (okv[k]) v[k] = rowstats[sbase + sr + static_cast<size_t>(tn) * rows_alloc];
+        if (++tn == n_stat_tiles) { tn = 0; ++it; }
+      }
       StatTree acc;   // the groups of a row join in the same aligned tree as the units inside a group
-      const float2* rs = rowstats + sbase + rr;
-      for (int tn = 0; tn < n_stat_tiles; ++tn) acc.add(rs[static_cast<size_t>(tn) * rows_alloc]);
-      const float2 a = acc.total();
-      s1 += a.x; s2 += a.y;
+      tn = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (okv[k]) acc.add(v[k]);
+        if (++tn == n_stat_tiles) {
+          if (acc.n) { const float2 a = acc.total(); s1 += a.x; s2 += a.y; }
+          acc.n = 0;
+          tn = 0;
+        }
+      }
+    } else {
+      for (int rr = g.Wp + tid; rr < g.S; rr += 256) {
+        if (!geo_is_pixel(g, rr)) continue;
+        StatTree acc;
+        const float2* rs = rowstats + sbase + rr;
+        for (int tn = 0; tn < n_stat_tiles; ++tn) acc.add(rs[static_cast<size_t>(tn) * rows_alloc]);
+        const float2 a = acc.total();
+        s1 += a.x; s2 += a.y;
+      }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -355,22 +382,19 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
     }
     if ((tid & 31) == 0) { red[0][tid >> 5] = s1; red[1][tid >> 5] = s2; }
     __syncthreads();
-    if (tid == 0) {
-      double t1 = 0.0, t2 = 0.0;
+    // every thread finishes the reduction itself (same order): no second barrier
+    double t1 = 0.0, t2 = 0.0;
 #pragma unroll
-      for (int w = 0; w < 8; ++w) { t1 += red[0][w]; t2 += red[1][w]; }
-      const double cnt = static_cast<double>(g.H) * g.W * C;
-      const double mean = t1 / cnt;
-      double var = t2 / cnt - mean * mean;
-      if (var < 0.0) var = 0.0;
-      s_mean = static_cast<float>(mean);
-      s_rstd = rsqrtf(static_cast<float>(var) + 1e-5f);
-    }
-    __syncthreads();
+    for (int w = 0; w < 8; ++w) { t1 += red[0][w]; t2 += red[1][w]; }
+    // inv_cnt = 1 / (H W C) from the host: no double-precision division on this path
+    const double dmean = t1 * inv_cnt;
+    double var = t2 * inv_cnt - dmean * dmean;
+    if (var < 0.0) var = 0.0;
+    mean = static_cast<float>(dmean);
+    rstd = rsqrtf(static_cast<float>(var) + 1e-5f);
   }
   float sc[8], sh[8];   // y = x * sc + sh  ==  (x - mean) * rstd * gamma + beta (+ emb)
   {
-    const float mean = s_mean, rstd = s_rstd;
     const float4 ga = *reinterpret_cast<const float4*>(gamma + c0), gb = *reinterpret_cast<const float4*>(gamma + c0 + 4);
     const float4 ba = *reinterpret_cast<const float4*>(beta + c0), bb = *reinterpret_cast<const float4*>(beta + c0 + 4);
     const float gm[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
@@ -473,43 +497,68 @@ __global__ void maxpool2_kernel(const T* __restrict__ in, Geo gi, Geo go, int C,
 
 // Up-stage input: cat([skip, pad(bilinear_x2_align_corners(x))], channel).
 // models/unet_cond.py:76, 87-97.  Output geometry = skip geometry.
+// grid = (chunks of the sample's H*W*C/8 vectors, n); a thread moves kUpcatU vectors of the same
+// channel group, all loads first (a 16-byte vector per thread does not keep HBM busy).
+constexpr int kUpcatU = 4;
 template <typename T>
-__global__ void upcat_kernel(const T* __restrict__ skip, int Cs, int n_skip, const T* __restrict__ xin, Geo gx,
-                             int Cx, Geo go, T* __restrict__ out) {
+__global__ void __launch_bounds__(256, 4)
+upcat_kernel(const T* __restrict__ skip, int Cs, int n_skip, const T* __restrict__ xin, Geo gx,
+             int Cx, Geo go, T* __restrict__ out, int quarter /* vectors per sample / kUpcatU, multiple of C/8 */) {
   pdl_trigger();
   pdl_wait();
   const int C = Cs + Cx;
   const int vpr = C / 8;
-  const long long total = static_cast<long long>(go.n) * go.H * go.W * vpr;
-  const long long v = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (v >= total) return;
-  const int c0 = static_cast<int>(v % vpr) * 8;
-  long long pix = v / vpr;
-  const int x = static_cast<int>(pix % go.W); pix /= go.W;
-  const int y = static_cast<int>(pix % go.H);
-  const int b = static_cast<int>(pix / go.H);
-  const int r = geo_row(go, b, y, x);
-  float o[8];
+  const int per_sample = go.H * go.W * vpr;
+  const int v0 = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v0 >= quarter) return;
+  const int b = blockIdx.y;
+  const int pix0 = v0 / vpr;
+  const int c0 = (v0 - pix0 * vpr) * 8;       // the same for all kUpcatU vectors: quarter % vpr == 0
+  const int pstep = quarter / vpr;
+  int row[kUpcatU], py[kUpcatU], px[kUpcatU];
+  bool ok[kUpcatU];
+#pragma unroll
+  for (int u = 0; u < kUpcatU; ++u) {
+    const int pix = pix0 + u * pstep;
+    ok[u] = v0 + u * quarter < per_sample;
+    py[u] = fdiv(pix, go.mW, go.W);
+    px[u] = pix - py[u] * go.W;
+    row[u] = geo_row(go, b, py[u], px[u]);
+  }
   if (c0 < Cs) {
     // the skip tensor may hold only the shared half of a guidance pair (n_skip = go.n / 2)
-    const int rs = b >= n_skip ? r - n_skip * go.S : r;
-    load8(skip + static_cast<size_t>(rs) * Cs + c0, o);
-  } else {
-    const int cx = c0 - Cs;
-    const int Hu = 2 * gx.H, Wu = 2 * gx.W;
+    const int shift = b >= n_skip ? n_skip * go.S : 0;
+    Raw8<T> r[kUpcatU];
+#pragma unroll
+    for (int u = 0; u < kUpcatU; ++u)
+      if (ok[u]) r[u].load(skip + static_cast<size_t>(row[u] - shift) * Cs + c0);
+#pragma unroll
+    for (int u = 0; u < kUpcatU; ++u)
+      if (ok[u]) r[u].store(out + static_cast<size_t>(row[u]) * C + c0);
+    return;
+  }
+  const int cx = c0 - Cs;
+  const int Hu = 2 * gx.H, Wu = 2 * gx.W;
+  // align_corners=True: src = dst * (in - 1) / (out - 1), computed in fp32 like ATen.
+  const float sy = (Hu > 1) ? static_cast<float>(gx.H - 1) / static_cast<float>(Hu - 1) : 0.f;
+  const float sx = (Wu > 1) ? static_cast<float>(gx.W - 1) / static_cast<float>(Wu - 1) : 0.f;
+#pragma unroll
+  for (int u = 0; u < kUpcatU; ++u) {
+    if (!ok[u]) continue;
+    const int y = py[u], x = px[u];
+    float o[8];
     if (y < Hu && x < Wu) {
-      // align_corners=True: src = dst * (in - 1) / (out - 1), computed in fp32 like ATen.
-      const float sy = (Hu > 1) ? static_cast<float>(gx.H - 1) / static_cast<float>(Hu - 1) : 0.f;
-      const float sx = (Wu > 1) ? static_cast<float>(gx.W - 1) / static_cast<float>(Wu - 1) : 0.f;
       const float fy = sy * y, fx = sx * x;
       const int y0 = static_cast<int>(fy), x0 = static_cast<int>(fx);
       const int y1 = y0 + ((y0 < gx.H - 1) ? 1 : 0), x1 = x0 + ((x0 < gx.W - 1) ? 1 : 0);
       const float ly1 = fy - y0, ly0 = 1.f - ly1, lx1 = fx - x0, lx0 = 1.f - lx1;
+      Raw8<T> q[4];
+      q[0].load(xin + static_cast<size_t>(geo_row(gx, b, y0, x0)) * Cx + cx);
+      q[1].load(xin + static_cast<size_t>(geo_row(gx, b, y0, x1)) * Cx + cx);
+      q[2].load(xin + static_cast<size_t>(geo_row(gx, b, y1, x0)) * Cx + cx);
+      q[3].load(xin + static_cast<size_t>(geo_row(gx, b, y1, x1)) * Cx + cx);
       float v00[8], v01[8], v10[8], v11[8];
-      load8(xin + static_cast<size_t>(geo_row(gx, b, y0, x0)) * Cx + cx, v00);
-      load8(xin + static_cast<size_t>(geo_row(gx, b, y0, x1)) * Cx + cx, v01);
-      load8(xin + static_cast<size_t>(geo_row(gx, b, y1, x0)) * Cx + cx, v10);
-      load8(xin + static_cast<size_t>(geo_row(gx, b, y1, x1)) * Cx + cx, v11);
+      q[0].unpack(v00); q[1].unpack(v01); q[2].unpack(v10); q[3].unpack(v11);
 #pragma unroll
       for (int i = 0; i < 8; ++i)
         o[i] = ly0 * (lx0 * v00[i] + lx1 * v01[i]) + ly1 * (lx0 * v10[i] + lx1 * v11[i]);
@@ -517,8 +566,8 @@ __global__ void upcat_kernel(const T* __restrict__ skip, int Cs, int n_skip, con
 #pragma unroll
       for (int i = 0; i < 8; ++i) o[i] = 0.f;
     }
+    store8(out + static_cast<size_t>(row[u]) * C + c0, o);
   }
-  store8(out + static_cast<size_t>(r) * C + c0, o);
 }
 
 // LayerNorm over the channels of every real pixel (token).  LPT = C/8 lanes share a token,
