@@ -169,6 +169,7 @@ struct Act {  // an activation in padded pixel-matrix layout
   int C = 0;
   Geo g;
   CUtensorMap tmap;
+  CUtensorMap tmap_halo;    // box of kHaloRows rows: the shared A window of a 3x3 kernel row (gemm_tc.cuh, kRow3)
   float2* stats = nullptr;  // [n_stat_tiles][rows_alloc] GroupNorm row partials (conv outputs only)
   int n_stat_tiles = 0;
 };
@@ -248,6 +249,12 @@ class Engine : public IEngine {
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    {
+      const char* re = getenv("DMB200_ROW3");   // 0: nine separate A tiles per K chunk
+      row3_ = re ? atoi(re) : 1;
+    }
     const char* pe = getenv("DMB200_PAIRS");
     use_pairs_ = pe ? (pe[0] - '0') : 1;
     const char* ne = getenv("DMB200_NARROW_TILES");
@@ -394,6 +401,7 @@ class Engine : public IEngine {
   cudaStream_t side_ = nullptr;
   cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
   bool use_pdl_ = false;   // DMB200_PDL=1: programmatic dependent launch (measured: no gain at batch 1, -1.6 % at 256)
+  int row3_ = 1;   // DMB200_ROW3=0: every tap of a 3x3 conv loads its own A tile
   bool use_fused_tail_ = true;   // DMB200_FUSED_TAIL=0: out_proj / LayerNorm / ff1 / ff2 as four launches
   bool use_acc4_ = true;   // DMB200_ACC4=0: two epilogue warpgroups for every launch
   int min_bn_ = 16;
@@ -628,7 +636,10 @@ Act<T> Engine<T>::new_act(Pool& pool, int n, int H, int W, int C, bool with_stat
   a.C = C;
   a.g = make_geo(n, H, W);
   a.p = pool.alloc_n<T>(static_cast<size_t>(a.g.rows_alloc) * C);
-  if (C % ElemTraits<T>::kChunkK == 0) a.tmap = make_tmap<T>(a.p, C, a.g.rows_alloc, kTileM);
+  if (C % ElemTraits<T>::kChunkK == 0) {
+    a.tmap = make_tmap<T>(a.p, C, a.g.rows_alloc, kTileM);
+    a.tmap_halo = make_tmap<T>(a.p, C, a.g.rows_alloc, kHaloRows);
+  }
   if (with_stats) {
     a.n_stat_tiles = stat_tiles;
     a.stats = pool.alloc_n<float2>(static_cast<size_t>(stat_tiles) * a.g.rows_alloc);
@@ -686,8 +697,15 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     if (group == 3) group = 2;
     while (group > 1 && ring / (group * pair_bytes) < 2) group >>= 1;
   }
+  // 3x3 convs: one 130-row A window per (kernel row, K chunk) shared by the row's three taps,
+  // when at least three such stages fit (N tile <= 128 for CTA pairs, <= 64 otherwise)
+  const int row3_stage = static_cast<int>(kHaloBytes) + 3 * (bn / ctas) * 128;
+  const bool row3 = row3_ && ntaps == 9 && !acc4 && ring / row3_stage >= 3 && shifts[1] == shifts[0] + 1 &&
+                    shifts[2] == shifts[1] + 1 && shifts[4] == shifts[3] + 1 && shifts[5] == shifts[4] + 1 &&
+                    shifts[7] == shifts[6] + 1 && shifts[8] == shifts[7] + 1;
+  if (row3) group = 1;
   p.group = group;
-  const int stage_bytes = group * pair_bytes;
+  const int stage_bytes = row3 ? row3_stage : group * pair_bytes;
   p.stages = std::min(kMaxStages, ring / stage_bytes);
   p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM * ctas, bn);
   p.tmem_cols = tmem_cols_for(bn * n_acc / 2);
@@ -709,7 +727,8 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = use_pdl_ ? 2 : 1;
-    if (group == 1) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1>, a.tmap, w.tmap_for(bn / 2), tout, p));
+    if (row3) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1, 2, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
+    else if (group == 1) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1>, a.tmap, w.tmap_for(bn / 2), tout, p));
     else if (group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2>, a.tmap, w.tmap_for(bn / 2), tout, p));
     else DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 4>, a.tmap, w.tmap_for(bn / 2), tout, p));
   } else {
@@ -719,6 +738,8 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
       if (group == 1) launch(gemm_tc_kernel<T, 1, 1, 4>, grid, kT4, smem, s, a.tmap, w.tmap_for(bn), tout, p);
       else if (group == 2) launch(gemm_tc_kernel<T, 1, 2, 4>, grid, kT4, smem, s, a.tmap, w.tmap_for(bn), tout, p);
       else launch(gemm_tc_kernel<T, 1, 4, 4>, grid, kT4, smem, s, a.tmap, w.tmap_for(bn), tout, p);
+    } else if (row3) {
+      launch(gemm_tc_kernel<T, 1, 1, 2, true>, grid, kGemmThreads, smem, s, a.tmap_halo, w.tmap_for(bn), tout, p);
     } else
     if (group == 1) launch(gemm_tc_kernel<T, 1, 1>, grid, kGemmThreads, smem, s, a.tmap, w.tmap_for(bn), tout, p);
     else if (group == 2) launch(gemm_tc_kernel<T, 1, 2>, grid, kGemmThreads, smem, s, a.tmap, w.tmap_for(bn), tout, p);

@@ -84,7 +84,19 @@ constexpr int gemm_staging_bytes(int acc) { return acc * kTileM * 128; }
 // launches (the Linear layers) are bound by the epilogue's dependent instruction stream: with
 // two warpgroups an SM scheduler holds two epilogue warps and issues in 23-38 % of its cycles
 // (ncu, profiles/r1_v3_ncu_full_up_path.md); four warpgroups (N tile <= 128) double that.
-template <typename T, int kCtas, int kGroup, int kAcc = 2>
+//
+// kRow3 (3x3 convolutions): the three taps of one kernel row are row shifts by -1 / 0 / +1 of the
+// same PM rows, so their A operands overlap in 127 of 128 rows.  A stage then holds ONE 130-row
+// A window (rows m0 + dy Wp - 1 ...) and the weight tiles of the row's three taps; the MMAs of
+// tap dx read the window at a start address 128 dx bytes further.  The 128B swizzle is an XOR
+// on shared-memory ADDRESS bits (TMA wrote the window with the same rule), so the shifted start
+// needs nothing else: descriptor base_offset stays 0 (measured on B200: base_offset = dx gives
+// wrong results, 0 is exact).  The A operand crosses the L2 -> SM fabric 3 times per K chunk
+// instead of 9, and that fabric, not the tensor pipe, is what bounds these launches (ncu:
+// 10-14 TB/s of xbar reads at 55-72 % tensor-pipe activity).
+constexpr int kHaloRows = kTileM + 2;
+constexpr uint32_t kHaloBytes = 136 * 128;   // 130 rows, padded to whole 8-row swizzle groups
+template <typename T, int kCtas, int kGroup, int kAcc = 2, bool kRow3 = false>
 __global__ void __launch_bounds__(gemm_threads(kAcc), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_out, const GemmParams p) {
@@ -109,7 +121,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const uint32_t a_bytes = kTileM * 128;
   const uint32_t b_bytes = static_cast<uint32_t>(p.block_n / kCtas) * 128;
   const uint32_t pair_bytes = a_bytes + b_bytes;                       // one (tap, K chunk) operand pair
-  const uint32_t stage_bytes = static_cast<uint32_t>(kGroup) * pair_bytes;
+  const uint32_t stage_bytes = kRow3 ? kHaloBytes + 3u * b_bytes : static_cast<uint32_t>(kGroup) * pair_bytes;
   uint8_t* staging = smem + static_cast<size_t>(p.stages) * stage_bytes;  // 1024-aligned (stage_bytes % 1024 == 0)
 
   if (warp == 0 && lane == 0) {
@@ -154,10 +166,40 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       const int m_tile = tile / p.n_tiles;
       const int m0 = (m_tile * kCtas + static_cast<int>(rank)) * kTileM;
       const int n0 = n_tile * p.block_n + static_cast<int>(rank) * (p.block_n / kCtas);
+      if constexpr (kRow3) {
+        // stage = (kernel row dy, K chunk): the 130-row window + the weight tiles of its three taps
+        int dy = 0, kc = 0;
+        for (int it = 0; it < 3 * p.k_chunks; ++it) {
+          const int a_row = m0 + p.a_shift[3 * dy + 1] - 1;
+          const int k_col = kc * Tr::kChunkK;
+          const int b0 = p.b_row[3 * dy] + n0, b1 = p.b_row[3 * dy + 1] + n0, b2 = p.b_row[3 * dy + 2] + n0;
+          if (++kc == p.k_chunks) { kc = 0; ++dy; }
+          uint8_t* sa = smem + stage * stage_bytes;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (elect_one()) {
+            if (kCtas == 1 || rank == 0) mbar_expect_tx(&full_bar[stage], (kHaloRows * 128u + 3u * b_bytes) * kCtas);
+            if constexpr (kCtas == 2) {
+              const uint32_t lead_bar = lead_full0 + stage * 8;
+              tma_load_2d_pair(sa, &tmap_a, lead_bar, k_col, a_row);
+              tma_load_2d_pair(sa + kHaloBytes, &tmap_b, lead_bar, k_col, b0);
+              tma_load_2d_pair(sa + kHaloBytes + b_bytes, &tmap_b, lead_bar, k_col, b1);
+              tma_load_2d_pair(sa + kHaloBytes + 2 * b_bytes, &tmap_b, lead_bar, k_col, b2);
+            } else {
+              tma_load_2d(sa, &tmap_a, &full_bar[stage], k_col, a_row);
+              tma_load_2d(sa + kHaloBytes, &tmap_b, &full_bar[stage], k_col, b0);
+              tma_load_2d(sa + kHaloBytes + b_bytes, &tmap_b, &full_bar[stage], k_col, b1);
+              tma_load_2d(sa + kHaloBytes + 2 * b_bytes, &tmap_b, &full_bar[stage], k_col, b2);
+            }
+          }
+          __syncwarp();
+          if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
+        }
+      }
       // (tap, K chunk) pairs are walked in order; the per-tap row offsets are looked up when
       // the tap changes, i.e. long before the next barrier wake-up needs them
       int tap = 0, kc = 0;
       int a_cur = m0 + p.a_shift[0], b_cur = p.b_row[0] + n0;
+      if constexpr (!kRow3)
       for (int it0 = 0; it0 < n_iter; it0 += kGroup) {
         int a_row[kGroup], b_row[kGroup], k_col[kGroup];
 #pragma unroll
@@ -205,6 +247,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         mbar_wait(&tmem_empty_bar[as], aph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * p.block_n;
+        if constexpr (kRow3) {
+          const int n3 = 3 * p.k_chunks;
+          for (int it = 0; it < n3; ++it) {
+            const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+            const uint64_t adesc0 = umma_desc_sw128(sa);
+            const uint64_t bdesc0 = umma_desc_sw128(sa + kHaloBytes);
+            const uint64_t bstep = static_cast<uint64_t>(b_bytes >> 4);
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            if (elect_one()) {
+#pragma unroll
+              for (int dx = 0; dx < 3; ++dx) {
+                // window rows dx .. dx + 127: start address + 128 dx bytes (16-byte units)
+                const uint64_t ad = adesc0 + static_cast<uint64_t>(dx * 8);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const uint32_t acc = (it > 0 || dx > 0 || k > 0) ? 1u : 0u;
+                  if constexpr (kCtas == 2) umma_ss_pair<Tr::kTf32>(d_tmem, ad + (k * 2), bdesc0 + dx * bstep + (k * 2), p.idesc, acc);
+                  else umma_ss<Tr::kTf32>(d_tmem, ad + (k * 2), bdesc0 + dx * bstep + (k * 2), p.idesc, acc);
+                }
+              }
+              if constexpr (kCtas == 2) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
+              if (it == n3 - 1) {
+                if constexpr (kCtas == 2) umma_commit_pair(&tmem_full_bar[as]); else umma_commit(&tmem_full_bar[as]);
+              }
+            }
+            __syncwarp();
+            if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
+          }
+        }
+        if constexpr (!kRow3)
         for (int it0 = 0; it0 < n_iter; it0 += kGroup) {
           const int cnt = min(kGroup, n_iter - it0);
           const uint32_t sa = smem_u32(smem + stage * stage_bytes);
