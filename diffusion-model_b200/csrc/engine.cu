@@ -313,7 +313,7 @@ class Engine : public IEngine {
   void reset_launches() override { launches_ = 0; }
 
  private:
-  static constexpr int kGemmSmemMax = 227 * 1024 - 2048;  // static smem (barriers, stat_part) comes out of the same 227 KB
+  static constexpr int kGemmSmemMax = 227 * 1024 - 1024;  // static smem (barriers, < 300 bytes) comes out of the same 227 KB
 
   // ---- weights
   const float* f(const std::string& name) const {
@@ -698,7 +698,7 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     while (group > 1 && ring / (group * pair_bytes) < 2) group >>= 1;
   }
   // 3x3 convs: one 130-row A window per (kernel row, K chunk) shared by the row's three taps,
-  // when at least three such stages fit (N tile <= 128 for CTA pairs, <= 64 otherwise)
+  // when at least three such stages fit (any N tile for CTA pairs, <= 128 otherwise)
   const int row3_stage = static_cast<int>(kHaloBytes) + 3 * (bn / ctas) * 128;
   const bool row3 = row3_ && ntaps == 9 && !acc4 && ring / row3_stage >= 3 && shifts[1] == shifts[0] + 1 &&
                     shifts[2] == shifts[1] + 1 && shifts[4] == shifts[3] + 1 && shifts[5] == shifts[4] + 1 &&

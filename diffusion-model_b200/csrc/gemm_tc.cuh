@@ -91,11 +91,12 @@ constexpr int gemm_staging_bytes(int acc) { return acc * kTileM * 128; }
 // tap dx read the window at a start address 128 dx bytes further.  The 128B swizzle is an XOR
 // on shared-memory ADDRESS bits (TMA wrote the window with the same rule), so the shifted start
 // needs nothing else: descriptor base_offset stays 0 (measured on B200: base_offset = dx gives
-// wrong results, 0 is exact).  The A operand crosses the L2 -> SM fabric 3 times per K chunk
+// wrong results, 0 is exact); for the same reason the windows need 128-byte, not 1024-byte,
+// alignment and are packed back to back behind the (1024-aligned) weight tiles.  The A operand crosses the L2 -> SM fabric 3 times per K chunk
 // instead of 9, and that fabric, not the tensor pipe, is what bounds these launches (ncu:
 // 10-14 TB/s of xbar reads at 55-72 % tensor-pipe activity).
 constexpr int kHaloRows = kTileM + 2;
-constexpr uint32_t kHaloBytes = 136 * 128;   // 130 rows, padded to whole 8-row swizzle groups
+constexpr uint32_t kHaloBytes = kHaloRows * 128;   // windows are packed back to back: the swizzle follows the address
 template <typename T, int kCtas, int kGroup, int kAcc = 2, bool kRow3 = false>
 __global__ void __launch_bounds__(gemm_threads(kAcc), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -122,7 +123,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const uint32_t b_bytes = static_cast<uint32_t>(p.block_n / kCtas) * 128;
   const uint32_t pair_bytes = a_bytes + b_bytes;                       // one (tap, K chunk) operand pair
   const uint32_t stage_bytes = kRow3 ? kHaloBytes + 3u * b_bytes : static_cast<uint32_t>(kGroup) * pair_bytes;
-  uint8_t* staging = smem + static_cast<size_t>(p.stages) * stage_bytes;  // 1024-aligned (stage_bytes % 1024 == 0)
+  // shared memory: [stage ring][epilogue staging]; kRow3: [staging][weight tiles of all stages][A windows]
+  const uint32_t staging_bytes = p.tma_store ? static_cast<uint32_t>(gemm_staging_bytes(kAcc)) : 0u;
+  uint8_t* staging = kRow3 ? smem : smem + static_cast<size_t>(p.stages) * stage_bytes;  // 1024-aligned (stage_bytes % 1024 == 0)
+  uint8_t* ring_b = smem + staging_bytes;                                       // kRow3: 3 weight tiles per stage
+  uint8_t* ring_a = ring_b + static_cast<size_t>(p.stages) * 3u * b_bytes;      // kRow3: one window per stage
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -174,21 +179,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           const int k_col = kc * Tr::kChunkK;
           const int b0 = p.b_row[3 * dy] + n0, b1 = p.b_row[3 * dy + 1] + n0, b2 = p.b_row[3 * dy + 2] + n0;
           if (++kc == p.k_chunks) { kc = 0; ++dy; }
-          uint8_t* sa = smem + stage * stage_bytes;
+          uint8_t* sa = ring_a + stage * kHaloBytes;
+          uint8_t* sb = ring_b + stage * 3u * b_bytes;
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (elect_one()) {
-            if (kCtas == 1 || rank == 0) mbar_expect_tx(&full_bar[stage], (kHaloRows * 128u + 3u * b_bytes) * kCtas);
+            if (kCtas == 1 || rank == 0) mbar_expect_tx(&full_bar[stage], stage_bytes * kCtas);
             if constexpr (kCtas == 2) {
               const uint32_t lead_bar = lead_full0 + stage * 8;
               tma_load_2d_pair(sa, &tmap_a, lead_bar, k_col, a_row);
-              tma_load_2d_pair(sa + kHaloBytes, &tmap_b, lead_bar, k_col, b0);
-              tma_load_2d_pair(sa + kHaloBytes + b_bytes, &tmap_b, lead_bar, k_col, b1);
-              tma_load_2d_pair(sa + kHaloBytes + 2 * b_bytes, &tmap_b, lead_bar, k_col, b2);
+              tma_load_2d_pair(sb, &tmap_b, lead_bar, k_col, b0);
+              tma_load_2d_pair(sb + b_bytes, &tmap_b, lead_bar, k_col, b1);
+              tma_load_2d_pair(sb + 2 * b_bytes, &tmap_b, lead_bar, k_col, b2);
             } else {
               tma_load_2d(sa, &tmap_a, &full_bar[stage], k_col, a_row);
-              tma_load_2d(sa + kHaloBytes, &tmap_b, &full_bar[stage], k_col, b0);
-              tma_load_2d(sa + kHaloBytes + b_bytes, &tmap_b, &full_bar[stage], k_col, b1);
-              tma_load_2d(sa + kHaloBytes + 2 * b_bytes, &tmap_b, &full_bar[stage], k_col, b2);
+              tma_load_2d(sb, &tmap_b, &full_bar[stage], k_col, b0);
+              tma_load_2d(sb + b_bytes, &tmap_b, &full_bar[stage], k_col, b1);
+              tma_load_2d(sb + 2 * b_bytes, &tmap_b, &full_bar[stage], k_col, b2);
             }
           }
           __syncwarp();
@@ -250,9 +256,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         if constexpr (kRow3) {
           const int n3 = 3 * p.k_chunks;
           for (int it = 0; it < n3; ++it) {
-            const uint32_t sa = smem_u32(smem + stage * stage_bytes);
-            const uint64_t adesc0 = umma_desc_sw128(sa);
-            const uint64_t bdesc0 = umma_desc_sw128(sa + kHaloBytes);
+            const uint64_t adesc0 = umma_desc_sw128(smem_u32(ring_a + stage * kHaloBytes));
+            const uint64_t bdesc0 = umma_desc_sw128(smem_u32(ring_b + stage * 3u * b_bytes));
             const uint64_t bstep = static_cast<uint64_t>(b_bytes >> 4);
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
