@@ -336,6 +336,20 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   // sample reduces them in the same fixed order (double), so the result does not depend on
   // the sample's position in the batch nor on how the batch is sharded.
   __shared__ double red[2][8];
+  // affine parameters (and the embedding row) do not depend on the statistics: their loads are
+  // issued first, so they are in flight together with the partials below
+  float gm[8], bt[8];
+  {
+    const float4 ga = *reinterpret_cast<const float4*>(gamma + c0), gb = *reinterpret_cast<const float4*>(gamma + c0 + 4);
+    const float4 ba = *reinterpret_cast<const float4*>(beta + c0), bb = *reinterpret_cast<const float4*>(beta + c0 + 4);
+    gm[0] = ga.x; gm[1] = ga.y; gm[2] = ga.z; gm[3] = ga.w; gm[4] = gb.x; gm[5] = gb.y; gm[6] = gb.z; gm[7] = gb.w;
+    bt[0] = ba.x; bt[1] = ba.y; bt[2] = ba.z; bt[3] = ba.w; bt[4] = bb.x; bt[5] = bb.y; bt[6] = bb.z; bt[7] = bb.w;
+    if (MODE == GN_ADD_EMB) {
+      const float* e = embproj + static_cast<size_t>(b) * kProjCols + emb_off + c0;
+      const float4 ea = *reinterpret_cast<const float4*>(e), eb = *reinterpret_cast<const float4*>(e + 4);
+      bt[0] += ea.x; bt[1] += ea.y; bt[2] += ea.z; bt[3] += ea.w; bt[4] += eb.x; bt[5] += eb.y; bt[6] += eb.z; bt[7] += eb.w;
+    }
+  }
   float mean, rstd;
   {
     double s1 = 0.0, s2 = 0.0;
@@ -394,21 +408,10 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
     rstd = rsqrtf(static_cast<float>(var) + 1e-5f);
   }
   float sc[8], sh[8];   // y = x * sc + sh  ==  (x - mean) * rstd * gamma + beta (+ emb)
-  {
-    const float4 ga = *reinterpret_cast<const float4*>(gamma + c0), gb = *reinterpret_cast<const float4*>(gamma + c0 + 4);
-    const float4 ba = *reinterpret_cast<const float4*>(beta + c0), bb = *reinterpret_cast<const float4*>(beta + c0 + 4);
-    const float gm[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
-    const float bt[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      sc[i] = rstd * gm[i];
-      sh[i] = fmaf(-mean, sc[i], bt[i]);
-    }
-    if (MODE == GN_ADD_EMB) {
-      const float* e = embproj + static_cast<size_t>(b) * kProjCols + emb_off + c0;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) sh[i] += e[i];
-    }
+  for (int i = 0; i < 8; ++i) {
+    sc[i] = rstd * gm[i];
+    sh[i] = fmaf(-mean, sc[i], bt[i]);
   }
   // rows of this CTA: [r_begin, r_end) of the sample's S rows, skipping the leading pad row
   const int rows = g.S - g.Wp;
