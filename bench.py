@@ -342,6 +342,28 @@ def run_native(args):
         "kernel_groups_ms_per_denoise_step": {k: round(v["ms_per_step"], 4) for k, v in groups.items()},
     }
 
+    # ---- BASELINE's second figure: batch-1 ms per denoise step (config 5, the generate_steps
+    # latency path): the CUDA-graph loop on one sample, with and without the per-step latent dump
+    batch1 = None
+    if rank == 0:
+        y1, v1, m1 = y[:1].contiguous(), vals[:1].contiguous(), mask[:1].contiguous()
+        n1 = min(T, 200)
+        res = {}
+        for dump in (False, True):
+            xd = torch.empty((n1, 1, 4, 28, 28), device=dev) if dump else None
+            x1 = ctx.philox_normal(1, seed=7, sample_offset=0, t=0)
+            ctx.sample_loop(x1, y1, 0, v1, m1, args.guidance, coef, T, n1, seed=5, x_dump=xd)
+            torch.cuda.synchronize()
+            x1 = ctx.philox_normal(1, seed=8, sample_offset=0, t=0)
+            b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            b0.record()
+            ctx.sample_loop(x1, y1, 0, v1, m1, args.guidance, coef, T, n1, seed=6, x_dump=xd)
+            b1.record()
+            torch.cuda.synchronize()
+            res["with_latent_dump" if dump else "plain"] = b0.elapsed_time(b1) / n1
+        batch1 = {"ms_per_denoise_step": res["plain"], "ms_per_denoise_step_with_latent_dump": res["with_latent_dump"],
+                  "steps_timed": n1, "note": "batch 1, CFG pair = 2 U-Net passes per step, CUDA-graph loop"}
+
     cpu = None
     if rank == 0 and not args.no_cpu_baseline:
         cpu = cpu_reference_sample(min(B, 16), args.cpu_sample_steps, T, args.guidance)
@@ -371,6 +393,7 @@ def run_native(args):
             "roofline": roofline,
             "cpu_baseline": cpu,
             "ms_per_denoise_step": ms_total / args.steps / T,
+            "batch1": batch1,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
