@@ -270,6 +270,12 @@ class Engine : public IEngine {
       DMB_CUDA(cudaFuncSetAttribute(attn_tail_kernel<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail_smem_bytes<64, 4>()));
       DMB_CUDA(cudaFuncSetAttribute(attn_tail_kernel<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail_smem_bytes<128, 2>()));
     }
+    {
+      const char* le = getenv("DMB200_FUSE_LN1");
+      fuse_ln1_ = !(le && le[0] == '0');
+      const char* ke = getenv("DMB200_KEEP_TAPS");
+      keep_taps_ = ke && ke[0] == '1';
+    }
     const char* fe = getenv("DMB200_FUSED_TAIL");
     use_fused_tail_ = !(fe && fe[0] == '0');
     const char* bn = getenv("DMB200_BN256");
@@ -401,6 +407,8 @@ class Engine : public IEngine {
   cudaStream_t side_ = nullptr;
   cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
   bool use_pdl_ = false;   // DMB200_PDL=1: programmatic dependent launch (measured: no gain at batch 1, -1.6 % at 256)
+  bool fuse_ln1_ = true;    // DMB200_FUSE_LN1=0: the attention block's first LayerNorm as its own launch
+  bool keep_taps_ = false;  // DMB200_KEEP_TAPS=1: also store the un-normalised stage outputs (down1.. up3 taps)
   int row3_ = 1;   // DMB200_ROW3=0: every tap of a 3x3 conv loads its own A tile
   bool use_fused_tail_ = true;   // DMB200_FUSED_TAIL=0: out_proj / LayerNorm / ff1 / ff2 as four launches
   bool use_acc4_ = true;   // DMB200_ACC4=0: two epilogue warpgroups for every launch
@@ -816,10 +824,30 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   }
 
   bool emb_joined = false;
+  // `ln_name` (GN_ADD_EMB only): the LayerNorm of the attention block that follows is applied in
+  // the same kernel and the returned activation is LayerNorm(x); `pre_tap` then holds the
+  // un-normalised x when the context keeps taps (DMB200_KEEP_TAPS=1, the parity tests).
+  Act<T> pre_tap;
+  bool have_pre_tap = false, last_gn_fused_ln = false;
   auto gn = [&](const Act<T>& raw, const std::string& gname, int mode, const Act<T>* residual, int emb_off,
-                int n_out = 0) {
+                int n_out = 0, const std::string& ln_name = std::string()) {
     if (n_out == 0) n_out = raw.g.n;
     Act<T> out = new_act(pool, n_out, raw.g.H, raw.g.W, raw.C, false);
+    // fused where the launch is latency-bound (small maps / small batch: one launch and one pass
+    // less); on large activations the two streaming kernels are faster than the fused one, whose
+    // per-token shuffles make it issue-bound (measured at batch 256: 57 vs 34 + 15 us at 28x28)
+    const bool fuse_ln = !ln_name.empty() &&
+                         static_cast<size_t>(n_out) * raw.g.H * raw.g.W * raw.C * sizeof(T) <= (4u << 20);
+    const float* ln_w = fuse_ln ? f(ln_name + ".weight") : nullptr;
+    const float* ln_b = fuse_ln ? f(ln_name + ".bias") : nullptr;
+    T* pre = nullptr;
+    have_pre_tap = false;
+    last_gn_fused_ln = fuse_ln;
+    if (fuse_ln && keep_taps_) {
+      pre_tap = new_act(pool, n_out, raw.g.H, raw.g.W, raw.C, false);
+      pre = pre_tap.p;
+      have_pre_tap = true;
+    }
     const float* gamma = f(gname + ".weight");
     const float* beta = f(gname + ".bias");
     const T* res = residual ? residual->p : nullptr;
@@ -835,9 +863,17 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     }
     ops.tag("gn1_apply " + std::to_string(raw.C) + " @" + std::to_string(raw.g.H) + " m" + std::to_string(mode), 0,
             static_cast<double>(n_out) * total_vec * 8 * sizeof(T) * (residual ? 3 : 2));
-    ops.push_back([this, raw, out, gamma, beta, mode, res, embproj, emb_off, splits](cudaStream_t s) {
+    ops.push_back([this, raw, out, gamma, beta, mode, res, embproj, emb_off, splits, fuse_ln, ln_w, ln_b, pre](cudaStream_t s) {
       const dim3 grid(splits, out.g.n);
-#define DMB_GN_ARGS raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc, gamma, beta, res, embproj, emb_off, out.g, raw.C, out.p, raw.g.n, 1.0 / (static_cast<double>(raw.g.H) * raw.g.W * raw.C)
+      if (fuse_ln) {
+        launch(gn1_apply_kernel<T, GN_ADD_EMB, true>, grid, 256, 0, s, raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc,
+               gamma, beta, res, embproj, emb_off, out.g, raw.C, out.p, raw.g.n,
+               1.0 / (static_cast<double>(raw.g.H) * raw.g.W * raw.C), ln_w, ln_b, pre);
+        DMB_CHECK_LAUNCH();
+        count();
+        return;
+      }
+#define DMB_GN_ARGS raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc, gamma, beta, res, embproj, emb_off, out.g, raw.C, out.p, raw.g.n, 1.0 / (static_cast<double>(raw.g.H) * raw.g.W * raw.C), static_cast<const float*>(nullptr), static_cast<const float*>(nullptr), static_cast<T*>(nullptr)
       if (mode == GN_GELU) launch(gn1_apply_kernel<T, GN_GELU>, grid, 256, 0, s, DMB_GN_ARGS);
       else if (mode == GN_RES_GELU) launch(gn1_apply_kernel<T, GN_RES_GELU>, grid, 256, 0, s, DMB_GN_ARGS);
       else if (mode == GN_ADD_EMB) launch(gn1_apply_kernel<T, GN_ADD_EMB>, grid, 256, 0, s, DMB_GN_ARGS);
@@ -858,13 +894,15 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   };
   // ResBlock (models/unet_cond.py:10-30); last_mode is what follows the second GroupNorm.
   auto resblock = [&](const Act<T>& in, const std::string& p, bool residual, int last_mode, int emb_off,
-                      int n_out = 0) {
+                      int n_out = 0, const std::string& ln_name = std::string()) {
     Act<T> r1 = conv(in, p + ".double_conv.0.weight");
     Act<T> h = gn(r1, p + ".double_conv.1", GN_GELU, nullptr, 0);
     Act<T> r2 = conv(h, p + ".double_conv.3.weight");
-    return gn(r2, p + ".double_conv.4", residual ? GN_RES_GELU : last_mode, residual ? &in : nullptr, emb_off, n_out);
+    return gn(r2, p + ".double_conv.4", residual ? GN_RES_GELU : last_mode, residual ? &in : nullptr, emb_off, n_out,
+              ln_name);
   };
-  auto attention = [&](const Act<T>& x, const std::string& p) {
+  // x_is_normed: the producing GroupNorm kernel already applied this block's first LayerNorm
+  auto attention = [&](const Act<T>& x, const std::string& p, bool x_is_normed) {
     const int C = x.C, H = x.g.H, W = x.g.W, nn = x.g.n;
     auto ln = [&](const Act<T>& in, const std::string& name) {
       Act<T> out = new_act(pool, nn, H, W, C, false);
@@ -883,7 +921,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       });
       return out;
     };
-    Act<T> xl = ln(x, p + ".ln");
+    Act<T> xl = x_is_normed ? x : ln(x, p + ".ln");
     Act<T> qkv = new_act(pool, nn, H, W, 3 * C, false);
     const double tok = static_cast<double>(nn) * H * W;
     auto lin_tag = [&](int K, int N) {
@@ -962,7 +1000,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.push_back(op_lin(f1, gw_.at(p + ".ff2"), out, 0, &o));
     return out;
   };
-  auto down = [&](const Act<T>& x, const std::string& p, int emb_off, int n_out = 0) {
+  auto down = [&](const Act<T>& x, const std::string& p, int emb_off, const std::string& ln_name, int n_out = 0) {
     Act<T> pooled = new_act(pool, x.g.n, x.g.H / 2, x.g.W / 2, x.C, false);
     ops.tag("maxpool", 0, 1.25 * pooled.g.n * x.g.H * x.g.W * x.C * sizeof(T));
     ops.push_back([this, x, pooled](cudaStream_t s) {
@@ -972,9 +1010,9 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       count();
     });
     Act<T> a = resblock(pooled, p + ".maxpool_conv.1", true, GN_NONE, 0);
-    return resblock(a, p + ".maxpool_conv.2", false, GN_ADD_EMB, emb_off, n_out);
+    return resblock(a, p + ".maxpool_conv.2", false, GN_ADD_EMB, emb_off, n_out, ln_name);
   };
-  auto up = [&](const Act<T>& x, const Act<T>& skip, const std::string& p, int emb_off) {
+  auto up = [&](const Act<T>& x, const Act<T>& skip, const std::string& p, int emb_off, const std::string& ln_name) {
     Act<T> cat = new_act(pool, x.g.n, skip.g.H, skip.g.W, skip.C + x.C, false);
     ops.tag("upcat", 0, 2.0 * cat.g.n * cat.g.H * cat.g.W * cat.C * sizeof(T));
     ops.push_back([this, x, skip, cat](cudaStream_t s) {
@@ -986,7 +1024,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       count();
     });
     Act<T> a = resblock(cat, p + ".conv.0", true, GN_NONE, 0);
-    return resblock(a, p + ".conv.1", false, GN_ADD_EMB, emb_off);
+    return resblock(a, p + ".conv.1", false, GN_ADD_EMB, emb_off, 0, ln_name);
   };
 
   // Classifier-free guidance runs the conditional and the unconditional sample of a pair
@@ -1016,21 +1054,30 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   Act<T> r1 = conv(h0, "inc.double_conv.3.weight");
   Act<T> x1 = gn(r1, "inc.double_conv.4", GN_NONE, nullptr, 0);
   P.taps["inc"] = x1;
-  Act<T> x2 = down(x1, "down1", 0, n);    P.taps["down1"] = x2;
-  x2 = attention(x2, "sa1");              P.taps["sa1"] = x2;
-  Act<T> x3 = down(x2, "down2", 128);     P.taps["down2"] = x3;
-  x3 = attention(x3, "sa2");              P.taps["sa2"] = x3;
-  Act<T> x4 = down(x3, "down3", 384);     P.taps["down3"] = x4;
-  x4 = attention(x4, "sa3");              P.taps["sa3"] = x4;
+  // each down / up stage ends in GroupNorm + embedding add and feeds an attention block whose
+  // first LayerNorm is applied by the same kernel (fuse_ln1_)
+  auto lnn = [&](const char* sa) { return fuse_ln1_ ? std::string(sa) + ".ln" : std::string(); };
+  bool normed = false;   // did the stage's last GroupNorm kernel apply the LayerNorm?
+  auto stage_tap = [&](const char* name, const Act<T>& stage_out) {
+    normed = last_gn_fused_ln;
+    if (!normed) P.taps[name] = stage_out;
+    else if (have_pre_tap) P.taps[name] = pre_tap;
+  };
+  Act<T> x2 = down(x1, "down1", 0, lnn("sa1"), n);   stage_tap("down1", x2);
+  x2 = attention(x2, "sa1", normed);                 P.taps["sa1"] = x2;
+  Act<T> x3 = down(x2, "down2", 128, lnn("sa2"));    stage_tap("down2", x3);
+  x3 = attention(x3, "sa2", normed);                 P.taps["sa2"] = x3;
+  Act<T> x4 = down(x3, "down3", 384, lnn("sa3"));    stage_tap("down3", x4);
+  x4 = attention(x4, "sa3", normed);                 P.taps["sa3"] = x4;
   x4 = resblock(x4, "bot1", false, GN_NONE, 0);  P.taps["bot1"] = x4;
   x4 = resblock(x4, "bot2", false, GN_NONE, 0);  P.taps["bot2"] = x4;
   x4 = resblock(x4, "bot3", false, GN_NONE, 0);  P.taps["bot3"] = x4;
-  Act<T> u = up(x4, x3, "up1", 640);      P.taps["up1"] = u;
-  u = attention(u, "sa4");                P.taps["sa4"] = u;
-  u = up(u, x2, "up2", 768);              P.taps["up2"] = u;
-  u = attention(u, "sa5");                P.taps["sa5"] = u;
-  u = up(u, x1, "up3", 832);              P.taps["up3"] = u;
-  u = attention(u, "sa6");                P.taps["sa6"] = u;
+  Act<T> u = up(x4, x3, "up1", 640, lnn("sa4"));     stage_tap("up1", u);
+  u = attention(u, "sa4", normed);                   P.taps["sa4"] = u;
+  u = up(u, x2, "up2", 768, lnn("sa5"));             stage_tap("up2", u);
+  u = attention(u, "sa5", normed);                   P.taps["sa5"] = u;
+  u = up(u, x1, "up3", 832, lnn("sa6"));             stage_tap("up3", u);
+  u = attention(u, "sa6", normed);                   P.taps["sa6"] = u;
   P.feat = u;
 }
 

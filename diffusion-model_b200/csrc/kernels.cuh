@@ -314,12 +314,19 @@ enum GnMode : int { GN_NONE = 0, GN_GELU = 1, GN_RES_GELU = 2, GN_ADD_EMB = 3 };
 // stay zero in `out`).  grid = (splits, n).  MODE is a template parameter to keep the
 // register count low enough for 4 CTAs per SM (the erf GELU makes this kernel issue-bound
 // as much as HBM-bound).
-template <typename T, int MODE>
+// kLN (with GN_ADD_EMB, C <= 256): the block's output feeds nn.LayerNorm(C) per token and
+// nothing else (unet_cond.py:47: x_ln = x = self.ln(x)), and the C/8 lanes that share a row sit
+// in one warp, so the LayerNorm is applied here -- on the bf16-rounded value, exactly what the
+// separate launch would have read back -- and `out` receives LayerNorm(x); the un-normalised x
+// is stored to `out_pre` only when the caller keeps it for inspection (taps).
+template <typename T, int MODE, bool kLN = false>
 __global__ void __launch_bounds__(256, 3)
 gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats, int n_stat_tiles, int rows_alloc,
                  const float* __restrict__ gamma, const float* __restrict__ beta,
                  const T* __restrict__ residual, const float* __restrict__ embproj,
-                 int emb_off, Geo g, int C, T* __restrict__ out, int n_src, double inv_cnt) {
+                 int emb_off, Geo g, int C, T* __restrict__ out, int n_src, double inv_cnt,
+                 const float* __restrict__ ln_w = nullptr, const float* __restrict__ ln_b = nullptr,
+                 T* __restrict__ out_pre = nullptr) {
   pdl_trigger();
   pdl_wait();
   // `raw` holds n_src samples; output sample b reads raw sample b mod n_src (n_src < gridDim.y
@@ -419,7 +426,17 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   const int r_begin = g.Wp + blockIdx.x * per;
   const int r_end = min(g.S, r_begin + per);
   const size_t base = static_cast<size_t>(b) * g.S;
-  constexpr int U = (MODE == GN_RES_GELU) ? 4 : 8;  // 16-byte loads in flight per thread and stream
+  constexpr int U = (MODE == GN_RES_GELU || kLN) ? 4 : 8;  // 16-byte loads in flight per thread and stream
+  float lw[8], lb[8];
+  uint32_t row_mask = 0xffffffffu;   // the lanes that share this thread's row
+  if constexpr (kLN) {
+    const float4 wa = *reinterpret_cast<const float4*>(ln_w + c0), wb = *reinterpret_cast<const float4*>(ln_w + c0 + 4);
+    const float4 ba = *reinterpret_cast<const float4*>(ln_b + c0), bb = *reinterpret_cast<const float4*>(ln_b + c0 + 4);
+    lw[0] = wa.x; lw[1] = wa.y; lw[2] = wa.z; lw[3] = wa.w; lw[4] = wb.x; lw[5] = wb.y; lw[6] = wb.z; lw[7] = wb.w;
+    lb[0] = ba.x; lb[1] = ba.y; lb[2] = ba.z; lb[3] = ba.w; lb[4] = bb.x; lb[5] = bb.y; lb[6] = bb.z; lb[7] = bb.w;
+    if (vpr < 32) row_mask = ((1u << vpr) - 1u) << ((tid & 31) & ~(vpr - 1));
+  }
+  T* pp = nullptr;
   // Incremental addressing: the row advances by rows_per_iter per load, its column inside the
   // padded image row (x) is tracked modulo Wp, so the loop has no division and no 64-bit
   // multiply.
@@ -430,6 +447,7 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   const T* rp = raw + (static_cast<size_t>(b_src) * g.S + rr) * C + c0;
   const T* sp = (MODE == GN_RES_GELU) ? residual + first : nullptr;
   T* op = out + first;
+  if constexpr (kLN) pp = out_pre ? out_pre + first : nullptr;
   const int stride = rows_per_iter * C;
   while (rr < r_end) {
     Raw8<T> xr[U], rs[U];
@@ -460,6 +478,24 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
 #pragma unroll
           for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>(rv[i] + xv[i]);
         }
+        if constexpr (kLN) {
+          // (the lanes of a row take this branch together: ok[u] depends on the row only)
+#pragma unroll
+          for (int i = 0; i < 8; ++i) xv[i] = to_f32(from_f32<T>(xv[i]));   // what the stored tensor holds
+          if (pp) store8(pp + u * stride, xv);
+          float sum = 0.f;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) sum += xv[i];
+          for (int o = vpr >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(row_mask, sum, o);
+          const float mu = sum / static_cast<float>(C);
+          float q = 0.f;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { const float d = xv[i] - mu; q += d * d; }
+          for (int o = vpr >> 1; o > 0; o >>= 1) q += __shfl_xor_sync(row_mask, q, o);
+          const float rs_ln = rsqrtf(q / static_cast<float>(C) + 1e-5f);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) xv[i] = (xv[i] - mu) * rs_ln * lw[i] + lb[i];
+        }
         store8(op + u * stride, xv);
       }
     }
@@ -467,6 +503,7 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
     rp += U * stride;
     if (MODE == GN_RES_GELU) sp += U * stride;
     op += U * stride;
+    if constexpr (kLN) { if (pp) pp += U * stride; }
   }
 }
 

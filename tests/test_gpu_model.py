@@ -244,7 +244,8 @@ def test_launches_are_counted(models):
     g = torch.Generator().manual_seed(1)
     x = torch.randn((1, 4, 28, 28), generator=g).to(DEV)
     unet(x, torch.tensor([5], device=DEV), torch.tensor([1], device=DEV))
-    assert ctx.launch_count() > 100
+    # one forward is ~100 launches of this library's kernels (fewer as launches get fused)
+    assert ctx.launch_count() >= 80
 
 
 def test_strided_ddim_extension_matches_oracle(models):
@@ -289,7 +290,7 @@ def _fresh_context(env):
                 os.environ[k] = v
 
 
-@pytest.mark.parametrize("switch", ["DMB200_FUSED_TAIL", "DMB200_ROW3"])
+@pytest.mark.parametrize("switch", ["DMB200_FUSED_TAIL", "DMB200_ROW3", "DMB200_FUSE_LN1"])
 def test_fused_kernels_agree_with_separate_launches(models, switch):
     """The fused attention-block tail (attn_tail_kernel) and the kernel-row A windows of the 3x3
     convs (kRow3) are re-schedulings of the same arithmetic: the U-Net output must agree with the
@@ -320,4 +321,7 @@ def test_fused_kernels_agree_with_separate_launches(models, switch):
     report(f"variant_{switch}", {"rel_l2": r, "launches": launches})
     if switch == "DMB200_FUSED_TAIL":   # the switch took effect: 4 fused blocks x 3 launches saved
         assert launches[1] - launches[0] == 12, launches
+    if switch == "DMB200_FUSE_LN1":     # 6 LayerNorm launches saved; same arithmetic in the same order
+        assert launches[1] - launches[0] == 6, launches
+        assert r < 1e-6, r
     assert r < 1e-2, (switch, r)
