@@ -60,6 +60,24 @@ CUtensorMap make_tmap(const void* base, uint64_t inner, uint64_t rows, uint32_t 
   return m;
 }
 
+// 3D view of a PM activation: (channel, PM row inside the sample, sample), box = {128 bytes of
+// channels, 1 row, 128 samples}: the A / output tile of the pixel-major conv mode (gemm_tc.cuh).
+template <typename T>
+CUtensorMap make_tmap_samples(const void* base, uint64_t C, uint64_t S, uint64_t n) {
+  CUtensorMap m;
+  memset(&m, 0, sizeof(m));
+  const cuuint64_t gdim[3] = {C, S, n};
+  const cuuint64_t gstride[2] = {C * sizeof(T), S * C * sizeof(T)};
+  const cuuint32_t box[3] = {static_cast<cuuint32_t>(ElemTraits<T>::kChunkK), 1, static_cast<cuuint32_t>(kTileM)};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUtensorMapDataType dt = sizeof(T) == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  CUresult r = encode_tiled_fn()(&m, dt, 3, const_cast<void*>(base), gdim, gstride, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) fail(3, "cuTensorMapEncodeTiled (3D) failed with code " + std::to_string(static_cast<int>(r)));
+  return m;
+}
+
 // ---------------------------------------------------------------------------
 // Device memory owned by the engine.
 // ---------------------------------------------------------------------------
@@ -169,6 +187,8 @@ struct Act {  // an activation in padded pixel-matrix layout
   int C = 0;
   Geo g;
   CUtensorMap tmap;
+  CUtensorMap tmap_samples; // 3D (channel, row of the sample, sample) view: pixel-major conv mode on small maps
+  bool has_samples_map = false;
   CUtensorMap tmap_halo;    // box of kHaloRows rows: the shared A window of a 3x3 kernel row (gemm_tc.cuh, kRow3)
   float2* stats = nullptr;  // [n_stat_tiles][rows_alloc] GroupNorm row partials (conv outputs only)
   int n_stat_tiles = 0;
@@ -252,6 +272,10 @@ class Engine : public IEngine {
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     {
+      const char* pe3 = getenv("DMB200_PIX");
+      pix_mode_ = !(pe3 && pe3[0] == '0');
+      if (const char* e = getenv("DMB200_PIX_MINKN")) pix_min_kn_ = atoll(e);
+      if (const char* e = getenv("DMB200_PIX_FILL")) pix_fill_pct_ = atoi(e);
       const char* re = getenv("DMB200_ROW3");   // 0: nine separate A tiles per K chunk
       row3_ = re ? atoi(re) : 1;
     }
@@ -409,6 +433,9 @@ class Engine : public IEngine {
   bool use_pdl_ = false;   // DMB200_PDL=1: programmatic dependent launch (measured: no gain at batch 1, -1.6 % at 256)
   bool fuse_ln1_ = true;    // DMB200_FUSE_LN1=0: the attention block's first LayerNorm as its own launch
   bool keep_taps_ = false;  // DMB200_KEEP_TAPS=1: also store the un-normalised stage outputs (down1.. up3 taps)
+  long long pix_min_kn_ = 256 * 256;   // pixel-major only for C_in * C_out >= this
+  int pix_fill_pct_ = 90;              // narrow the N tile while there are fewer tiles than this share of the SMs
+  bool pix_mode_ = true;   // DMB200_PIX=0: small maps keep the padded-row GEMM at every batch size
   int row3_ = 1;   // DMB200_ROW3=0: every tap of a 3x3 conv loads its own A tile
   bool use_fused_tail_ = true;   // DMB200_FUSED_TAIL=0: out_proj / LayerNorm / ff1 / ff2 as four launches
   bool use_acc4_ = true;   // DMB200_ACC4=0: two epilogue warpgroups for every launch
@@ -647,6 +674,10 @@ Act<T> Engine<T>::new_act(Pool& pool, int n, int H, int W, int C, bool with_stat
   if (C % ElemTraits<T>::kChunkK == 0) {
     a.tmap = make_tmap<T>(a.p, C, a.g.rows_alloc, kTileM);
     a.tmap_halo = make_tmap<T>(a.p, C, a.g.rows_alloc, kHaloRows);
+    if (H * W <= 64) {
+      a.tmap_samples = make_tmap_samples<T>(a.p, C, a.g.S, n);
+      a.has_samples_map = true;
+    }
   }
   if (with_stats) {
     a.n_stat_tiles = stat_tiles;
@@ -671,21 +702,48 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     p.b_row[i] = (phase * ntaps + i) * w.rows_per_tap;
   }
   p.k_chunks = w.K / ElemTraits<T>::kChunkK;
-  const int bn = effective_bn(w, a.g.rows_valid);
+  // Pixel-major mode for 3x3 convs on small maps at large batch (gemm_tc.cuh, PixTile)
+  const bool conv3 = ntaps == 9 && shifts[1] == shifts[0] + 1 && shifts[2] == shifts[1] + 1 &&
+                     shifts[4] == shifts[3] + 1 && shifts[5] == shifts[4] + 1 && shifts[7] == shifts[6] + 1 &&
+                     shifts[8] == shifts[7] + 1 && shifts[3] == shifts[0] + a.g.Wp && shifts[6] == shifts[3] + a.g.Wp;
+  const int HW = a.g.H * a.g.W;
+  bool pix = pix_mode_ && conv3 && a.g.H <= 7 && a.g.W <= 7 && a.g.n >= 2 * kTileM && a.has_samples_map && out_act &&
+             out_act->has_samples_map && ep.epi == EPI_STORE && ep.map_mode == 0 && w.bn % ElemTraits<T>::kChunkK == 0 &&
+             out_act->C == w.rows_per_tap && ep.out == out_act->p;
+  int bn = effective_bn(w, a.g.rows_valid);
+  if (pix && static_cast<long long>(w.K) * w.N < pix_min_kn_) pix = false;   // short K loops: per-tile overheads win
+  if (pix) {   // tiles = pixels x batch tiles x N tiles
+    bn = w.bn;
+    while (narrow_tiles_ && bn > 64 && HW * cdiv(a.g.n, kTileM) * (w.rows_per_tap / bn) * 100 < num_sms_ * pix_fill_pct_) bn >>= 1;
+  }
   p.block_n = bn;
   p.stat_cols = std::min(bn, ElemTraits<T>::kChunkK);
   p.n_tiles = w.rows_per_tap / bn;
   // CTA pairs (256-row tiles) when there is enough work to keep every pair busy
-  const int m_tiles1 = cdiv(a.g.rows_valid, kTileM);
+  const int m_tiles1 = pix ? HW * cdiv(a.g.n, kTileM) : cdiv(a.g.rows_valid, kTileM);
   // (short K loops -- the Linear layers -- are epilogue-bound and lose on the pair's cross-CTA hand-shakes)
   const bool pair = bn >= 32 && ((use_pairs_ == 1 && ntaps * p.k_chunks >= 8 && (m_tiles1 / 2) * p.n_tiles >= num_sms_ / 2) ||
                                    (use_pairs_ == 2 && m_tiles1 >= 2));
   const int ctas = pair ? 2 : 1;
   p.m_tiles = cdiv(a.g.rows_valid, kTileM * ctas);
+  p.pix = pix ? 1 : 0;
+  if (pix) {
+    p.pix_m_tiles = cdiv(a.g.n, kTileM * ctas);
+    p.m_tiles = HW * p.pix_m_tiles;
+    // pixels with the most neighbours (the longest K loops) first
+    int k = 0;
+    for (int want = 9; want >= 1; --want)
+      for (int pi = 0; pi < HW; ++pi) {
+        const int py = pi / a.g.W, px = pi % a.g.W;
+        const int nb = (3 - (py == 0) - (py == a.g.H - 1)) * (3 - (px == 0) - (px == a.g.W - 1));
+        if (nb == want) p.pix_order[k++] = static_cast<unsigned char>(pi);
+      }
+  }
   p.tma_store = (out_act && ep.epi == EPI_STORE && ep.map_mode == 0 && bn % ElemTraits<T>::kChunkK == 0 &&
                  out_act->C % ElemTraits<T>::kChunkK == 0 && out_act->C >= p.n_tiles * bn &&
                  out_act->g.rows_alloc == a.g.rows_alloc && ep.out == out_act->p && ep.ldc == out_act->C)
                     ? 1 : 0;
+  if (pix) DMB_REQUIRE(p.tma_store == 1, "pixel-major conv needs the TMA-store epilogue");
   const int pair_bytes = kTileM * 128 + (bn / ctas) * 128;   // one (tap, K chunk) operand pair
   // Linear layers (one tap, short K, N tile <= 128): four accumulator stages / epilogue warpgroups
   const bool acc4 = use_acc4_ && !pair && ntaps == 1 && bn <= 128 && p.tma_store;
@@ -695,7 +753,7 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   // One barrier hand-shake costs the issuing threads ~500 cycles (measured): group enough
   // operand pairs per stage that their MMAs (4 x bn/2 cycles per pair) cover it, while
   // keeping at least 3 stages in flight.
-  const int n_iter = ntaps * p.k_chunks;
+  const int n_iter = (pix ? 1 : ntaps) * p.k_chunks;   // (pixel-major: the shortest K loop bounds the group)
   int group = std::max(1, std::min(std::min(n_iter, kMaxGroup), cdiv(256, bn)));
   if (group == 3) group = 2;
   while (group > 1 && ring / (group * pair_bytes) < 3) group >>= 1;
@@ -708,7 +766,7 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   // 3x3 convs: one 130-row A window per (kernel row, K chunk) shared by the row's three taps,
   // when at least three such stages fit (any N tile for CTA pairs, <= 128 otherwise)
   const int row3_stage = static_cast<int>(kHaloBytes) + 3 * (bn / ctas) * 128;
-  const bool row3 = row3_ && ntaps == 9 && !acc4 && ring / row3_stage >= 3 && shifts[1] == shifts[0] + 1 &&
+  const bool row3 = !pix && row3_ && ntaps == 9 && !acc4 && ring / row3_stage >= 3 && shifts[1] == shifts[0] + 1 &&
                     shifts[2] == shifts[1] + 1 && shifts[4] == shifts[3] + 1 && shifts[5] == shifts[4] + 1 &&
                     shifts[7] == shifts[6] + 1 && shifts[8] == shifts[7] + 1;
   if (row3) group = 1;
@@ -721,7 +779,8 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   p.rows_alloc = a.g.rows_alloc;
   p.n_valid = w.N;
   const int smem = p.stages * stage_bytes + staging + 1024;
-  const CUtensorMap& tout = p.tma_store ? out_act->tmap : a.tmap;
+  const CUtensorMap& tout = pix ? out_act->tmap_samples : (p.tma_store ? out_act->tmap : a.tmap);
+  const CUtensorMap& ta = pix ? a.tmap_samples : a.tmap;
   if (pair) {
     const int clusters = std::min(p.m_tiles * p.n_tiles, num_sms_ / 2);
     cudaLaunchConfig_t cfg{};
@@ -736,22 +795,22 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = use_pdl_ ? 2 : 1;
     if (row3) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1, 2, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
-    else if (group == 1) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1>, a.tmap, w.tmap_for(bn / 2), tout, p));
-    else if (group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2>, a.tmap, w.tmap_for(bn / 2), tout, p));
-    else DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 4>, a.tmap, w.tmap_for(bn / 2), tout, p));
+    else if (group == 1) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1>, ta, w.tmap_for(bn / 2), tout, p));
+    else if (group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2>, ta, w.tmap_for(bn / 2), tout, p));
+    else DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 4>, ta, w.tmap_for(bn / 2), tout, p));
   } else {
     const int grid = std::min(p.m_tiles * p.n_tiles, num_sms_);
     if (acc4) {
       constexpr int kT4 = gemm_threads(4);
-      if (group == 1) launch(gemm_tc_kernel<T, 1, 1, 4>, grid, kT4, smem, s, a.tmap, w.tmap_for(bn), tout, p);
-      else if (group == 2) launch(gemm_tc_kernel<T, 1, 2, 4>, grid, kT4, smem, s, a.tmap, w.tmap_for(bn), tout, p);
-      else launch(gemm_tc_kernel<T, 1, 4, 4>, grid, kT4, smem, s, a.tmap, w.tmap_for(bn), tout, p);
+      if (group == 1) launch(gemm_tc_kernel<T, 1, 1, 4>, grid, kT4, smem, s, ta, w.tmap_for(bn), tout, p);
+      else if (group == 2) launch(gemm_tc_kernel<T, 1, 2, 4>, grid, kT4, smem, s, ta, w.tmap_for(bn), tout, p);
+      else launch(gemm_tc_kernel<T, 1, 4, 4>, grid, kT4, smem, s, ta, w.tmap_for(bn), tout, p);
     } else if (row3) {
       launch(gemm_tc_kernel<T, 1, 1, 2, true>, grid, kGemmThreads, smem, s, a.tmap_halo, w.tmap_for(bn), tout, p);
     } else
-    if (group == 1) launch(gemm_tc_kernel<T, 1, 1>, grid, kGemmThreads, smem, s, a.tmap, w.tmap_for(bn), tout, p);
-    else if (group == 2) launch(gemm_tc_kernel<T, 1, 2>, grid, kGemmThreads, smem, s, a.tmap, w.tmap_for(bn), tout, p);
-    else launch(gemm_tc_kernel<T, 1, 4>, grid, kGemmThreads, smem, s, a.tmap, w.tmap_for(bn), tout, p);
+    if (group == 1) launch(gemm_tc_kernel<T, 1, 1>, grid, kGemmThreads, smem, s, ta, w.tmap_for(bn), tout, p);
+    else if (group == 2) launch(gemm_tc_kernel<T, 1, 2>, grid, kGemmThreads, smem, s, ta, w.tmap_for(bn), tout, p);
+    else launch(gemm_tc_kernel<T, 1, 4>, grid, kGemmThreads, smem, s, ta, w.tmap_for(bn), tout, p);
   }
   DMB_CHECK_LAUNCH();
   count();

@@ -65,6 +65,12 @@ struct GemmParams {
   Geo geo_out;
   int up_a, up_b;
   int tma_store;          // 1: epilogue stores through smem + TMA (tmap_out); 0: per-thread stores
+  // pixel-major 3x3 conv (small maps at large batch, see PixTile): tmap_a / tmap_out are the 3D
+  // (channel, PM row of the sample, sample) maps, M runs over SAMPLES, a tile belongs to one
+  // output pixel and its taps are the pixel's in-image neighbours
+  int pix;
+  int pix_m_tiles;             // tiles (of kTileM * kCtas samples) along the batch
+  unsigned char pix_order[64]; // output pixels, those with the most neighbours first (longest tiles first)
   float* img_f32;         // EPI_IMAGE: (n, n_valid, H, W) planar fp32, sigmoid applied
   uint8_t* img_u8;        // EPI_IMAGE: same, x255 clamp truncate
 };
@@ -73,6 +79,35 @@ constexpr int kGemmThreads = 384;                // kAcc = 2: 4 control warps + 
 constexpr int kStagingBytes = 2 * kTileM * 128;  // one 128-row x 128-byte sub-tile per epilogue warpgroup
 constexpr int gemm_threads(int acc) { return 128 + 128 * acc; }
 constexpr int gemm_staging_bytes(int acc) { return acc * kTileM * 128; }
+
+// Pixel-major tile of a 3x3 / pad-1 convolution on a small map.  The PM layout spends
+// (H+1)(W+1)/(HW) MMA rows on padding (1.31x at 7x7, 1.78x at 3x3) and every output row runs all
+// nine taps, although border pixels have only 4 or 6 neighbours inside the image.  When the
+// batch is large the GEMM is turned around: the M dimension runs over SAMPLES, a tile belongs to
+// ONE output pixel p, and its K loop visits only the neighbours q of p that exist: A tile = pixel
+// q of 128 consecutive samples (a {64 ch, 1 row, 128 samples} box of the 3D tensor map), B tile =
+// the weight block of tap q - p.  MMA work = (3H-2)(3W-2) pixel pairs per sample instead of
+// 9(H+1)(W+1): 1.6x less at 7x7, 2.9x less at 3x3.
+struct PixTile {
+  int n_tile, m_tile, py, px, prow;   // prow = PM row of the output pixel inside its sample
+  int dy_lo, dx_lo, ndx, ntap;        // neighbours: dy in [dy_lo, dy_lo + ntap / ndx), dx in [dx_lo, dx_lo + ndx)
+};
+__device__ __forceinline__ PixTile pix_tile(const GemmParams& p, int tile) {
+  PixTile t;
+  t.n_tile = tile % p.n_tiles;
+  const int rest = tile / p.n_tiles;
+  t.m_tile = rest % p.pix_m_tiles;
+  const int pix = p.pix_order[rest / p.pix_m_tiles];
+  t.py = pix / p.geo.W;
+  t.px = pix - t.py * p.geo.W;
+  t.prow = (t.py + 1) * p.geo.Wp + t.px;
+  t.dy_lo = t.py == 0 ? 1 : 0;
+  t.dx_lo = t.px == 0 ? 1 : 0;
+  const int ndy = 3 - t.dy_lo - (t.py == p.geo.H - 1 ? 1 : 0);
+  t.ndx = 3 - t.dx_lo - (t.px == p.geo.W - 1 ? 1 : 0);
+  t.ntap = ndy * t.ndx;
+  return t;
+}
 
 // kCtas == 2: launched as clusters of two CTAs (cta_group::2).  The pair owns a 256-row tile:
 // CTA rank r loads rows [m0 + 128 r, +128) of A and rows [n0 + r BLOCK_N/2, +BLOCK_N/2) of the
@@ -155,8 +190,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const uint32_t tmem_base = tmem_base_smem;
   pdl_wait();   // barriers, TMEM and descriptors are set up; from here on global memory is touched
 
-  const int total_tiles = p.m_tiles * p.n_tiles;
-  const int n_iter = p.num_taps * p.k_chunks;
+  const int total_tiles = p.m_tiles * p.n_tiles;   // (pixel-major: m_tiles = pixels x batch tiles)
+  const int n_iter_all = p.num_taps * p.k_chunks;
 
   // The producer and MMA warps run their loops with ALL 32 lanes (warp-uniform control flow
   // and operands) and elect one lane only around the asynchronous instructions: ptxas then
@@ -167,10 +202,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint32_t stage = 0, phase = 0;
     const uint32_t lead_full0 = (kCtas == 2) ? mapa_shared(smem_u32(&full_bar[0]), 0) : 0u;
     for (int tile = cl; tile < total_tiles; tile += num_cl) {
-      const int n_tile = tile % p.n_tiles;
-      const int m_tile = tile / p.n_tiles;
+      int n_tile = tile % p.n_tiles;
+      int m_tile = tile / p.n_tiles;
+      int n_iter = n_iter_all;
+      PixTile pt{};
+      if (!kRow3 && p.pix) {
+        pt = pix_tile(p, tile);
+        n_tile = pt.n_tile; m_tile = pt.m_tile;
+        n_iter = pt.ntap * p.k_chunks;
+      }
       const int m0 = (m_tile * kCtas + static_cast<int>(rank)) * kTileM;
       const int n0 = n_tile * p.block_n + static_cast<int>(rank) * (p.block_n / kCtas);
+      // operand coordinates of a tap: generic = (shifted PM row, weight row); pixel-major = (PM row
+      // of the tap's neighbour pixel inside the sample, weight row); the sample coordinate is m0
+      auto tap_coords = [&](int tap, int& a_c, int& b_c) {
+        if (!kRow3 && p.pix) {
+          const int dyi = tap / pt.ndx;
+          const int dy = pt.dy_lo + dyi, dx = pt.dx_lo + (tap - dyi * pt.ndx);
+          a_c = pt.prow + (dy - 1) * p.geo.Wp + (dx - 1);
+          b_c = p.b_row[dy * 3 + dx] + n0;
+        } else {
+          a_c = m0 + p.a_shift[tap];
+          b_c = p.b_row[tap] + n0;
+        }
+      };
       if constexpr (kRow3) {
         // stage = (kernel row dy, K chunk): the 130-row window + the weight tiles of its three taps
         int dy = 0, kc = 0;
@@ -204,7 +259,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       // (tap, K chunk) pairs are walked in order; the per-tap row offsets are looked up when
       // the tap changes, i.e. long before the next barrier wake-up needs them
       int tap = 0, kc = 0;
-      int a_cur = m0 + p.a_shift[0], b_cur = p.b_row[0] + n0;
+      int a_cur, b_cur;
+      tap_coords(0, a_cur, b_cur);
+      const bool pix = !kRow3 && p.pix;
       if constexpr (!kRow3)
       for (int it0 = 0; it0 < n_iter; it0 += kGroup) {
         int a_row[kGroup], b_row[kGroup], k_col[kGroup];
@@ -214,7 +271,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           if (it0 + gi < n_iter && ++kc == p.k_chunks) {
             kc = 0;
             ++tap;
-            if (tap < p.num_taps) { a_cur = m0 + p.a_shift[tap]; b_cur = p.b_row[tap] + n0; }
+            if (tap * p.k_chunks < n_iter) tap_coords(tap, a_cur, b_cur);
           }
         }
         const int cnt = min(kGroup, n_iter - it0);
@@ -229,10 +286,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
               if constexpr (kCtas == 2) {
                 // both CTAs' bytes are accounted on the leader's barrier
                 const uint32_t lead_bar = lead_full0 + stage * 8;
-                tma_load_2d_pair(sp, &tmap_a, lead_bar, k_col[gi], a_row[gi]);
+                if (pix) tma_load_3d_pair(sp, &tmap_a, lead_bar, k_col[gi], a_row[gi], m0);
+                else tma_load_2d_pair(sp, &tmap_a, lead_bar, k_col[gi], a_row[gi]);
                 tma_load_2d_pair(sp + a_bytes, &tmap_b, lead_bar, k_col[gi], b_row[gi]);
               } else {
-                tma_load_2d(sp, &tmap_a, &full_bar[stage], k_col[gi], a_row[gi]);
+                if (pix) tma_load_3d(sp, &tmap_a, &full_bar[stage], k_col[gi], a_row[gi], m0);
+                else tma_load_2d(sp, &tmap_a, &full_bar[stage], k_col[gi], a_row[gi]);
                 tma_load_2d(sp + a_bytes, &tmap_b, &full_bar[stage], k_col[gi], b_row[gi]);
               }
             }
@@ -253,6 +312,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         mbar_wait(&tmem_empty_bar[as], aph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * p.block_n;
+        const int n_iter = (!kRow3 && p.pix) ? pix_tile(p, tile).ntap * p.k_chunks : n_iter_all;
         if constexpr (kRow3) {
           const int n3 = 3 * p.k_chunks;
           for (int it = 0; it < n3; ++it) {
@@ -342,13 +402,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     uint32_t tile_count = 0;
     for (int tile = cl; tile < total_tiles; tile += num_cl, ++tile_count) {
       if ((tile_count % kAcc) != as) continue;
-      const int n_tile = tile % p.n_tiles;
-      const int m_tile = tile / p.n_tiles;
+      int n_tile = tile % p.n_tiles;
+      int m_tile = tile / p.n_tiles;
+      int prow = 0;
+      const bool pix = !kRow3 && p.pix;
+      if (pix) {
+        const PixTile pt = pix_tile(p, tile);
+        n_tile = pt.n_tile; m_tile = pt.m_tile; prow = pt.prow;
+      }
       const int n0 = n_tile * p.block_n;
       const int m0 = (m_tile * kCtas + static_cast<int>(rank)) * kTileM;
-      const int r = m0 + row_in_tile;
+      int r = m0 + row_in_tile;
       int b = 0, y = 0, x = 0;
-      const bool valid = geo_decode(p.geo, r, b, y, x);
+      bool valid;
+      if (pix) {   // rows of the tile are samples; r = the output pixel's PM row
+        valid = r < p.geo.n;
+        r = r * p.geo.S + prow;
+      } else {
+        valid = geo_decode(p.geo, r, b, y, x);
+      }
 
       const uint32_t aph = (tile_count / kAcc) & 1;
       mbar_wait(&tmem_full_bar[as], aph);
@@ -443,7 +515,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           fence_async_proxy();
           named_bar_sync(bar_id, 128);
           if (store_thread) {
-            tma_store_2d(&tmap_out, buf, n0 + k * kSubN, m0);
+            if (pix) tma_store_3d(&tmap_out, buf, n0 + k * kSubN, prow, m0);
+            else tma_store_2d(&tmap_out, buf, n0 + k * kSubN, m0);
             tma_store_commit();
           }
         }

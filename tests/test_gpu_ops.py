@@ -46,7 +46,10 @@ def test_linear(ctx, rows, K, N, act, use_bias):
 @pytest.mark.parametrize("B,Cin,Cout,H,W", [
     (2, 64, 64, 28, 28), (3, 128, 128, 14, 14), (2, 256, 512, 3, 3), (1, 512, 256, 7, 7),
     (2, 64, 3, 12, 12), (1, 64, 128, 1, 1), (5, 128, 64, 7, 5), (16, 256, 256, 14, 14),
-    (64, 128, 128, 28, 28), (96, 64, 256, 14, 14), (40, 128, 64, 28, 28)])  # large: CTA-pair (cta_group::2) tiles
+    (64, 128, 128, 28, 28), (96, 64, 256, 14, 14), (40, 128, 64, 28, 28),  # large: CTA-pair (cta_group::2) tiles
+    # small maps at batch >= 256: pixel-major tiles (M over samples, K over the in-image neighbours)
+    (256, 128, 128, 7, 7), (300, 256, 512, 3, 3), (257, 64, 64, 7, 7), (260, 512, 256, 5, 7), (512, 64, 128, 2, 2),
+    (256, 128, 64, 1, 1)])
 def test_conv3x3(ctx, B, Cin, Cout, H, W):
     g = torch.Generator().manual_seed(B * 1000 + Cin + Cout + H)
     x = bf16_round(torch.randn((B, Cin, H, W), generator=g))
