@@ -276,6 +276,7 @@ class Engine : public IEngine {
       pix_mode_ = !(pe3 && pe3[0] == '0');
       if (const char* e = getenv("DMB200_PIX_MINKN")) pix_min_kn_ = atoll(e);
       if (const char* e = getenv("DMB200_PIX_FILL")) pix_fill_pct_ = atoi(e);
+      if (const char* e = getenv("DMB200_PIX_MAXHW")) pix_max_hw_ = atoi(e);
       const char* re = getenv("DMB200_ROW3");   // 0: nine separate A tiles per K chunk
       row3_ = re ? atoi(re) : 1;
     }
@@ -434,6 +435,7 @@ class Engine : public IEngine {
   bool fuse_ln1_ = true;    // DMB200_FUSE_LN1=0: the attention block's first LayerNorm as its own launch
   bool keep_taps_ = false;  // DMB200_KEEP_TAPS=1: also store the un-normalised stage outputs (down1.. up3 taps)
   long long pix_min_kn_ = 256 * 256;   // pixel-major only for C_in * C_out >= this
+  int pix_max_hw_ = 14;                // largest map side that may run pixel-major
   int pix_fill_pct_ = 90;              // narrow the N tile while there are fewer tiles than this share of the SMs
   bool pix_mode_ = true;   // DMB200_PIX=0: small maps keep the padded-row GEMM at every batch size
   int row3_ = 1;   // DMB200_ROW3=0: every tap of a 3x3 conv loads its own A tile
@@ -674,7 +676,7 @@ Act<T> Engine<T>::new_act(Pool& pool, int n, int H, int W, int C, bool with_stat
   if (C % ElemTraits<T>::kChunkK == 0) {
     a.tmap = make_tmap<T>(a.p, C, a.g.rows_alloc, kTileM);
     a.tmap_halo = make_tmap<T>(a.p, C, a.g.rows_alloc, kHaloRows);
-    if (H * W <= 64) {
+    if (H * W <= 196) {
       a.tmap_samples = make_tmap_samples<T>(a.p, C, a.g.S, n);
       a.has_samples_map = true;
     }
@@ -707,7 +709,7 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
                      shifts[4] == shifts[3] + 1 && shifts[5] == shifts[4] + 1 && shifts[7] == shifts[6] + 1 &&
                      shifts[8] == shifts[7] + 1 && shifts[3] == shifts[0] + a.g.Wp && shifts[6] == shifts[3] + a.g.Wp;
   const int HW = a.g.H * a.g.W;
-  bool pix = pix_mode_ && conv3 && a.g.H <= 7 && a.g.W <= 7 && a.g.n >= 2 * kTileM && a.has_samples_map && out_act &&
+  bool pix = pix_mode_ && conv3 && a.g.H <= pix_max_hw_ && a.g.W <= pix_max_hw_ && HW <= 196 && a.g.n >= 2 * kTileM && a.has_samples_map && out_act &&
              out_act->has_samples_map && ep.epi == EPI_STORE && ep.map_mode == 0 && w.bn % ElemTraits<T>::kChunkK == 0 &&
              out_act->C == w.rows_per_tap && ep.out == out_act->p;
   int bn = effective_bn(w, a.g.rows_valid);

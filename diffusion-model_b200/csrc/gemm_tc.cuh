@@ -70,7 +70,7 @@ struct GemmParams {
   // output pixel and its taps are the pixel's in-image neighbours
   int pix;
   int pix_m_tiles;             // tiles (of kTileM * kCtas samples) along the batch
-  unsigned char pix_order[64]; // output pixels, those with the most neighbours first (longest tiles first)
+  unsigned char pix_order[196]; // output pixels (maps up to 14 x 14), those with the most neighbours first (longest tiles first)
   float* img_f32;         // EPI_IMAGE: (n, n_valid, H, W) planar fp32, sigmoid applied
   uint8_t* img_u8;        // EPI_IMAGE: same, x255 clamp truncate
 };
