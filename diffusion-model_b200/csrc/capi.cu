@@ -4,6 +4,7 @@
 #include <cstring>
 
 #include "engine.cuh"
+#include "score.cuh"
 
 struct dmb_ctx {
   dmb::IEngine* eng;
@@ -143,6 +144,34 @@ int dmb_vae_decode(dmb_ctx* ctx, const float* z, int B, float* img_f32, uint8_t*
     DMB_REQUIRE(ctx && z, "ctx and z are required");
     DMB_REQUIRE(img_f32 || img_u8, "at least one output buffer is required");
     ctx->eng->vae_decode(z, B, img_f32, img_u8, st(stream));
+  });
+}
+
+int dmb_score_masks(dmb_ctx* ctx, const uint8_t* pred, int pred_channels, const uint8_t* gt, int gt_channels,
+                    int B, int H, int W, int threshold, int invert, double sigma, int64_t* counts,
+                    double* weighted_hit, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && pred && gt && counts && weighted_hit, "ctx, pred, gt, counts and weighted_hit are required");
+    DMB_REQUIRE(B >= 1 && H >= 1 && W >= 1 && H <= dmb::kScoreMaxSide && W <= dmb::kScoreMaxSide,
+                "B >= 1 and 1 <= H, W <= 254 are required");
+    DMB_REQUIRE((pred_channels == 0 || pred_channels == 1 || pred_channels == 3) &&
+                    (gt_channels == 0 || gt_channels == 1 || gt_channels == 3),
+                "channels must be 0 (mask), 1 (grey) or 3 (RGB)");
+    DMB_REQUIRE(sigma > 0.0, "sigma must be > 0");   // eval_iou_noise.py:197, 225
+    DMB_CUDA(cudaSetDevice(ctx->device));
+    static bool attr_set = false;
+    if (!attr_set) {
+      DMB_CUDA(cudaFuncSetAttribute(dmb::score_masks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    static_cast<int>(dmb::score_smem_bytes(dmb::kScoreMaxSide, dmb::kScoreMaxSide))));
+      attr_set = true;
+    }
+    dmb::ScoreParams p{};
+    p.pred = pred; p.gt = gt; p.pred_channels = pred_channels; p.gt_channels = gt_channels;
+    p.B = B; p.H = H; p.W = W; p.threshold = threshold; p.invert = invert; p.sigma = sigma;
+    p.counts = reinterpret_cast<long long*>(counts);
+    p.weighted_hit = weighted_hit;
+    dmb::score_masks_kernel<<<B, dmb::kScoreThreads, dmb::score_smem_bytes(H, W), st(stream)>>>(p);
+    DMB_CHECK_LAUNCH();
   });
 }
 

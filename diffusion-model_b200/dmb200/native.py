@@ -43,6 +43,8 @@ _SIGNATURES = {
     "dmb_sample_loop_strided": (C.c_int, [_P, _P, _P, C.c_int, _P, _P, C.c_float, _P, C.c_int, C.c_int, C.c_int,
                                           C.c_int, _P, C.c_uint64, C.c_uint64, _P, _P, C.c_int, _P]),
     "dmb_vae_decode": (C.c_int, [_P, _P, C.c_int, _P, _P, _P]),
+    "dmb_score_masks": (C.c_int, [_P, _P, C.c_int, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
+                                  _P, _P, _P]),
     "dmb_philox_normal": (C.c_int, [_P, _P, C.c_int, C.c_uint64, C.c_uint64, C.c_int, _P]),
     "dmb_launch_count": (C.c_int64, [_P]),
     "dmb_reset_launch_count": (C.c_int, [_P]),
@@ -232,6 +234,28 @@ class Context:
         u8 = torch.empty((B, 3, 224, 224), device=self.device, dtype=torch.uint8) if want_u8 else None
         self._call("dmb_vae_decode", self._h, _ptr(z), B, _ptr(f32), _ptr(u8), self._stream())
         return f32, u8
+
+    def score_masks(self, pred, gt, threshold=128, invert=True, sigma=2.0):
+        """Device-side counters of eval_iou_noise.compute_metrics for a batch.  pred / gt: uint8 CUDA
+        tensors, (B,3,H,W) RGB images or (B,1,H,W) grey images (binarised like load_binary_mask) or
+        (B,H,W) masks (non-zero = foreground).  Returns (counts (B,6) int64, weighted_hit (B,) f64)."""
+        def chan(t, name):
+            _check_dev(t, self.device, torch.uint8, name)
+            if t.dim() == 3:
+                return 0
+            if t.dim() == 4 and t.shape[1] in (1, 3):
+                return int(t.shape[1])
+            raise ValueError(f"{name} must be (B,H,W), (B,1,H,W) or (B,3,H,W) uint8, got {tuple(t.shape)}")
+        pc, gc = chan(pred, "pred"), chan(gt, "gt")
+        pred, gt = pred.contiguous(), gt.contiguous()
+        B, H, W = pred.shape[0], pred.shape[-2], pred.shape[-1]
+        if (gt.shape[0], gt.shape[-2], gt.shape[-1]) != (B, H, W):
+            raise ValueError(f"Shape mismatch: gt{tuple(gt.shape)} vs pred{tuple(pred.shape)}")
+        counts = torch.empty((B, 6), device=self.device, dtype=torch.int64)
+        hit = torch.empty((B,), device=self.device, dtype=torch.float64)
+        self._call("dmb_score_masks", self._h, _ptr(pred), pc, _ptr(gt), gc, B, H, W, int(threshold), int(bool(invert)),
+                   float(sigma), _ptr(counts), _ptr(hit), self._stream())
+        return counts, hit
 
     def philox_normal(self, B, seed, sample_offset, t):
         out = torch.empty((B, 4, 28, 28), device=self.device, dtype=torch.float32)

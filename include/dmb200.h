@@ -99,6 +99,19 @@ int dmb_sample_loop_strided(dmb_ctx* ctx, float* x, const int64_t* y, int null_l
  * img_u8 (B,3,224,224) [dev] or NULL. */
 int dmb_vae_decode(dmb_ctx* ctx, const float* z, int B, float* img_f32, uint8_t* img_u8, void* stream);
 
+/* Scoring of generated images against ground-truth masks on the device:
+ * eval_iou_noise.py:77-94 load_binary_mask (PIL "L" conversion + threshold), :162-171 exact
+ * Euclidean distance transform, :185-232 gaussian_weighted_recall / far_noise_ratio, :239-272
+ * compute_metrics.  pred (B, pc, H, W) u8 [dev], gt (B, gc, H, W) u8 [dev]; channels 3 = RGB image,
+ * 1 = grey image (both binarised: L < threshold if invert else L >= threshold), 0 = mask (non-zero
+ * = foreground).  H, W <= 254.  counts (B,6) int64 [dev] = inter, union, gt_area, pred_area, fp,
+ * far_noise (pred pixels farther than sigma from the ground truth); weighted_hit (B,) f64 [dev] =
+ * sum over pred pixels of exp(-d^2 / (2 sigma^2)).  The caller forms the reference's float64
+ * ratios from these (iou = inter/union ...), which makes every ratio but gauss_recall bit-exact. */
+int dmb_score_masks(dmb_ctx* ctx, const uint8_t* pred, int pred_channels, const uint8_t* gt, int gt_channels,
+                    int B, int H, int W, int threshold, int invert, double sigma, int64_t* counts,
+                    double* weighted_hit, void* stream);
+
 /* The Philox noise dmb_denoise_cond_step / dmb_sample_loop would draw for step t:
  * out (B,4,28,28) [dev]. */
 int dmb_philox_normal(dmb_ctx* ctx, float* out, int B, uint64_t seed, uint64_t sample_offset, int t,

@@ -118,3 +118,25 @@ def test_metrics_edge_cases():
     assert m["iou"] == 0.0 and m["far_noise_ratio"] == 0.0 and m["gauss_recall"] == 0.0
     with pytest.raises(ValueError):
         R.compute_metrics(z, np.zeros((4, 4), bool))
+
+
+def test_scoring_oracle_matches_scipy():
+    """Pins the two third-party behaviours the on-GPU scorer (csrc/score.cuh) restates: scipy's
+    exact Euclidean distance transform -- including its answer for an input with no background
+    pixel, sqrt((y+1)^2 + x^2) (a virtual background pixel at (-1, 0)), which far_noise_ratio reaches when the ground truth is
+    empty (eval_iou_noise.py:162-171, 211-232) -- and Pillow's integer RGB -> L conversion
+    (eval_iou_noise.py:87)."""
+    from scipy.ndimage import distance_transform_edt
+    from PIL import Image
+    yy, xx = np.mgrid[0:9, 0:13]
+    d = distance_transform_edt(np.ones((9, 13), bool))
+    assert np.array_equal(d, np.sqrt(((yy + 1) ** 2 + xx ** 2).astype(np.float64)))
+    rng = np.random.default_rng(3)
+    gt = rng.random((17, 23)) < 0.05
+    gy, gx = np.nonzero(gt)
+    y17, x23 = np.mgrid[0:17, 0:23]
+    brute = ((y17[..., None] - gy) ** 2 + (x23[..., None] - gx) ** 2).min(-1)   # exact squared distances
+    assert np.array_equal(distance_transform_edt(~gt), np.sqrt(brute.astype(np.float64)))
+    rgb = rng.integers(0, 256, (3, 31, 29), dtype=np.uint8)
+    pil = np.array(Image.fromarray(np.moveaxis(rgb, 0, -1), mode="RGB").convert("L"))
+    assert np.array_equal(R.u8_to_gray(rgb), pil)
