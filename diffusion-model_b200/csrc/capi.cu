@@ -163,6 +163,9 @@ int dmb_score_masks(dmb_ctx* ctx, const uint8_t* pred, int pred_channels, const 
     if (!attr_set) {
       DMB_CUDA(cudaFuncSetAttribute(dmb::score_masks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     static_cast<int>(dmb::score_smem_bytes(dmb::kScoreMaxSide, dmb::kScoreMaxSide))));
+      // two 100 KB CTAs per SM at 224 x 224: ask for the largest shared-memory carve-out
+      DMB_CUDA(cudaFuncSetAttribute(dmb::score_masks_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                    cudaSharedmemCarveoutMaxShared));
       attr_set = true;
     }
     dmb::ScoreParams p{};

@@ -21,7 +21,7 @@
 
 namespace dmb {
 
-constexpr int kScoreThreads = 256;
+constexpr int kScoreThreads = 512;   // the per-pixel searches are latency chains: 32 warps per SM (two CTAs)
 constexpr int kScoreMaxSide = 254;   // column distances are kept in one byte (255 = no ground truth in the column)
 
 struct ScoreParams {
@@ -41,36 +41,54 @@ __device__ __forceinline__ uint32_t pil_luma(uint32_t r, uint32_t g, uint32_t b)
   return (r * 19595u + g * 38470u + b * 7471u + 0x8000u) >> 16;
 }
 
+// foreground bytes (0 / 1) of four pixels packed in a word
+__device__ __forceinline__ uint32_t fg4(uint32_t r, uint32_t g, uint32_t b, int channels, int threshold, int invert) {
+  uint32_t out = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int L = channels == 3 ? static_cast<int>(pil_luma((r >> (8 * k)) & 255u, (g >> (8 * k)) & 255u, (b >> (8 * k)) & 255u))
+                                : static_cast<int>((r >> (8 * k)) & 255u);
+    const bool fg = channels == 0 ? (L != 0) : (invert ? (L < threshold) : (L >= threshold));
+    out |= (fg ? 1u : 0u) << (8 * k);
+  }
+  return out;
+}
+
+// One image plane set -> one byte per pixel in shared memory.  16 pixels per thread and load,
+// two such vectors in flight per thread and plane (1024 threads per SM): the image is read once from HBM and this is
+// the only HBM traffic of the kernel, so the loads have to cover the memory latency.
 __device__ __forceinline__ void binarise_plane(const uint8_t* __restrict__ src, int channels, int HW, int threshold,
                                                int invert, uint8_t* __restrict__ dst) {
-  // 4 pixels per thread per iteration (HW is a multiple of 4 for every map this path sees; the
-  // tail is handled bytewise)
-  const bool vec = (HW & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 3) == 0;
-  const int n4 = vec ? HW >> 2 : 0;
-  for (int i = threadIdx.x; i < n4; i += kScoreThreads) {
-    uint32_t out = 0;
-    if (channels == 3) {
-      const uint32_t r = *reinterpret_cast<const uint32_t*>(src + 4 * i);
-      const uint32_t g = *reinterpret_cast<const uint32_t*>(src + HW + 4 * i);
-      const uint32_t b = *reinterpret_cast<const uint32_t*>(src + 2 * HW + 4 * i);
+  const bool vec = (HW & 15) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+  const int n16 = vec ? HW >> 4 : 0;
+  constexpr int U = 2;
+  for (int i0 = threadIdx.x; i0 < n16; i0 += U * kScoreThreads) {
+    uint4 r[U], g[U], b[U];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const uint32_t L = pil_luma((r >> (8 * k)) & 255u, (g >> (8 * k)) & 255u, (b >> (8 * k)) & 255u);
-        const bool fg = invert ? (static_cast<int>(L) < threshold) : (static_cast<int>(L) >= threshold);
-        out |= (fg ? 1u : 0u) << (8 * k);
-      }
-    } else {
-      const uint32_t v = *reinterpret_cast<const uint32_t*>(src + 4 * i);
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int L = static_cast<int>((v >> (8 * k)) & 255u);
-        const bool fg = channels == 0 ? (L != 0) : (invert ? (L < threshold) : (L >= threshold));
-        out |= (fg ? 1u : 0u) << (8 * k);
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * kScoreThreads;
+      if (i < n16) {
+        r[u] = *reinterpret_cast<const uint4*>(src + 16 * i);
+        if (channels == 3) {
+          g[u] = *reinterpret_cast<const uint4*>(src + HW + 16 * i);
+          b[u] = *reinterpret_cast<const uint4*>(src + 2 * HW + 16 * i);
+        }
       }
     }
-    *reinterpret_cast<uint32_t*>(dst + 4 * i) = out;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = i0 + u * kScoreThreads;
+      if (i < n16) {
+        uint4 o;
+        o.x = fg4(r[u].x, g[u].x, b[u].x, channels, threshold, invert);
+        o.y = fg4(r[u].y, g[u].y, b[u].y, channels, threshold, invert);
+        o.z = fg4(r[u].z, g[u].z, b[u].z, channels, threshold, invert);
+        o.w = fg4(r[u].w, g[u].w, b[u].w, channels, threshold, invert);
+        *reinterpret_cast<uint4*>(dst + 16 * i) = o;
+      }
+    }
   }
-  for (int i = 4 * n4 + threadIdx.x; i < HW; i += kScoreThreads) {
+  for (int i = 16 * n16 + threadIdx.x; i < HW; i += kScoreThreads) {
     int L;
     if (channels == 3) L = static_cast<int>(pil_luma(src[i], src[HW + i], src[2 * HW + i]));
     else L = src[i];
@@ -78,7 +96,7 @@ __device__ __forceinline__ void binarise_plane(const uint8_t* __restrict__ src, 
   }
 }
 
-static __global__ void __launch_bounds__(kScoreThreads)
+static __global__ void __launch_bounds__(kScoreThreads, 2)
 score_masks_kernel(const ScoreParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ int cnt[5];            // inter, union, gt_area, pred_area, fp
@@ -119,54 +137,103 @@ score_masks_kernel(const ScoreParams p) {
   __syncthreads();
   const bool gt_empty = cnt[2] == 0;
 
-  // column pass (in place): g[y][x] = distance along the column to the nearest ground-truth pixel
+  // column pass (in place): g[y][x] = distance along the column to the nearest ground-truth pixel.
+  // The loads do not depend on the running distance, so eight rows are fetched at a time and
+  // only the register chain is serial.
   for (int x = tid; x < W; x += kScoreThreads) {
-    int d = 255;
-    for (int y = 0; y < H; ++y) {
-      d = g[y * W + x] ? 0 : min(d + 1, 255);
-      g[y * W + x] = static_cast<uint8_t>(d);
+    uint8_t* col = g + x;
+    int d = 255, y = 0;
+    for (; y + 8 <= H; y += 8, col += 8 * W) {
+      int v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = col[k * W];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        d = v[k] ? 0 : min(d + 1, 255);
+        col[k * W] = static_cast<uint8_t>(d);
+      }
+    }
+    for (; y < H; ++y, col += W) {
+      d = col[0] ? 0 : min(d + 1, 255);
+      col[0] = static_cast<uint8_t>(d);
     }
     d = 255;
-    for (int y = H - 1; y >= 0; --y) {
-      const int down = g[y * W + x];
-      d = down == 0 ? 0 : min(d + 1, 255);
-      g[y * W + x] = static_cast<uint8_t>(min(d, down));
+    y = H;
+    for (; y >= 8; y -= 8) {
+      col -= 8 * W;
+      int v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = col[(7 - k) * W];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        d = v[k] == 0 ? 0 : min(d + 1, 255);
+        col[(7 - k) * W] = static_cast<uint8_t>(min(d, v[k]));
+      }
+    }
+    for (; y > 0; --y) {
+      col -= W;
+      const int v = col[0];
+      d = v == 0 ? 0 : min(d + 1, 255);
+      col[0] = static_cast<uint8_t>(min(d, v));
     }
   }
   __syncthreads();
 
-  // row pass at the predicted pixels; a warp owns 32 consecutive pixels at a time
+  // row pass at the predicted pixels; a warp owns 32 consecutive pixels at a time: the squared
+  // distance of each predicted pixel is found by all 32 lanes (they split the row, shuffle-min)
+  // and kept by the pixel's own lane, which then does the float64 part for it
   const double two_s2 = 2.0 * (p.sigma * p.sigma);
   int far = 0;
   double hit = 0.0;
-  for (int base = warp * 32; base < HW; base += kScoreThreads) {
-    const int i = base + lane;
-    uint32_t todo = __ballot_sync(0xffffffffu, i < HW && pm[i] != 0);
-    while (todo) {
-      const int src = __ffs(todo) - 1;
-      todo &= todo - 1;
-      const int pi = base + src;
-      const int y = pi / W, x = pi - y * W;
-      long long d2;
-      if (gt_empty) {
-        d2 = static_cast<long long>(y + 1) * (y + 1) + static_cast<long long>(x) * x;
-      } else {
-        int best = 0x7fffffff;
-        const uint8_t* grow = g + y * W;
-        for (int xx = lane; xx < W; xx += 32) {
-          const int gy = grow[xx];
-          if (gy != 255) best = min(best, (x - xx) * (x - xx) + gy * gy);
-        }
+  // (a lane first looks at four pixels at once: most 128-pixel spans of a line drawing are empty)
+  const bool words = (HW & 3) == 0;
+  const int span = words ? 128 : 32;
+  for (int base0 = warp * span; base0 < HW; base0 += (kScoreThreads / 32) * span) {
+    uint32_t w4 = 0;
+    if (words) {
+      const int wi = base0 + 4 * lane;
+      if (wi < HW) w4 = *reinterpret_cast<const uint32_t*>(pm + wi);
+      if (!__any_sync(0xffffffffu, w4 != 0)) continue;
+    }
+    for (int sub = 0; sub < (words ? 4 : 1); ++sub) {
+      // sub-span `sub`: pixel base0 + 4 * lane + sub belongs to this lane
+      const int i = words ? base0 + 4 * lane + sub : base0 + lane;
+      const bool mine = words ? ((w4 >> (8 * sub)) & 255u) != 0 : (i < HW && pm[i] != 0);
+      uint32_t todo = __ballot_sync(0xffffffffu, mine);
+      long long d2_mine = 0;
+      while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int pi = words ? base0 + 4 * src + sub : base0 + src;
+        const int y = pi / W, x = pi - y * W;
+        long long d2;
+        if (gt_empty) {
+          d2 = static_cast<long long>(y + 1) * (y + 1) + static_cast<long long>(x) * x;
+        } else {
+          int best = 0x7fffffff;
+          const uint8_t* grow = g + y * W;
+          for (int xx = lane; xx < W; xx += 32) {
+            const int gy = grow[xx];
+            if (gy != 255) best = min(best, (x - xx) * (x - xx) + gy * gy);
+          }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
-        d2 = best;
+          for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+          d2 = best;
+        }
+        if (lane == src) d2_mine = d2;
       }
-      if (lane == 0) {
-        const double dist = sqrt(static_cast<double>(d2));
+      if (mine) {
+        const double dist = sqrt(static_cast<double>(d2_mine));
         far += dist > p.sigma ? 1 : 0;
         hit += exp(-(dist * dist) / two_s2);   // the reference's expression, in float64
       }
     }
+  }
+  // fixed-order reduction over the lanes, then over the warps: the sum is deterministic
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    far += __shfl_xor_sync(0xffffffffu, far, o);
+    hit += __shfl_xor_sync(0xffffffffu, hit, o);
   }
   if (lane == 0) {
     atomicAdd(&far_cnt, far);
