@@ -2,6 +2,11 @@
 #include "../../include/dmb200.h"
 
 #include <cstring>
+#include <atomic>
+#include <cstdio>
+#include <thread>
+#include <vector>
+#include <zlib.h>
 
 #include "engine.cuh"
 #include "score.cuh"
@@ -175,6 +180,78 @@ int dmb_score_masks(dmb_ctx* ctx, const uint8_t* pred, int pred_channels, const 
     p.weighted_hit = weighted_hit;
     dmb::score_masks_kernel<<<B, dmb::kScoreThreads, dmb::score_smem_bytes(H, W), st(stream)>>>(p);
     DMB_CHECK_LAUNCH();
+  });
+}
+
+// ---------------------------------------------------------------------------
+// Host side of the output path: PNG files from a batch of planar u8 images.
+// ---------------------------------------------------------------------------
+namespace {
+void png_chunk(std::vector<unsigned char>& out, const char* type, const unsigned char* data, size_t n) {
+  auto be32 = [&](uint32_t v) { for (int s = 24; s >= 0; s -= 8) out.push_back(static_cast<unsigned char>(v >> s)); };
+  be32(static_cast<uint32_t>(n));
+  const size_t start = out.size();
+  out.insert(out.end(), type, type + 4);
+  if (n) out.insert(out.end(), data, data + n);
+  be32(static_cast<uint32_t>(crc32(0L, out.data() + start, static_cast<uInt>(n + 4))));
+}
+
+// one image (C, H, W) planar u8 -> PNG bytes (8-bit grey or RGB, filter type 0 on every row)
+bool png_encode(const unsigned char* img, int C, int H, int W, int level, std::vector<unsigned char>& out) {
+  std::vector<unsigned char> raw(static_cast<size_t>(H) * (1 + static_cast<size_t>(W) * C));
+  const size_t plane = static_cast<size_t>(H) * W;
+  unsigned char* q = raw.data();
+  for (int y = 0; y < H; ++y) {
+    *q++ = 0;
+    const unsigned char* r0 = img + static_cast<size_t>(y) * W;
+    if (C == 1) {
+      memcpy(q, r0, W);
+      q += W;
+    } else {
+      for (int x = 0; x < W; ++x) { *q++ = r0[x]; *q++ = r0[plane + x]; *q++ = r0[2 * plane + x]; }
+    }
+  }
+  uLongf zn = compressBound(static_cast<uLong>(raw.size()));
+  std::vector<unsigned char> z(zn);
+  if (compress2(z.data(), &zn, raw.data(), static_cast<uLong>(raw.size()), level) != Z_OK) return false;
+  static const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+  out.assign(sig, sig + 8);
+  unsigned char ihdr[13];
+  for (int i = 0; i < 4; ++i) { ihdr[i] = static_cast<unsigned char>(W >> (24 - 8 * i)); ihdr[4 + i] = static_cast<unsigned char>(H >> (24 - 8 * i)); }
+  ihdr[8] = 8; ihdr[9] = C == 1 ? 0 : 2; ihdr[10] = 0; ihdr[11] = 0; ihdr[12] = 0;
+  png_chunk(out, "IHDR", ihdr, 13);
+  png_chunk(out, "IDAT", z.data(), zn);
+  png_chunk(out, "IEND", nullptr, 0);
+  return true;
+}
+}  // namespace
+
+int dmb_write_png_batch(const uint8_t* images, int n, int C, int H, int W, const char* const* paths, int threads,
+                        int compression_level) {
+  return guarded([&] {
+    DMB_REQUIRE(images && paths && n >= 0, "images and paths are required");
+    DMB_REQUIRE((C == 1 || C == 3) && H >= 1 && W >= 1, "C must be 1 (grey) or 3 (RGB); H, W >= 1");
+    DMB_REQUIRE(compression_level >= 0 && compression_level <= 9, "compression_level must be 0..9");
+    const int nt = std::max(1, std::min(threads > 0 ? threads : static_cast<int>(std::thread::hardware_concurrency()), n));
+    std::atomic<int> next{0};
+    std::atomic<int> failed{-1};
+    auto work = [&]() {
+      std::vector<unsigned char> png;
+      for (int i = next.fetch_add(1); i < n; i = next.fetch_add(1)) {
+        bool ok = png_encode(images + static_cast<size_t>(i) * C * H * W, C, H, W, compression_level, png);
+        if (ok) {
+          FILE* f = fopen(paths[i], "wb");
+          ok = f && fwrite(png.data(), 1, png.size(), f) == png.size();
+          if (f) ok = (fclose(f) == 0) && ok;
+        }
+        if (!ok) { int exp = -1; failed.compare_exchange_strong(exp, i); }
+      }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < nt; ++t) pool.emplace_back(work);
+    work();
+    for (auto& t : pool) t.join();
+    if (failed.load() >= 0) dmb::fail(6, std::string("could not write '") + paths[failed.load()] + "'");
   });
 }
 

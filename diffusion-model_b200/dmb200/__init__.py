@@ -5,4 +5,4 @@ all arithmetic of the sampling path runs in the library.  There is no CPU fallba
 entry point raises if the library or a B200 is missing.
 """
 from .native import (Context, NativeError, context_for, library_path, load_library,  # noqa: F401
-                     PRECISION_BF16, PRECISION_TF32)
+                     PRECISION_BF16, PRECISION_TF32, write_png_batch)

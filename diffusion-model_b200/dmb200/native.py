@@ -45,6 +45,7 @@ _SIGNATURES = {
     "dmb_vae_decode": (C.c_int, [_P, _P, C.c_int, _P, _P, _P]),
     "dmb_score_masks": (C.c_int, [_P, _P, C.c_int, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
                                   _P, _P, _P]),
+    "dmb_write_png_batch": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_char_p), C.c_int, C.c_int]),
     "dmb_philox_normal": (C.c_int, [_P, _P, C.c_int, C.c_uint64, C.c_uint64, C.c_int, _P]),
     "dmb_launch_count": (C.c_int64, [_P]),
     "dmb_reset_launch_count": (C.c_int, [_P]),
@@ -76,6 +77,32 @@ def load_library():
                 fn.argtypes = args
             _lib = lib
     return _lib
+
+
+def write_png_batch(images: torch.Tensor, paths: Sequence[str], threads: int = 0, compression_level: int = 3) -> None:
+    """(n,3,H,W) / (n,1,H,W) / (n,H,W) uint8 tensor (CUDA or CPU) -> one PNG per image, encoded in
+    parallel on the host by the native library (dmb_write_png_batch).  A CUDA batch crosses PCIe
+    in ONE copy into pinned memory."""
+    if images.dtype != torch.uint8 or images.dim() not in (3, 4):
+        raise ValueError(f"images must be uint8 (n,C,H,W) or (n,H,W), got {images.dtype} {tuple(images.shape)}")
+    if images.dim() == 3:
+        images = images[:, None]
+    n, Cc, H, W = images.shape
+    if Cc not in (1, 3):
+        raise ValueError(f"images must have 1 or 3 channels, got {Cc}")
+    if len(paths) != n:
+        raise ValueError(f"{n} images but {len(paths)} paths")
+    if images.is_cuda:
+        host = torch.empty(images.shape, dtype=torch.uint8, pin_memory=True)
+        host.copy_(images.contiguous(), non_blocking=True)
+        torch.cuda.current_stream(images.device).synchronize()
+    else:
+        host = images.contiguous()
+    arr = (C.c_char_p * n)(*[os.fsencode(p) for p in paths])
+    lib = load_library()
+    rc = lib.dmb_write_png_batch(C.c_void_p(host.data_ptr()), n, Cc, H, W, arr, int(threads), int(compression_level))
+    if rc != 0:
+        raise NativeError(f"dmb_write_png_batch failed ({rc}): " + lib.dmb_last_error_string().decode("utf-8", "replace"))
 
 
 def _ptr(t: Optional[torch.Tensor]):

@@ -112,6 +112,16 @@ int dmb_score_masks(dmb_ctx* ctx, const uint8_t* pred, int pred_channels, const 
                     int B, int H, int W, int threshold, int invert, double sigma, int64_t* counts,
                     double* weighted_hit, void* stream);
 
+/* Output path: writes n PNG files from a HOST batch of planar u8 images
+ * (n, C, H, W), C = 3 (RGB) or 1 (grey), in parallel on `threads` host threads (<= 0: all).
+ * Replaces the per-image `.cpu()` -> ToPILImage -> image.save loop of Diffuser.reverse_to_img +
+ * Utils.saveImages (diff.py:58-64, utils.py:216-224) and the per-step saves of
+ * generate_steps.py:47-66, 164-167; the caller keeps the reference's file names.  The files
+ * decode to exactly the input pixels (8-bit, no interlace); their bytes are not PIL's.
+ * Needs no context and no GPU. */
+int dmb_write_png_batch(const uint8_t* images, int n, int C, int H, int W, const char* const* paths, int threads,
+                        int compression_level);
+
 /* The Philox noise dmb_denoise_cond_step / dmb_sample_loop would draw for step t:
  * out (B,4,28,28) [dev]. */
 int dmb_philox_normal(dmb_ctx* ctx, float* out, int B, uint64_t seed, uint64_t sample_offset, int t,

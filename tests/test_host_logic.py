@@ -194,3 +194,43 @@ def test_strided_coefficients_match_ddim_formula():
     import pytest
     with pytest.raises(ValueError):
         d.strided_coefficients(7)
+
+
+def test_png_batch_writer_round_trips_pixels(tmp_path):
+    """Extension N4 (output path): the native parallel PNG writer behind Utils.saveImages(tensor).
+    Every file must decode (PIL) to exactly the pixels that went in, under the reference's file
+    names (utils.py:216-224), for RGB and grey, odd sizes and every compression level used."""
+    import numpy as np
+    import torch
+    from PIL import Image
+    from utils import Utils
+    from dmb200 import write_png_batch
+    rng = np.random.default_rng(0)
+    imgs = torch.from_numpy(rng.integers(0, 256, (37, 3, 224, 224), dtype=np.uint8))
+    imgs[0] = 255
+    imgs[1] = 0
+    Utils.saveImages(str(tmp_path), imgs)
+    for i in range(imgs.shape[0]):
+        im = Image.open(tmp_path / f"pic{i + 1}.png")
+        assert im.mode == "RGB" and im.size == (224, 224)
+        assert np.array_equal(np.moveaxis(np.array(im), -1, 0), imgs[i].numpy()), i
+    # same pixels as the reference's own path (ToPILImage-equivalent -> image.save)
+    ref_dir = tmp_path / "ref"
+    ref_dir.mkdir()
+    Utils.saveImages(str(ref_dir), [Image.fromarray(np.moveaxis(imgs[i].numpy(), 0, -1), mode="RGB") for i in range(3)])
+    for i in range(3):
+        assert np.array_equal(np.array(Image.open(ref_dir / f"pic{i + 1}.png")), np.array(Image.open(tmp_path / f"pic{i + 1}.png")))
+    grey = torch.from_numpy(rng.integers(0, 256, (5, 28, 31), dtype=np.uint8))
+    for level in (0, 1, 9):
+        paths = [str(tmp_path / f"g{level}_{i}.png") for i in range(5)]
+        write_png_batch(grey, paths, threads=2, compression_level=level)
+        for i, p in enumerate(paths):
+            im = Image.open(p)
+            assert im.mode == "L" and np.array_equal(np.array(im), grey[i].numpy())
+    Utils.saveStepImages(str(tmp_path), imgs[:2], [1000, 1])
+    assert (tmp_path / "t1000.png").exists() and (tmp_path / "t1.png").exists()
+    with pytest.raises(ValueError):
+        write_png_batch(grey, ["only_one.png"])
+    from dmb200 import NativeError
+    with pytest.raises(NativeError):
+        write_png_batch(grey[:1], [str(tmp_path / "no_such_dir" / "x.png")])
