@@ -426,7 +426,10 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   const int r_begin = g.Wp + blockIdx.x * per;
   const int r_end = min(g.S, r_begin + per);
   const size_t base = static_cast<size_t>(b) * g.S;
-  constexpr int U = (MODE == GN_RES_GELU || kLN) ? 4 : 8;  // 16-byte loads in flight per thread and stream
+  // Two register batches of U 16-byte loads per stream: the next batch is issued BEFORE the
+  // current one is consumed, so loads stay in flight while the GELU runs (the kernel is bound by
+  // its load -> compute -> store latency chain, not by HBM or by issue slots).
+  constexpr int U = (MODE == GN_RES_GELU || kLN) ? 2 : 4;
   float lw[8], lb[8];
   uint32_t row_mask = 0xffffffffu;   // the lanes that share this thread's row
   if constexpr (kLN) {
@@ -440,7 +443,8 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   // Incremental addressing: the row advances by rows_per_iter per load, its column inside the
   // padded image row (x) is tracked modulo Wp, so the loop has no division and no 64-bit
   // multiply.
-  int rr = r_begin + tid / vpr;
+  int rr = r_begin + tid / vpr;       // row cursor of the consumer
+  int ri = rr;                        // row cursor of the load issue (one batch ahead)
   int x = rr - fdiv(rr, g.mWp, g.Wp) * g.Wp;
   const int xstep = rows_per_iter - fdiv(rows_per_iter, g.mWp, g.Wp) * g.Wp;  // rows_per_iter mod Wp
   const size_t first = (base + rr) * C + c0;
@@ -449,12 +453,10 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   T* op = out + first;
   if constexpr (kLN) pp = out_pre ? out_pre + first : nullptr;
   const int stride = rows_per_iter * C;
-  while (rr < r_end) {
-    Raw8<T> xr[U], rs[U];
-    bool ok[U];
+  auto issue = [&](Raw8<T>* xr, Raw8<T>* rs, bool* ok) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      ok[u] = (rr + u * rows_per_iter < r_end) && (x != g.W);
+      ok[u] = (ri + u * rows_per_iter < r_end) && (x != g.W);
       if (ok[u]) {
         xr[u].load(rp + u * stride);
         if (MODE == GN_RES_GELU) rs[u].load(sp + u * stride);
@@ -462,6 +464,11 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
       x += xstep;
       if (x >= g.Wp) x -= g.Wp;
     }
+    ri += U * rows_per_iter;
+    rp += U * stride;
+    if (MODE == GN_RES_GELU) sp += U * stride;
+  };
+  auto consume = [&](const Raw8<T>* xr, const Raw8<T>* rs, const bool* ok) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (ok[u]) {
@@ -500,10 +507,18 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
       }
     }
     rr += U * rows_per_iter;
-    rp += U * stride;
-    if (MODE == GN_RES_GELU) sp += U * stride;
     op += U * stride;
     if constexpr (kLN) { if (pp) pp += U * stride; }
+  };
+  Raw8<T> xa[U], ra[U], xb[U], rb[U];
+  bool oka[U], okb[U];
+  issue(xa, ra, oka);
+  while (rr < r_end) {
+    issue(xb, rb, okb);
+    consume(xa, ra, oka);
+    if (rr >= r_end) break;
+    issue(xa, ra, oka);
+    consume(xb, rb, okb);
   }
 }
 
