@@ -43,6 +43,12 @@ __device__ __forceinline__ uint32_t pil_luma(uint32_t r, uint32_t g, uint32_t b)
 
 // foreground bytes (0 / 1) of four pixels packed in a word
 __device__ __forceinline__ uint32_t fg4(uint32_t r, uint32_t g, uint32_t b, int channels, int threshold, int invert) {
+  if (channels == 0) {   // mask bytes: non-zero -> 1 (OR-fold every byte into its lowest bit)
+    uint32_t x = r | (r >> 4);
+    x |= x >> 2;
+    x |= x >> 1;
+    return x & 0x01010101u;
+  }
   uint32_t out = 0;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -115,12 +121,22 @@ score_masks_kernel(const ScoreParams p) {
   binarise_plane(p.gt + static_cast<size_t>(b) * gc * HW, p.gt_channels, HW, p.threshold, p.invert, g);
   __syncthreads();
 
-  {  // areas
-    int c_inter = 0, c_union = 0, c_gt = 0, c_pred = 0, c_fp = 0;
-    for (int i = tid; i < HW; i += kScoreThreads) {
-      const int a = g[i], q = pm[i];
-      c_inter += a & q; c_union += a | q; c_gt += a; c_pred += q; c_fp += q & (a ^ 1);
+  {  // areas: 16 pixels per load, the 0 / 1 bytes counted with popc
+    int c_inter = 0, c_union = 0, c_gt = 0, c_pred = 0;
+    const int n16 = HW >> 4;
+    for (int i = tid; i < n16; i += kScoreThreads) {
+      const uint4 a = *reinterpret_cast<const uint4*>(g + 16 * i);
+      const uint4 q = *reinterpret_cast<const uint4*>(pm + 16 * i);
+      c_inter += __popc(a.x & q.x) + __popc(a.y & q.y) + __popc(a.z & q.z) + __popc(a.w & q.w);
+      c_union += __popc(a.x | q.x) + __popc(a.y | q.y) + __popc(a.z | q.z) + __popc(a.w | q.w);
+      c_gt += __popc(a.x) + __popc(a.y) + __popc(a.z) + __popc(a.w);
+      c_pred += __popc(q.x) + __popc(q.y) + __popc(q.z) + __popc(q.w);
     }
+    for (int i = 16 * n16 + tid; i < HW; i += kScoreThreads) {
+      const int a = g[i], q = pm[i];
+      c_inter += a & q; c_union += a | q; c_gt += a; c_pred += q;
+    }
+    int c_fp = c_pred - c_inter;   // pred and not gt
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       c_inter += __shfl_xor_sync(0xffffffffu, c_inter, o);
@@ -210,14 +226,27 @@ score_masks_kernel(const ScoreParams p) {
         if (gt_empty) {
           d2 = static_cast<long long>(y + 1) * (y + 1) + static_cast<long long>(x) * x;
         } else {
+          // the 32 columns around x first: a candidate <= 16^2 there cannot be beaten by a
+          // column at least 16 away, which is the common case (predictions lie near the truth)
           int best = 0x7fffffff;
           const uint8_t* grow = g + y * W;
-          for (int xx = lane; xx < W; xx += 32) {
-            const int gy = grow[xx];
-            if (gy != 255) best = min(best, (x - xx) * (x - xx) + gy * gy);
+          {
+            const int xx = x - 16 + lane;
+            if (xx >= 0 && xx < W) {
+              const int gy = grow[xx];
+              if (gy != 255) best = (x - xx) * (x - xx) + gy * gy;
+            }
           }
 #pragma unroll
           for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+          if (best > 256) {   // (uniform: every lane holds the minimum) -- search the whole row
+            for (int xx = lane; xx < W; xx += 32) {
+              const int gy = grow[xx];
+              if (gy != 255) best = min(best, (x - xx) * (x - xx) + gy * gy);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+          }
           d2 = best;
         }
         if (lane == src) d2_mine = d2;
