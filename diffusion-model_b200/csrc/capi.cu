@@ -152,6 +152,30 @@ int dmb_vae_decode(dmb_ctx* ctx, const float* z, int B, float* img_f32, uint8_t*
   });
 }
 
+int dmb_load_vae_enc_weights(dmb_ctx* ctx, int n, const char* const* names, const void* const* ptrs,
+                             const int64_t* numels) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx, "ctx is NULL");
+    ctx->eng->load_vae_enc(collect(n, names, ptrs, numels));
+  });
+}
+
+int dmb_vae_encode(dmb_ctx* ctx, const float* img, const float* eps, int B, float* z, float* mu, float* logvar,
+                   float* kl_sample, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && img && eps && z && kl_sample, "ctx, img, eps, z and kl_sample are required");
+    ctx->eng->vae_encode(img, eps, B, z, mu, logvar, kl_sample, st(stream));
+  });
+}
+
+int dmb_add_noise(dmb_ctx* ctx, const float* x0, const int64_t* t, const float* alpha_bars, int T,
+                  const float* noise, int B, int64_t per_sample, float* x_t, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && x0 && t && alpha_bars && noise && x_t, "ctx, x0, t, alpha_bars, noise and x_t are required");
+    ctx->eng->add_noise(x0, ll(t), alpha_bars, T, noise, B, static_cast<long long>(per_sample), x_t, st(stream));
+  });
+}
+
 int dmb_score_masks(dmb_ctx* ctx, const uint8_t* pred, int pred_channels, const uint8_t* gt, int gt_channels,
                     int B, int H, int W, int threshold, int invert, double sigma, int64_t* counts,
                     double* weighted_hit, void* stream) {

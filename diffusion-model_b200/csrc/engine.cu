@@ -147,6 +147,21 @@ __global__ void repack_convT_kernel(const float* __restrict__ w, int Ci, int Co,
   const int kx = (pb == 0) ? (tv == 0 ? 1 : 3) : (tv == 0 ? 0 : 2);
   out[i] = from_f32<T>(w[((static_cast<size_t>(ci) * Co + co) * 4 + ky) * 4 + kx]);
 }
+// Conv2d(4, stride 2, pad 1) weight [Co][Ci][4][4] -> [tap(u,v)][Co][(sy*2+sx)*Ci + ci] with
+// ky = 2u + sy, kx = 2v + sx: the 2x2-tap form over the offset space-to-depth input
+// (kernels.cuh, gn8_apply_gelu_s2d_kernel).
+template <typename T>
+__global__ void repack_conv4s2_kernel(const float* __restrict__ w, int Co, int Ci, T* __restrict__ out) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long total = 16LL * Co * Ci;
+  if (i >= total) return;
+  const int ci = static_cast<int>(i % Ci);
+  const int q = static_cast<int>((i / Ci) % 4);
+  const int co = static_cast<int>((i / (4LL * Ci)) % Co);
+  const int tap = static_cast<int>(i / (4LL * Ci * Co));
+  const int ky = 2 * (tap >> 1) + (q >> 1), kx = 2 * (tap & 1) + (q & 1);
+  out[i] = from_f32<T>(w[((static_cast<size_t>(co) * Ci + ci) * 4 + ky) * 4 + kx]);
+}
 template <typename T>
 __global__ void cast_kernel(const float* __restrict__ in, long long n, T* __restrict__ out) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -327,6 +342,11 @@ class Engine : public IEngine {
                    const float* noise, unsigned long long seed, unsigned long long sample_offset, float* x_dump,
                    float* eps_dump, int B, cudaStream_t s) override;
   void vae_decode(const float* z, int B, float* img_f32, uint8_t* img_u8, cudaStream_t s) override;
+  void load_vae_enc(const TensorMapIn& w) override;
+  void vae_encode(const float* img, const float* eps, int B, float* z, float* mu, float* logvar, float* kl_sample,
+                  cudaStream_t s) override;
+  void add_noise(const float* x0, const long long* t, const float* alpha_bars, int T_steps, const float* noise, int B,
+                 long long per_sample, float* x_t, cudaStream_t s) override;
   void get_tap(const char* name, float* out, int64_t capacity, int64_t* shape4, cudaStream_t s) override;
   void op_conv3x3(const float* x, const float* w, int B, int Cin, int Cout, int H, int W, float* out,
                   cudaStream_t s) override;
@@ -361,6 +381,7 @@ class Engine : public IEngine {
   GemmW<T> make_conv3x3_w(const std::string& name, int Co, int Ci, Pool& pool);
   GemmW<T> make_linear_w(const std::string& wname, const std::string& bname, int N, int K, Pool& pool);
   GemmW<T> make_convT_w(const std::string& wname, const std::string& bname, int Ci, int Co, Pool& pool);
+  GemmW<T> make_conv4s2_w(const std::string& wname, const std::string& bname, int Ci, int Co, Pool& pool);
   GemmW<T> make_conv3x3_from_ptr(const float* w_dev, int Co, int Ci, Pool& pool);
 
   // ---- launch helpers
@@ -465,6 +486,21 @@ class Engine : public IEngine {
   };
   std::unique_ptr<VaePlan> vae_plan_;
   void build_vae_plan(VaePlan& p, int B);
+  struct VaeEncPlan {
+    Pool pool;
+    OpList ops;
+    int B = 0;
+    const float* img = nullptr;
+    const float* eps = nullptr;
+    float* z = nullptr;
+    float* mu = nullptr;
+    float* logvar = nullptr;
+    float* kl = nullptr;
+  };
+  std::unique_ptr<VaeEncPlan> vae_enc_plan_;
+  void build_vae_enc_plan(VaeEncPlan& p, int B);
+  Pool wpool_vae_enc_;
+  bool vae_enc_loaded_ = false;
 
   void count(int n = 1) {
     if (counting_) launches_ += n;
@@ -538,6 +574,22 @@ GemmW<T> Engine<T>::make_convT_w(const std::string& wname, const std::string& bn
   repack_convT_kernel<T><<<cdiv(16LL * Co * Ci, 256), 256>>>(f(wname), Ci, Co, g.w);
   DMB_CHECK_LAUNCH();
   for (int i = 0; i < 6; ++i) g.tmap_bn[i] = make_tmap<T>(g.w, Ci, 16ull * Co, 8 << i);
+  if (!bname.empty()) g.bias = f(bname);
+  return g;
+}
+
+template <typename T>
+GemmW<T> Engine<T>::make_conv4s2_w(const std::string& wname, const std::string& bname, int Ci, int Co, Pool& pool) {
+  DMB_REQUIRE(numel(wname) == 16LL * Co * Ci, "unexpected size of " + wname);
+  GemmW<T> g;
+  g.K = 4 * Ci; g.N = Co; g.ntaps = 4;
+  g.bn = pick_block_n(Co);
+  g.rows_per_tap = Co;
+  DMB_REQUIRE(Co % g.bn == 0, "strided-conv output channels must be a multiple of the N tile");
+  g.w = pool.alloc_n<T>(16ull * Co * Ci);
+  repack_conv4s2_kernel<T><<<cdiv(16LL * Co * Ci, 256), 256>>>(f(wname), Co, Ci, g.w);
+  DMB_CHECK_LAUNCH();
+  for (int i = 0; i < 6; ++i) g.tmap_bn[i] = make_tmap<T>(g.w, 4 * Ci, 4ull * Co, 8 << i);
   if (!bname.empty()) g.bias = f(bname);
   return g;
 }
@@ -1439,6 +1491,169 @@ void Engine<T>::vae_decode(const float* z, int B, float* img_f32, uint8_t* img_u
     p.img_u8 = img_u8 ? img_u8 + b0 * img : nullptr;
     run_list(p.ops, s);
   }
+}
+
+// ---------------------------------------------------------------------------
+// VAE encoder (models/vae.py:16-31, 51-62).  Weights arrive under their
+// state_dict names ("enc.0.weight", ..., "to_mu.weight", "to_logvar.bias") and are kept under
+// the prefix "venc." so that reloading the decoder does not drop them.
+// ---------------------------------------------------------------------------
+template <typename T>
+void Engine<T>::load_vae_enc(const TensorMapIn& w) {
+  DMB_CUDA(cudaSetDevice(device_));
+  DMB_CUDA(cudaDeviceSynchronize());
+  vae_enc_plan_.reset();
+  for (auto it = blob_.begin(); it != blob_.end();) {
+    if (it->first.rfind("venc.", 0) == 0) it = blob_.erase(it); else ++it;
+  }
+  for (auto it = gw_.begin(); it != gw_.end();) {
+    if (it->first.rfind("venc.", 0) == 0) it = gw_.erase(it); else ++it;
+  }
+  wpool_vae_enc_.release();
+  vae_enc_loaded_ = false;
+  upload(w, "venc.", wpool_vae_enc_);
+  Pool& pool = wpool_vae_enc_;
+  DMB_REQUIRE(numel("venc.enc.0.weight") == 64 * 3 * 9, "enc.0 must be conv 3->64");
+  DMB_REQUIRE(numel("venc.to_mu.weight") == 4 * 256 && numel("venc.to_logvar.weight") == 4 * 256,
+              "to_mu / to_logvar must be 1x1 convs 256->4");
+  gw_["venc.enc.3"] = make_conv4s2_w("venc.enc.3.weight", "venc.enc.3.bias", 64, 64, pool);
+  gw_["venc.enc.6"] = make_conv3x3_w("venc.enc.6.weight", 128, 64, pool);
+  gw_["venc.enc.6"].bias = f("venc.enc.6.bias");
+  gw_["venc.enc.9"] = make_conv4s2_w("venc.enc.9.weight", "venc.enc.9.bias", 128, 128, pool);
+  gw_["venc.enc.12"] = make_conv3x3_w("venc.enc.12.weight", 256, 128, pool);
+  gw_["venc.enc.12"].bias = f("venc.enc.12.bias");
+  gw_["venc.enc.15"] = make_conv4s2_w("venc.enc.15.weight", "venc.enc.15.bias", 256, 256, pool);
+  DMB_CUDA(cudaDeviceSynchronize());
+  vae_enc_loaded_ = true;
+}
+
+template <typename T>
+void Engine<T>::build_vae_enc_plan(VaeEncPlan& P, int n) {
+  Pool& pool = P.pool;
+  P.B = n;
+  auto& ops = P.ops;
+  VaeEncPlan* pp = &P;
+
+  // GroupNorm(8)+GELU; s2d = written as the offset space-to-depth input of the strided conv
+  auto gn8 = [&](const Act<T>& raw, const std::string& name, bool s2d) {
+    Act<T> out = s2d ? new_act(pool, raw.g.n, raw.g.H / 2, raw.g.W / 2, 4 * raw.C, false)
+                     : new_act(pool, raw.g.n, raw.g.H, raw.g.W, raw.C, false);
+    const int total_vec = raw.g.H * raw.g.W * raw.C / 8;
+    const int chunks = std::max(1, std::min(32, total_vec / 4096));
+    double2* partial = pool.alloc_n<double2>(static_cast<size_t>(raw.g.n) * chunks * 8);
+    const float* gamma = f(name + ".weight");
+    const float* beta = f(name + ".bias");
+    ops.tag(s2d ? "vae-enc gn8+gelu (space-to-depth)" : "vae-enc gn8+gelu", 0,
+            3.0 * raw.g.n * total_vec * 8 * sizeof(T));
+    ops.push_back([this, raw, out, chunks, partial, gamma, beta, s2d](cudaStream_t s) {
+      gn8_stats_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, raw.g, raw.C, partial);
+      DMB_CHECK_LAUNCH();
+      if (s2d)
+        gn8_apply_gelu_s2d_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta,
+                                                                          raw.g, raw.C, out.g, out.p);
+      else
+        gn8_apply_gelu_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
+                                                                      raw.C, out.p);
+      DMB_CHECK_LAUNCH();
+      count(2);
+    });
+    return out;
+  };
+  auto conv = [&](const Act<T>& in, const std::string& wname) {
+    const GemmW<T>& w = gw_.at(wname);
+    Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, false);
+    ops.tag("vae-enc conv3x3 " + std::to_string(w.K) + "->" + std::to_string(w.N) + " @" + std::to_string(in.g.H),
+            2.0 * in.g.n * in.g.H * in.g.W * 9.0 * w.K * w.N);
+    ops.push_back(op_conv(in, w, out));
+    return out;
+  };
+  // 4x4 / stride 2 / pad 1 as a 2x2-tap GEMM over the space-to-depth input (K = 4 C_in per tap)
+  auto conv4s2 = [&](const Act<T>& in, const std::string& wname) {
+    const GemmW<T> w = gw_.at(wname);
+    Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, false);
+    ops.tag("vae-enc conv4x4s2 " + std::to_string(w.K / 4) + "->" + std::to_string(w.N) + " @" +
+                std::to_string(in.g.H * 2),
+            2.0 * in.g.n * in.g.H * in.g.W * 4.0 * w.K * w.N);
+    ops.push_back([this, in, w, out](cudaStream_t s) {
+      const int shifts[4] = {0, 1, in.g.Wp, in.g.Wp + 1};
+      GemmParams ep{};
+      ep.epi = EPI_STORE;
+      ep.out = out.p; ep.ldc = out.C; ep.bias = w.bias;
+      gemm(in, w, 0, shifts, 4, ep, s, &out);
+    });
+    return out;
+  };
+
+  Act<T> r0 = new_act(pool, n, 224, 224, 64, false);
+  {
+    const float* w0 = f("venc.enc.0.weight");
+    const float* b0 = f("venc.enc.0.bias");
+    ops.tag("vae-enc conv_in 3->64 @224", 2.0 * n * 224.0 * 224 * 27 * 64);
+    ops.push_back([this, r0, w0, b0, pp, n](cudaStream_t s) {
+      conv_in_kernel<T, 3><<<dim3(cdiv(224 * 224, 128), n, 1), 128, 0, s>>>(pp->img, n, w0, b0, 1.0f, r0.g, 64, r0.p,
+                                                                           nullptr);
+      DMB_CHECK_LAUNCH();
+      count();
+    });
+  }
+  Act<T> a = gn8(r0, "venc.enc.1", true);
+  a = gn8(conv4s2(a, "venc.enc.3"), "venc.enc.4", false);
+  a = gn8(conv(a, "venc.enc.6"), "venc.enc.7", true);
+  a = gn8(conv4s2(a, "venc.enc.9"), "venc.enc.10", false);
+  a = gn8(conv(a, "venc.enc.12"), "venc.enc.13", true);
+  a = gn8(conv4s2(a, "venc.enc.15"), "venc.enc.16", false);
+  {
+    const float* wm = f("venc.to_mu.weight");
+    const float* bm = f("venc.to_mu.bias");
+    const float* wl = f("venc.to_logvar.weight");
+    const float* bl = f("venc.to_logvar.bias");
+    ops.tag("vae-enc to_mu/to_logvar + reparameterise + KL", 2.0 * n * kLatH * kLatW * 256 * 8);
+    ops.push_back([this, a, wm, bm, wl, bl, pp, n](cudaStream_t s) {
+      vae_enc_head_kernel<T><<<n, 256, 0, s>>>(a.p, a.g, a.C, wm, bm, wl, bl, pp->eps, 0.18215f, 224.0f * 224.0f,
+                                               pp->z, pp->mu, pp->logvar, pp->kl);
+      DMB_CHECK_LAUNCH();
+      count();
+    });
+  }
+}
+
+template <typename T>
+void Engine<T>::vae_encode(const float* img, const float* eps, int B, float* z, float* mu, float* logvar,
+                           float* kl_sample, cudaStream_t s) {
+  DMB_CUDA(cudaSetDevice(device_));
+  if (!vae_enc_loaded_) fail(5, "VAE encoder weights have not been loaded (dmb_load_vae_enc_weights)");
+  DMB_REQUIRE(B >= 1, "batch must be >= 1");
+  const int kChunk = 32;
+  const size_t lat = static_cast<size_t>(kLatC) * kLatH * kLatW;
+  const size_t im = static_cast<size_t>(3) * 224 * 224;
+  for (int b0 = 0; b0 < B; b0 += kChunk) {
+    const int n = std::min(kChunk, B - b0);
+    if (!vae_enc_plan_ || vae_enc_plan_->B != n) {
+      DMB_CUDA(cudaStreamSynchronize(s));
+      vae_enc_plan_.reset(new VaeEncPlan());
+      build_vae_enc_plan(*vae_enc_plan_, n);
+      DMB_CUDA(cudaDeviceSynchronize());
+    }
+    VaeEncPlan& p = *vae_enc_plan_;
+    p.img = img + b0 * im;
+    p.eps = eps + b0 * lat;
+    p.z = z + b0 * lat;
+    p.mu = mu ? mu + b0 * lat : nullptr;
+    p.logvar = logvar ? logvar + b0 * lat : nullptr;
+    p.kl = kl_sample + b0;
+    run_list(p.ops, s);
+  }
+}
+
+template <typename T>
+void Engine<T>::add_noise(const float* x0, const long long* t, const float* alpha_bars, int T_steps, const float* noise,
+                          int B, long long per_sample, float* x_t, cudaStream_t s) {
+  DMB_CUDA(cudaSetDevice(device_));
+  DMB_REQUIRE(B >= 1 && per_sample >= 1 && T_steps >= 1, "B, per_sample and T must be >= 1");
+  const int gx = static_cast<int>(std::min<long long>(cdiv(per_sample, 256), 64));
+  add_noise_kernel<<<dim3(gx, B), 256, 0, s>>>(x0, t, alpha_bars, T_steps, noise, per_sample, x_t);
+  DMB_CHECK_LAUNCH();
+  count();
 }
 
 // ---------------------------------------------------------------------------

@@ -44,6 +44,12 @@ class IEngine {
                            const float* noise, unsigned long long seed, unsigned long long sample_offset,
                            float* x_dump, float* eps_dump, int B, cudaStream_t s) = 0;
   virtual void vae_decode(const float* z, int B, float* img_f32, uint8_t* img_u8, cudaStream_t s) = 0;
+  // VAE encoder + forward diffusion
+  virtual void load_vae_enc(const TensorMapIn& w) = 0;
+  virtual void vae_encode(const float* img, const float* eps, int B, float* z, float* mu, float* logvar,
+                          float* kl_sample, cudaStream_t s) = 0;
+  virtual void add_noise(const float* x0, const long long* t, const float* alpha_bars, int T, const float* noise,
+                         int B, long long per_sample, float* x_t, cudaStream_t s) = 0;
   virtual void get_tap(const char* name, float* out, int64_t capacity, int64_t* shape4, cudaStream_t s) = 0;
   virtual void op_conv3x3(const float* x, const float* w, int B, int Cin, int Cout, int H, int W, float* out,
                           cudaStream_t s) = 0;

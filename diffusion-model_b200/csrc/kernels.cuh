@@ -127,29 +127,31 @@ emb_kernel(EmbWeights w, const long long* __restrict__ t_vec, const long long* _
 // ---------------------------------------------------------------------------
 // Direct 3x3 / pad 1 convolution from an fp32 NCHW latent (4 channels) into a PM
 // activation.  Used for inc.double_conv.0 (4->64, no bias, GroupNorm row statistics)
-// and the VAE decoder's dec.0 (4->256, bias, input divided by the VAE scale factor).
+// and the VAE decoder's dec.0 (4->256, bias, input divided by the VAE scale factor); with
+// kCin = 3 it is the VAE encoder's enc.0 on the fp32 image (3->64, bias).
 // Thread = one pixel x 64 output channels; blockIdx.z selects the 64-channel group.
 // ---------------------------------------------------------------------------
-template <typename T>
+template <typename T, int kCin = kLatC>
 __global__ void __launch_bounds__(128)
 conv_in_kernel(const float* __restrict__ x, int B_src, const float* __restrict__ w_oihw,
                const float* __restrict__ bias, float in_div, Geo g, int cout,
                T* __restrict__ out, float2* __restrict__ rowstats) {
-  __shared__ float ws[36 * 64];
+  constexpr int kK = 9 * kCin;
+  __shared__ float ws[kK * 64];
   const int co0 = blockIdx.z * 64;
-  for (int i = threadIdx.x; i < 36 * 64; i += blockDim.x) {
+  for (int i = threadIdx.x; i < kK * 64; i += blockDim.x) {
     const int k = i / 64, co = i % 64;  // k = ci*9 + ky*3 + kx
-    ws[i] = w_oihw[(co0 + co) * 36 + k];
+    ws[i] = w_oihw[(co0 + co) * kK + k];
   }
   __syncthreads();
   const int be = blockIdx.y;
   const int pix = blockIdx.x * blockDim.x + threadIdx.x;
   if (pix >= g.H * g.W) return;
   const int y = pix / g.W, xx = pix % g.W;
-  const float* xs = x + static_cast<size_t>(be % B_src) * kLatC * g.H * g.W;
-  float in[36];
+  const float* xs = x + static_cast<size_t>(be % B_src) * kCin * g.H * g.W;
+  float in[kK];
 #pragma unroll
-  for (int ci = 0; ci < kLatC; ++ci)
+  for (int ci = 0; ci < kCin; ++ci)
 #pragma unroll
     for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
@@ -163,7 +165,7 @@ conv_in_kernel(const float* __restrict__ x, int B_src, const float* __restrict__
 #pragma unroll
   for (int co = 0; co < 64; ++co) acc[co] = bias ? bias[co0 + co] : 0.f;
 #pragma unroll
-  for (int k = 0; k < 36; ++k) {
+  for (int k = 0; k < kK; ++k) {
     const float v = in[k];
 #pragma unroll
     for (int co = 0; co < 64; ++co) acc[co] = fmaf(v, ws[k * 64 + co], acc[co]);
@@ -1053,6 +1055,146 @@ __global__ void pm_to_nchw_kernel(const T* __restrict__ in, Geo g, int C, int ld
   const int b = static_cast<int>(pix / g.H);
   out[((static_cast<size_t>(b) * C + c) * g.H + y) * g.W + x] =
       to_f32(in[static_cast<size_t>(geo_row(g, b, y, x)) * ld + col0 + c]);
+}
+
+// ---------------------------------------------------------------------------
+// VAE encoder (models/vae.py:16-31, 51-62).
+//
+// GroupNorm(8)+GELU whose consumer is a 4x4 / stride-2 / pad-1 convolution: the result is written
+// "space-to-depth with a one-pixel offset".  Position (py, px) of the half-resolution pixel
+// matrix -- ALL (H/2+1) x (W/2+1) positions of a sample, the pad column and pad row included --
+// holds the 2x2 block of source pixels (2py-1+sy, 2px-1+sx), sy, sx in {0,1}, as 4C channels
+// ((sy*2+sx)*C + c), zeros outside the image.  Output pixel (oy, ox) of the strided conv then
+// reads source rows 2oy-1 .. 2oy+2 = positions oy and oy+1: a 2x2-tap, stride-1 convolution with
+// K = 4C per tap and shifts {0, 1, Wp, Wp+1}, which is what the tcgen05 GEMM already runs -- no
+// strided gathers, no zero-padded K.
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+gn8_apply_gelu_s2d_kernel(const T* __restrict__ raw, const double2* __restrict__ partial, int n_chunks_stats,
+                          const float* __restrict__ gamma, const float* __restrict__ beta, Geo g, int C,
+                          Geo g2, T* __restrict__ out) {
+  __shared__ float s_mean[8], s_rstd[8];
+  const int b = blockIdx.y, tid = threadIdx.x;
+  if (tid < 8) {
+    double a = 0.0, q = 0.0;
+    for (int k = 0; k < n_chunks_stats; ++k) {
+      const double2 v = partial[(static_cast<size_t>(b) * n_chunks_stats + k) * 8 + tid];
+      a += v.x; q += v.y;
+    }
+    const double cnt = static_cast<double>(g.H) * g.W * (C / 8);
+    const double mean = a / cnt;
+    double var = q / cnt - mean * mean;
+    if (var < 0.0) var = 0.0;
+    s_mean[tid] = static_cast<float>(mean);
+    s_rstd[tid] = static_cast<float>(1.0 / sqrt(var + 1e-5));
+  }
+  __syncthreads();
+  const int vpr = C / 8, vpg = vpr / 8;
+  const int total = g2.S * 4 * vpr;          // every position of the sample, 4 source pixels each
+  const int per = (total + gridDim.x - 1) / gridDim.x;
+  const int begin = blockIdx.x * per;
+  const int end = min(total, begin + per);
+  for (int v = begin + tid; v < end; v += 256) {
+    const int vc = v % vpr, q = (v / vpr) & 3, pos = v / (4 * vpr);
+    const int py = pos / g2.Wp, px = pos - py * g2.Wp;
+    const int y = 2 * py - 1 + (q >> 1), x = 2 * px - 1 + (q & 1);
+    float xv[8];
+    if (y >= 0 && y < g.H && x >= 0 && x < g.W) {
+      const int c0 = vc * 8;
+      const float mean = s_mean[vc / vpg], rstd = s_rstd[vc / vpg];
+      load8(raw + static_cast<size_t>(geo_row(g, b, y, x)) * C + c0, xv);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>((xv[i] - mean) * rstd * gamma[c0 + i] + beta[c0 + i]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xv[i] = 0.f;
+    }
+    store8(out + (static_cast<size_t>(b) * g2.S + pos) * (4 * C) + q * C + vc * 8, xv);
+  }
+}
+
+// to_mu / to_logvar (1x1 convs, 256 -> 4 each), clamp, reparameterisation with the caller's
+// eps, latent scaling and the per-sample KL term (models/vae.py:53-62).  One CTA per sample,
+// one warp per pixel (lanes split the channels); the KL sum is accumulated in float64 in a
+// fixed order.  kl_sample[b] = 0.5 * sum(exp(logvar) + mu^2 - 1 - logvar) / kl_div.
+template <typename T>
+__global__ void __launch_bounds__(256)
+vae_enc_head_kernel(const T* __restrict__ h, Geo g, int C, const float* __restrict__ w_mu,
+                    const float* __restrict__ b_mu, const float* __restrict__ w_lv,
+                    const float* __restrict__ b_lv, const float* __restrict__ eps, float scale, float kl_div,
+                    float* __restrict__ z, float* __restrict__ mu_out, float* __restrict__ logvar_out,
+                    float* __restrict__ kl_sample) {
+  __shared__ double s_kl[8];
+  const int b = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int HW = g.H * g.W;
+  const int c0 = lane * 8;   // C == 256: eight channels per lane
+  float wm[4][8], wl[4][8];
+#pragma unroll
+  for (int o = 0; o < 4; ++o)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      wm[o][i] = w_mu[o * C + c0 + i];
+      wl[o][i] = w_lv[o * C + c0 + i];
+    }
+  double kl = 0.0;
+  for (int pix = warp; pix < HW; pix += 8) {
+    float xv[8];
+    load8(h + static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * C + c0, xv);
+    float acc[8];
+#pragma unroll
+    for (int o = 0; o < 4; ++o) {
+      float a = 0.f, l = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { a = fmaf(xv[i], wm[o][i], a); l = fmaf(xv[i], wl[o][i], l); }
+      acc[o] = a; acc[4 + o] = l;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], d);
+    if (lane < 4) {
+      const int o = lane;
+      float m = 0.f, lv = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) if (j == o) { m = acc[j]; lv = acc[4 + j]; }
+      m += b_mu[o];
+      lv = fminf(fmaxf(lv + b_lv[o], -30.0f), 20.0f);
+      const size_t idx = (static_cast<size_t>(b) * 4 + o) * HW + pix;
+      const float sd = expf(0.5f * lv);
+      z[idx] = (m + eps[idx] * sd) * scale;
+      if (mu_out) mu_out[idx] = m;
+      if (logvar_out) logvar_out[idx] = lv;
+      kl += static_cast<double>(expf(lv)) + static_cast<double>(m) * m - 1.0 - lv;
+    }
+  }
+  // lanes 0..3 of each warp hold partial sums: fold them, then the eight warps in order
+  kl += __shfl_down_sync(0xffffffffu, kl, 2);
+  kl += __shfl_down_sync(0xffffffffu, kl, 1);
+  if (lane == 0) s_kl[warp] = kl;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += s_kl[w];
+    kl_sample[b] = static_cast<float>(0.5 * t / kl_div);
+  }
+}
+
+// Diffuser.add_noise (diff.py:18-30): x_t = sqrt(ab) * x_0 + sqrt(1 - ab) * noise with
+// ab = alpha_bars[t - 1] per sample.  Every operation is rounded separately, like the three
+// torch kernels of the reference, so the result is bit-identical for the same noise.
+static __global__ void __launch_bounds__(256)
+add_noise_kernel(const float* __restrict__ x0, const long long* __restrict__ t, const float* __restrict__ alpha_bars,
+                 int T, const float* __restrict__ noise, long long per_sample, float* __restrict__ x_t) {
+  const int b = blockIdx.y;
+  long long ti = t[b] - 1;
+  ti = ti < 0 ? 0 : (ti >= T ? T - 1 : ti);
+  const float ab = alpha_bars[ti];
+  const float sa = sqrtf(ab), sb = sqrtf(__fsub_rn(1.0f, ab));
+  const long long base = static_cast<long long>(b) * per_sample;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < per_sample;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    x_t[base + i] = __fadd_rn(__fmul_rn(sa, x0[base + i]), __fmul_rn(sb, noise[base + i]));
 }
 
 }  // namespace dmb

@@ -264,8 +264,18 @@ class Diffuser:
         return ret([self.reverse_to_img(images[i]) for i in range(B)] if to_pil else images)
 
     # ------------------------------------------------------------------ not on the sampling path
-    def add_noise(self, x_0, t):
-        raise NotImplementedError("add_noise is the training-side forward process (diff.py:18-30); out of scope")
+    # ------------------------------------------------------------------ forward process (8f N3)
+    def add_noise(self, x_0, t, noise=None):
+        """(x_t, noise) like the reference (diff.py:18-30): the same range assertion, the same
+        ``torch.randn_like`` draw (pass ``noise`` to supply it), and the blend on the device with
+        every operation rounded separately -- bit-identical to the reference for the same noise."""
+        from dmb200 import context_for
+        assert (t >= 1).all() and (t <= self.num_timesteps).all()
+        if noise is None:
+            noise = torch.randn_like(x_0)
+        ctx = context_for(x_0.device)
+        x_t = ctx.add_noise(x_0, t.to(x_0.device), self.alpha_bars.to(x_0.device), noise)
+        return x_t, noise
 
     def denoise(self, model, x, t):
         raise NotImplementedError("unconditional denoise (diff.py:32-56) is outside the CFG sampling path")

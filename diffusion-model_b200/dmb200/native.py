@@ -43,6 +43,9 @@ _SIGNATURES = {
     "dmb_sample_loop_strided": (C.c_int, [_P, _P, _P, C.c_int, _P, _P, C.c_float, _P, C.c_int, C.c_int, C.c_int,
                                           C.c_int, _P, C.c_uint64, C.c_uint64, _P, _P, C.c_int, _P]),
     "dmb_vae_decode": (C.c_int, [_P, _P, C.c_int, _P, _P, _P]),
+    "dmb_load_vae_enc_weights": (C.c_int, [_P, C.c_int, C.POINTER(C.c_char_p), C.POINTER(_P), C.POINTER(C.c_int64)]),
+    "dmb_vae_encode": (C.c_int, [_P, _P, _P, C.c_int, _P, _P, _P, _P, _P]),
+    "dmb_add_noise": (C.c_int, [_P, _P, _P, _P, C.c_int, _P, C.c_int, C.c_int64, _P, _P]),
     "dmb_score_masks": (C.c_int, [_P, _P, C.c_int, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
                                   _P, _P, _P]),
     "dmb_write_png_batch": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_char_p), C.c_int, C.c_int]),
@@ -142,6 +145,7 @@ class Context:
         self._call("dmb_ctx_create", device.index, _PRECISION_NAMES[precision], C.byref(self._h))
         self._unet_token = None
         self._vae_token = None
+        self._vae_enc_token = None
 
     # -- plumbing
     def _call(self, name, *args):
@@ -199,6 +203,14 @@ class Context:
         if tok != self._vae_token:
             self._load("dmb_load_vae_dec_weights", {k: sd[k] for k in keys})
             self._vae_token = tok
+
+    def ensure_vae_enc(self, module: torch.nn.Module):
+        sd = module.state_dict(keep_vars=True)
+        keys = [k for k in sd if k.startswith(("enc.", "to_mu.", "to_logvar."))]
+        tok = (id(module),) + self._token(module, keys)
+        if tok != self._vae_enc_token:
+            self._load("dmb_load_vae_enc_weights", {k: sd[k] for k in keys})
+            self._vae_enc_token = tok
 
     # -- compute
     def unet_forward(self, x, t, y, vals, mask, want_geom=True):
@@ -261,6 +273,38 @@ class Context:
         u8 = torch.empty((B, 3, 224, 224), device=self.device, dtype=torch.uint8) if want_u8 else None
         self._call("dmb_vae_decode", self._h, _ptr(z), B, _ptr(f32), _ptr(u8), self._stream())
         return f32, u8
+
+    def vae_encode(self, img, eps, want_moments=False):
+        """VAE.encode on the device (vae.py:51-62).  img (B,3,224,224) fp32, eps (B,4,28,28) fp32 CUDA
+        tensors.  Returns (z, kl_per_sample, mu, logvar); mu / logvar are None unless want_moments."""
+        B = img.shape[0]
+        img = _check_dev(img.to(torch.float32).contiguous(), self.device, torch.float32, "x")
+        eps = _check_dev(eps.to(torch.float32).contiguous(), self.device, torch.float32, "eps")
+        if tuple(eps.shape) != (B, 4, 28, 28):
+            raise ValueError(f"eps must be ({B},4,28,28), got {tuple(eps.shape)}")
+        z = torch.empty((B, 4, 28, 28), device=self.device, dtype=torch.float32)
+        mu = torch.empty_like(z) if want_moments else None
+        logvar = torch.empty_like(z) if want_moments else None
+        kl = torch.empty((B,), device=self.device, dtype=torch.float32)
+        self._call("dmb_vae_encode", self._h, _ptr(img), _ptr(eps), B, _ptr(z), _ptr(mu), _ptr(logvar), _ptr(kl),
+                   self._stream())
+        return z, kl, mu, logvar
+
+    def add_noise(self, x0, t, alpha_bars, noise):
+        """Diffuser.add_noise on the device (diff.py:18-30); bit-identical for the same noise."""
+        B = x0.shape[0]
+        x0 = _check_dev(x0.contiguous(), self.device, torch.float32, "x_0")
+        noise = _check_dev(noise.contiguous(), self.device, torch.float32, "noise")
+        if noise.shape != x0.shape:
+            raise ValueError(f"noise {tuple(noise.shape)} does not match x_0 {tuple(x0.shape)}")
+        t = _check_dev(t.to(torch.long).contiguous(), self.device, torch.long, "t")
+        if t.numel() != B:
+            raise ValueError(f"t must hold one timestep per sample ({B}), got {t.numel()}")
+        ab = _check_dev(alpha_bars.to(torch.float32).contiguous(), self.device, torch.float32, "alpha_bars")
+        out = torch.empty_like(x0)
+        self._call("dmb_add_noise", self._h, _ptr(x0), _ptr(t), _ptr(ab), int(ab.numel()), _ptr(noise), B,
+                   int(x0.numel() // B), _ptr(out), self._stream())
+        return out
 
     def score_masks(self, pred, gt, threshold=128, invert=True, sigma=2.0):
         """Device-side counters of eval_iou_noise.compute_metrics for a batch.  pred / gt: uint8 CUDA

@@ -1,9 +1,10 @@
 """VAE -- B200-native drop-in for ``models/vae.py`` (vae.py:5-75).
 
-Only ``decode`` is on the sampling path (vae.py:64-69); it runs in libdmb200 (tcgen05
-convolutions / transposed convolutions, GroupNorm(8)+GELU, sigmoid).  The encoder's
-parameters are held so that reference checkpoints load, but ``encode`` is not implemented
-(SURVEY.md 8f row N3)."""
+``decode`` is on the sampling path (vae.py:64-69); it runs in libdmb200 (tcgen05
+convolutions / transposed convolutions, GroupNorm(8)+GELU, sigmoid).  ``encode``
+(vae.py:51-62) runs there too: the strided 4x4 convolutions become
+2x2-tap GEMMs over a space-to-depth activation, and the 1x1 heads, the clamp, the
+reparameterisation and the KL term are one kernel.  Forward only: no autograd."""
 from __future__ import annotations
 
 import torch
@@ -67,9 +68,37 @@ class VAE(nn.Module):
             _, u8 = self._ctx(z).vae_decode(z, want_f32=False, want_u8=True)
         return u8
 
-    def encode(self, x):
-        raise NotImplementedError("VAE.encode is not on the sampling path (SURVEY.md 8f N3); "
-                                  "Diffuser.sample_latent_cond derives the latent shape without it")
+    def _enc_ctx(self, x: torch.Tensor):
+        from dmb200 import context_for
+        if (self.in_channels, self.z_channels, self.base_channels) != (3, 4, 64) or abs(self.scale_factor - 0.18215) > 1e-12:
+            raise NotImplementedError("libdmb200 implements the default VAE (3, 4, 64, scale 0.18215)")
+        if x.dim() != 4 or tuple(x.shape[1:]) != (3, 224, 224):
+            raise ValueError(f"image batch must be (B,3,224,224), got {tuple(x.shape)}")
+        dev = self.to_mu.weight.device
+        if x.device != dev:
+            raise ValueError(f"input on {x.device} but parameters on {dev}")
+        ctx = context_for(dev, self.precision)
+        ctx.ensure_vae_enc(self)
+        return ctx
+
+    def encode(self, x, eps=None):
+        """(z, kl.mean()) like the reference (vae.py:51-62).  ``eps`` defaults to
+        ``torch.randn(B,4,28,28)`` drawn from torch's generator on the module's device -- the same
+        draw ``torch.randn_like(std)`` makes in the reference (vae.py:56)."""
+        with torch.no_grad():
+            ctx = self._enc_ctx(x)
+            if eps is None:
+                eps = torch.randn((x.shape[0], 4, 28, 28), device=x.device, dtype=torch.float32)
+            z, kl, _, _ = ctx.vae_encode(x, eps)
+            return z, kl.mean()
+
+    def encode_moments(self, x, eps=None):
+        """encode() plus the posterior moments: (z, kl_per_sample, mu, logvar_clamped)."""
+        with torch.no_grad():
+            ctx = self._enc_ctx(x)
+            if eps is None:
+                eps = torch.randn((x.shape[0], 4, 28, 28), device=x.device, dtype=torch.float32)
+            return ctx.vae_encode(x, eps, want_moments=True)
 
     def forward(self, x):
         raise NotImplementedError("VAE.forward (training) is outside the sampling path")

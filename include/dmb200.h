@@ -99,6 +99,29 @@ int dmb_sample_loop_strided(dmb_ctx* ctx, float* x, const int64_t* y, int null_l
  * img_u8 (B,3,224,224) [dev] or NULL. */
 int dmb_vae_decode(dmb_ctx* ctx, const float* z, int B, float* img_f32, uint8_t* img_u8, void* stream);
 
+/* VAE encoder weights: the state_dict entries of VAE.enc, VAE.to_mu and
+ * VAE.to_logvar under their own names ("enc.0.weight" ... "enc.16.bias", "to_mu.weight",
+ * "to_mu.bias", "to_logvar.weight", "to_logvar.bias"), fp32, host or device  (models/vae.py:16-31). */
+int dmb_load_vae_enc_weights(dmb_ctx* ctx, int n, const char* const* names, const void* const* ptrs /*[any]*/,
+                             const int64_t* numels);
+
+/* VAE.encode (models/vae.py:51-62).  img (B,3,224,224) fp32 [dev]; eps (B,4,28,28) [dev] is the
+ * standard-normal draw the reference takes from torch.randn_like(std) (:56) -- the caller owns
+ * the generator; z (B,4,28,28) [dev] = (mu + eps * exp(0.5 * logvar)) * 0.18215; mu / logvar
+ * (B,4,28,28) [dev] or NULL (logvar after the clamp to [-30, 20], :54); kl_sample (B) [dev] =
+ * 0.5 * sum(exp(logvar) + mu^2 - 1 - logvar) / (224 * 224) per sample (:61) -- the reference
+ * returns its mean over the batch. */
+int dmb_vae_encode(dmb_ctx* ctx, const float* img, const float* eps, int B, float* z, float* mu, float* logvar,
+                   float* kl_sample, void* stream);
+
+/* Diffuser.add_noise (diff.py:18-30): x_t = sqrt(ab) * x_0 + sqrt(1 - ab) * noise, ab =
+ * alpha_bars[t[b] - 1].  x0 / noise / x_t (B, per_sample) fp32 [dev]; t (B) int64 [dev], 1..T
+ * (the caller checks the range, as the reference asserts it on the host); alpha_bars (T) fp32
+ * [dev].  Each operation is rounded separately, as in the reference's three torch kernels, so
+ * the result is bit-identical for the same noise. */
+int dmb_add_noise(dmb_ctx* ctx, const float* x0, const int64_t* t, const float* alpha_bars, int T,
+                  const float* noise, int B, int64_t per_sample, float* x_t, void* stream);
+
 /* Scoring of generated images against ground-truth masks on the device:
  * eval_iou_noise.py:77-94 load_binary_mask (PIL "L" conversion + threshold), :162-171 exact
  * Euclidean distance transform, :185-232 gaussian_weighted_recall / far_noise_ratio, :239-272

@@ -260,6 +260,30 @@ def vae_decode(vsd: SD, z: torch.Tensor) -> torch.Tensor:
     return torch.sigmoid(h)
 
 
+def vae_encode(vsd: SD, x: torch.Tensor, eps: torch.Tensor):
+    """VAE.encode with the normal draw passed in: (z, kl_mean, mu, logvar_clamped).
+    models/vae.py:16-31 (enc), 51-62 (heads, clamp, reparameterisation, KL)."""
+    gn = lambda h, i: F.gelu(F.group_norm(h, 8, vsd[f"enc.{i}.weight"], vsd[f"enc.{i}.bias"], 1e-5))
+    h = gn(F.conv2d(x, vsd["enc.0.weight"], vsd["enc.0.bias"], stride=1, padding=1), 1)
+    h = gn(F.conv2d(h, vsd["enc.3.weight"], vsd["enc.3.bias"], stride=2, padding=1), 4)
+    h = gn(F.conv2d(h, vsd["enc.6.weight"], vsd["enc.6.bias"], stride=1, padding=1), 7)
+    h = gn(F.conv2d(h, vsd["enc.9.weight"], vsd["enc.9.bias"], stride=2, padding=1), 10)
+    h = gn(F.conv2d(h, vsd["enc.12.weight"], vsd["enc.12.bias"], stride=1, padding=1), 13)
+    h = gn(F.conv2d(h, vsd["enc.15.weight"], vsd["enc.15.bias"], stride=2, padding=1), 16)
+    mu = F.conv2d(h, vsd["to_mu.weight"], vsd["to_mu.bias"])
+    logvar = F.conv2d(h, vsd["to_logvar.weight"], vsd["to_logvar.bias"]).clamp(-30.0, 20.0)
+    std = torch.exp(0.5 * logvar)
+    z = (mu + eps * std) * VAE_SCALE
+    kl = 0.5 * torch.sum(torch.exp(logvar) + mu ** 2 - 1.0 - logvar, dim=(1, 2, 3)) / (x.size(2) * x.size(3))
+    return z, kl.mean(), mu, logvar
+
+
+def add_noise(x_0: torch.Tensor, t: torch.Tensor, noise: torch.Tensor, alpha_bars: torch.Tensor) -> torch.Tensor:
+    """Diffuser.add_noise with the normal draw passed in.  diff.py:18-30."""
+    ab = alpha_bars[t - 1].view(-1, 1, 1, 1)
+    return torch.sqrt(ab) * x_0 + torch.sqrt(1 - ab) * noise
+
+
 def to_u8(img: torch.Tensor) -> torch.Tensor:
     """x*255 -> clamp(0,255) -> uint8 (truncation).  diff.py:58-61."""
     return (img * 255).clamp(0, 255).to(torch.uint8)

@@ -140,3 +140,28 @@ def test_scoring_oracle_matches_scipy():
     rgb = rng.integers(0, 256, (3, 31, 29), dtype=np.uint8)
     pil = np.array(Image.fromarray(np.moveaxis(rgb, 0, -1), mode="RGB").convert("L"))
     assert np.array_equal(R.u8_to_gray(rgb), pil)
+
+
+# ---- VAE.encode and Diffuser.add_noise (tests/golden/make_golden_encode.py)
+@pytest.fixture(scope="module")
+def enc_golden():
+    import os
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_encode.npz"))
+
+
+def test_vae_encode_oracle_matches_reference(enc_golden, seeded_models):
+    _, vae = seeded_models
+    vsd = vae.state_dict()
+    np.testing.assert_allclose([float(v.double().sum()) for v in vsd.values()], enc_golden["vae_sums"], rtol=0, atol=0)
+    with torch.no_grad():
+        z, kl, mu, logvar = R.vae_encode(vsd, _t(enc_golden["G_x"]).float(), _t(enc_golden["G_eps"]))
+    # same torch build, same expressions: the restatement reproduces the reference bit for bit
+    assert torch.equal(z, _t(enc_golden["G_z"]))
+    assert torch.equal(mu, _t(enc_golden["G_mu"])) and torch.equal(logvar, _t(enc_golden["G_logvar"]))
+    assert float(kl) == float(enc_golden["G_kl"])
+
+
+def test_add_noise_oracle_matches_reference(enc_golden):
+    _, _, alpha_bars = R.schedule(1000)
+    x_t = R.add_noise(_t(enc_golden["H_x0"]), _t(enc_golden["H_t"]), _t(enc_golden["H_noise"]), alpha_bars)
+    assert torch.equal(x_t, _t(enc_golden["H_xt"]))
