@@ -496,6 +496,7 @@ class Engine : public IEngine {
     float* mu = nullptr;
     float* logvar = nullptr;
     float* kl = nullptr;
+    std::map<std::string, Act<T>> taps;   // "venc.<layer>": raw conv outputs and plain GN outputs (debug)
   };
   std::unique_ptr<VaeEncPlan> vae_enc_plan_;
   void build_vae_enc_plan(VaeEncPlan& p, int B);
@@ -1575,7 +1576,8 @@ void Engine<T>::build_vae_enc_plan(VaeEncPlan& P, int n) {
                 std::to_string(in.g.H * 2),
             2.0 * in.g.n * in.g.H * in.g.W * 4.0 * w.K * w.N);
     ops.push_back([this, in, w, out](cudaStream_t s) {
-      const int shifts[4] = {0, 1, in.g.Wp, in.g.Wp + 1};
+      // output pixel (oy, ox) sits at PM row (oy + 1) * Wp + ox (leading pad row); block (py, px) at py * Wp + px
+      const int shifts[4] = {-in.g.Wp, -in.g.Wp + 1, 0, 1};
       GemmParams ep{};
       ep.epi = EPI_STORE;
       ep.out = out.p; ep.ldc = out.C; ep.bias = w.bias;
@@ -1596,12 +1598,14 @@ void Engine<T>::build_vae_enc_plan(VaeEncPlan& P, int n) {
       count();
     });
   }
+  auto tap = [&](const char* name, const Act<T>& v) { P.taps[name] = v; return v; };
+  tap("venc.0", r0);
   Act<T> a = gn8(r0, "venc.enc.1", true);
-  a = gn8(conv4s2(a, "venc.enc.3"), "venc.enc.4", false);
-  a = gn8(conv(a, "venc.enc.6"), "venc.enc.7", true);
-  a = gn8(conv4s2(a, "venc.enc.9"), "venc.enc.10", false);
-  a = gn8(conv(a, "venc.enc.12"), "venc.enc.13", true);
-  a = gn8(conv4s2(a, "venc.enc.15"), "venc.enc.16", false);
+  a = tap("venc.5", gn8(tap("venc.3", conv4s2(a, "venc.enc.3")), "venc.enc.4", false));
+  a = gn8(tap("venc.6", conv(a, "venc.enc.6")), "venc.enc.7", true);
+  a = tap("venc.11", gn8(tap("venc.9", conv4s2(a, "venc.enc.9")), "venc.enc.10", false));
+  a = gn8(tap("venc.12", conv(a, "venc.enc.12")), "venc.enc.13", true);
+  a = tap("venc.17", gn8(tap("venc.15", conv4s2(a, "venc.enc.15")), "venc.enc.16", false));
   {
     const float* wm = f("venc.to_mu.weight");
     const float* bm = f("venc.to_mu.bias");
@@ -1661,9 +1665,21 @@ void Engine<T>::add_noise(const float* x0, const long long* t, const float* alph
 // ---------------------------------------------------------------------------
 template <typename T>
 void Engine<T>::get_tap(const char* name, float* out, int64_t capacity, int64_t* shape4, cudaStream_t s) {
+  const std::string nm(name);
+  if (nm.rfind("venc.", 0) == 0) {   // VAE encoder: output of enc.<i> of the last chunk (index of nn.Sequential)
+    if (!vae_enc_plan_) fail(5, "no VAE encode has been run yet");
+    auto it = vae_enc_plan_->taps.find(nm);
+    if (it == vae_enc_plan_->taps.end()) fail(2, "unknown tap '" + nm + "'");
+    const Act<T>& a = it->second;
+    shape4[0] = a.g.n; shape4[1] = a.C; shape4[2] = a.g.H; shape4[3] = a.g.W;
+    const long long total = static_cast<long long>(a.g.n) * a.C * a.g.H * a.g.W;
+    DMB_REQUIRE(capacity >= total, "tap buffer too small");
+    pm_to_nchw_kernel<T><<<cdiv(total, 256), 256, 0, s>>>(a.p, a.g, a.C, a.C, 0, out);
+    DMB_CHECK_LAUNCH();
+    return;
+  }
   if (!last_plan_) fail(5, "no forward has been run yet");
   Plan<T>& p = *last_plan_;
-  const std::string nm(name);
   const int n = p.doubled ? 2 * p.B : p.B;
   if (nm == "emb" || nm == "embproj") {
     const int cols = nm == "emb" ? kEmbDim : kProjCols;

@@ -1062,12 +1062,13 @@ __global__ void pm_to_nchw_kernel(const T* __restrict__ in, Geo g, int C, int ld
 //
 // GroupNorm(8)+GELU whose consumer is a 4x4 / stride-2 / pad-1 convolution: the result is written
 // "space-to-depth with a one-pixel offset".  Position (py, px) of the half-resolution pixel
-// matrix -- ALL (H/2+1) x (W/2+1) positions of a sample, the pad column and pad row included --
-// holds the 2x2 block of source pixels (2py-1+sy, 2px-1+sx), sy, sx in {0,1}, as 4C channels
-// ((sy*2+sx)*C + c), zeros outside the image.  Output pixel (oy, ox) of the strided conv then
-// reads source rows 2oy-1 .. 2oy+2 = positions oy and oy+1: a 2x2-tap, stride-1 convolution with
-// K = 4C per tap and shifts {0, 1, Wp, Wp+1}, which is what the tcgen05 GEMM already runs -- no
-// strided gathers, no zero-padded K.
+// matrix -- ALL (H/2+1) x (W/2+1) positions of a sample, the pad column and pad row included,
+// PM row py * Wp + px of the sample -- holds the 2x2 block of source pixels (2py-1+sy, 2px-1+sx),
+// sy, sx in {0,1}, as 4C channels ((sy*2+sx)*C + c), zeros outside the image.  Output pixel
+// (oy, ox) of the strided conv then reads source rows 2oy-1 .. 2oy+2 = blocks oy and oy+1: a
+// 2x2-tap, stride-1 convolution with K = 4C per tap.  The output pixel's own PM row is
+// (oy+1) * Wp + ox (the pad row leads), so the tap shifts are {-Wp, -Wp+1, 0, 1} -- which is what
+// the tcgen05 GEMM already runs: no strided gathers, no zero-padded K.
 // ---------------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256)

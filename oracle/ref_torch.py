@@ -260,16 +260,22 @@ def vae_decode(vsd: SD, z: torch.Tensor) -> torch.Tensor:
     return torch.sigmoid(h)
 
 
-def vae_encode(vsd: SD, x: torch.Tensor, eps: torch.Tensor):
+def vae_encode(vsd: SD, x: torch.Tensor, eps: torch.Tensor, taps: Optional[Dict[str, torch.Tensor]] = None):
     """VAE.encode with the normal draw passed in: (z, kl_mean, mu, logvar_clamped).
-    models/vae.py:16-31 (enc), 51-62 (heads, clamp, reparameterisation, KL)."""
-    gn = lambda h, i: F.gelu(F.group_norm(h, 8, vsd[f"enc.{i}.weight"], vsd[f"enc.{i}.bias"], 1e-5))
-    h = gn(F.conv2d(x, vsd["enc.0.weight"], vsd["enc.0.bias"], stride=1, padding=1), 1)
-    h = gn(F.conv2d(h, vsd["enc.3.weight"], vsd["enc.3.bias"], stride=2, padding=1), 4)
-    h = gn(F.conv2d(h, vsd["enc.6.weight"], vsd["enc.6.bias"], stride=1, padding=1), 7)
-    h = gn(F.conv2d(h, vsd["enc.9.weight"], vsd["enc.9.bias"], stride=2, padding=1), 10)
-    h = gn(F.conv2d(h, vsd["enc.12.weight"], vsd["enc.12.bias"], stride=1, padding=1), 13)
-    h = gn(F.conv2d(h, vsd["enc.15.weight"], vsd["enc.15.bias"], stride=2, padding=1), 16)
+    models/vae.py:16-31 (enc), 51-62 (heads, clamp, reparameterisation, KL).  taps (optional)
+    receives the outputs of enc[i] under "venc.<i>" (i = index in the nn.Sequential)."""
+    def rec(i, v):
+        if taps is not None:
+            taps[f"venc.{i}"] = v
+        return v
+    gn = lambda h, i: rec(i + 1, F.gelu(F.group_norm(h, 8, vsd[f"enc.{i}.weight"], vsd[f"enc.{i}.bias"], 1e-5)))
+    conv = lambda h, i, stride: rec(i, F.conv2d(h, vsd[f"enc.{i}.weight"], vsd[f"enc.{i}.bias"], stride=stride, padding=1))
+    h = gn(conv(x, 0, 1), 1)
+    h = gn(conv(h, 3, 2), 4)
+    h = gn(conv(h, 6, 1), 7)
+    h = gn(conv(h, 9, 2), 10)
+    h = gn(conv(h, 12, 1), 13)
+    h = gn(conv(h, 15, 2), 16)
     mu = F.conv2d(h, vsd["to_mu.weight"], vsd["to_mu.bias"])
     logvar = F.conv2d(h, vsd["to_logvar.weight"], vsd["to_logvar.bias"]).clamp(-30.0, 20.0)
     std = torch.exp(0.5 * logvar)

@@ -59,6 +59,26 @@ def test_encode_golden(enc_golden, vae_pair):
     assert torch.equal(z2, z) and abs(float(klm) - float(kl.mean())) < 1e-7
 
 
+def test_encode_layers_match_oracle(enc_golden, vae_pair):
+    """Every convolution output and plain GroupNorm output of the encoder against the oracle."""
+    from dmb200 import context_for
+    vae, vsd = vae_pair
+    x = _t(enc_golden["G_x"]).float()
+    eps = _t(enc_golden["G_eps"])
+    taps = {}
+    with torch.no_grad():
+        R.vae_encode(vsd, x, eps, taps=taps)
+    vae.encode(x.to(DEV), eps.to(DEV))
+    ctx = context_for(DEV)
+    rows = {}
+    for name in ("venc.0", "venc.3", "venc.5", "venc.6", "venc.9", "venc.11", "venc.12", "venc.15", "venc.17"):
+        got = ctx.get_tap(name)
+        assert tuple(got.shape) == tuple(taps[name].shape), name
+        rows[name] = rel_l2(got, taps[name])
+    report("vae_encode_layers", rows)
+    assert max(rows.values()) <= 3e-2, rows
+
+
 @pytest.mark.parametrize("batch", [1, 5, 33])
 def test_encode_matches_oracle(vae_pair, batch):
     """Seeded images against the oracle, incl. a batch that spans two chunks of 32."""
@@ -117,7 +137,7 @@ def test_encode_rejects_bad_input(vae_pair):
 def test_add_noise_golden_bit_exact(enc_golden):
     from diff import Diffuser
     g = enc_golden
-    d = Diffuser(num_timesteps=1000, device=DEV)
+    d = Diffuser(num_timesteps=1000, device="cpu")     # the golden run's schedule (CPU cumprod)
     x_t, noise = d.add_noise(_t(g["H_x0"]).to(DEV), _t(g["H_t"]).to(DEV), noise=_t(g["H_noise"]).to(DEV))
     assert torch.equal(x_t.cpu(), _t(g["H_xt"]))
     assert torch.equal(noise.cpu(), _t(g["H_noise"]))
