@@ -619,9 +619,13 @@ void Engine<T>::load_unet(const TensorMapIn& w) {
   DMB_CUDA(cudaDeviceSynchronize());
   plans_.clear();
   last_plan_ = nullptr;
-  gw_.clear();
+  // drop the U-Net's entries only: the VAE decoder ("vae.") and encoder ("venc.") keep theirs
+  auto is_vae = [](const std::string& k) { return k.rfind("vae.", 0) == 0 || k.rfind("venc.", 0) == 0; };
+  for (auto it = gw_.begin(); it != gw_.end();) {
+    if (is_vae(it->first)) ++it; else it = gw_.erase(it);
+  }
   for (auto it = blob_.begin(); it != blob_.end();) {
-    if (it->first.rfind("vae.", 0) == 0) ++it; else it = blob_.erase(it);
+    if (is_vae(it->first)) ++it; else it = blob_.erase(it);
   }
   wpool_unet_.release();
   unet_loaded_ = false;
@@ -1540,7 +1544,7 @@ void Engine<T>::build_vae_enc_plan(VaeEncPlan& P, int n) {
     Act<T> out = s2d ? new_act(pool, raw.g.n, raw.g.H / 2, raw.g.W / 2, 4 * raw.C, false)
                      : new_act(pool, raw.g.n, raw.g.H, raw.g.W, raw.C, false);
     const int total_vec = raw.g.H * raw.g.W * raw.C / 8;
-    const int chunks = std::max(1, std::min(32, total_vec / 4096));
+    const int chunks = std::max(1, std::min(96, total_vec / 4096));
     double2* partial = pool.alloc_n<double2>(static_cast<size_t>(raw.g.n) * chunks * 8);
     const float* gamma = f(name + ".weight");
     const float* beta = f(name + ".bias");
@@ -1592,8 +1596,7 @@ void Engine<T>::build_vae_enc_plan(VaeEncPlan& P, int n) {
     const float* b0 = f("venc.enc.0.bias");
     ops.tag("vae-enc conv_in 3->64 @224", 2.0 * n * 224.0 * 224 * 27 * 64);
     ops.push_back([this, r0, w0, b0, pp, n](cudaStream_t s) {
-      conv_in_kernel<T, 3><<<dim3(cdiv(224 * 224, 128), n, 1), 128, 0, s>>>(pp->img, n, w0, b0, 1.0f, r0.g, 64, r0.p,
-                                                                           nullptr);
+      enc_conv_in_kernel<T><<<dim3(cdiv(224 * 112, 128), n), 128, 0, s>>>(pp->img, w0, b0, r0.g, r0.p);
       DMB_CHECK_LAUNCH();
       count();
     });
@@ -1613,7 +1616,7 @@ void Engine<T>::build_vae_enc_plan(VaeEncPlan& P, int n) {
     const float* bl = f("venc.to_logvar.bias");
     ops.tag("vae-enc to_mu/to_logvar + reparameterise + KL", 2.0 * n * kLatH * kLatW * 256 * 8);
     ops.push_back([this, a, wm, bm, wl, bl, pp, n](cudaStream_t s) {
-      vae_enc_head_kernel<T><<<n, 256, 0, s>>>(a.p, a.g, a.C, wm, bm, wl, bl, pp->eps, 0.18215f, 224.0f * 224.0f,
+      vae_enc_head_kernel<T><<<n, 512, 0, s>>>(a.p, a.g, a.C, wm, bm, wl, bl, pp->eps, 0.18215f, 224.0f * 224.0f,
                                                pp->z, pp->mu, pp->logvar, pp->kl);
       DMB_CHECK_LAUNCH();
       count();

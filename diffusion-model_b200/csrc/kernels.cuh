@@ -127,31 +127,29 @@ emb_kernel(EmbWeights w, const long long* __restrict__ t_vec, const long long* _
 // ---------------------------------------------------------------------------
 // Direct 3x3 / pad 1 convolution from an fp32 NCHW latent (4 channels) into a PM
 // activation.  Used for inc.double_conv.0 (4->64, no bias, GroupNorm row statistics)
-// and the VAE decoder's dec.0 (4->256, bias, input divided by the VAE scale factor); with
-// kCin = 3 it is the VAE encoder's enc.0 on the fp32 image (3->64, bias).
+// and the VAE decoder's dec.0 (4->256, bias, input divided by the VAE scale factor).
 // Thread = one pixel x 64 output channels; blockIdx.z selects the 64-channel group.
 // ---------------------------------------------------------------------------
-template <typename T, int kCin = kLatC>
+template <typename T>
 __global__ void __launch_bounds__(128)
 conv_in_kernel(const float* __restrict__ x, int B_src, const float* __restrict__ w_oihw,
                const float* __restrict__ bias, float in_div, Geo g, int cout,
                T* __restrict__ out, float2* __restrict__ rowstats) {
-  constexpr int kK = 9 * kCin;
-  __shared__ float ws[kK * 64];
+  __shared__ float ws[36 * 64];
   const int co0 = blockIdx.z * 64;
-  for (int i = threadIdx.x; i < kK * 64; i += blockDim.x) {
+  for (int i = threadIdx.x; i < 36 * 64; i += blockDim.x) {
     const int k = i / 64, co = i % 64;  // k = ci*9 + ky*3 + kx
-    ws[i] = w_oihw[(co0 + co) * kK + k];
+    ws[i] = w_oihw[(co0 + co) * 36 + k];
   }
   __syncthreads();
   const int be = blockIdx.y;
   const int pix = blockIdx.x * blockDim.x + threadIdx.x;
   if (pix >= g.H * g.W) return;
   const int y = pix / g.W, xx = pix % g.W;
-  const float* xs = x + static_cast<size_t>(be % B_src) * kCin * g.H * g.W;
-  float in[kK];
+  const float* xs = x + static_cast<size_t>(be % B_src) * kLatC * g.H * g.W;
+  float in[36];
 #pragma unroll
-  for (int ci = 0; ci < kCin; ++ci)
+  for (int ci = 0; ci < kLatC; ++ci)
 #pragma unroll
     for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
@@ -165,7 +163,7 @@ conv_in_kernel(const float* __restrict__ x, int B_src, const float* __restrict__
 #pragma unroll
   for (int co = 0; co < 64; ++co) acc[co] = bias ? bias[co0 + co] : 0.f;
 #pragma unroll
-  for (int k = 0; k < kK; ++k) {
+  for (int k = 0; k < 36; ++k) {
     const float v = in[k];
 #pragma unroll
     for (int co = 0; co < 64; ++co) acc[co] = fmaf(v, ws[k * 64 + co], acc[co]);
@@ -966,24 +964,67 @@ gn8_stats_kernel(const T* __restrict__ raw, Geo g, int C, double2* __restrict__ 
   const int begin = blockIdx.x * per;
   const int end = min(total, begin + per);
   float s = 0.f, ss = 0.f;
-  for (int v = begin + tid; v < end; v += 256) {
-    const int pix = v / vpr, c0 = (v % vpr) * 8;
-    float xv[8];
-    load8(raw + static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * C + c0, xv);
+  constexpr int U = 4;   // loads in flight per thread
+  for (int v0 = begin + tid; v0 < end; v0 += 256 * U) {
+    float xv[U][8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { s += xv[i]; ss += xv[i] * xv[i]; }
+    for (int u = 0; u < U; ++u) {
+      const int v = v0 + u * 256;
+      if (v < end) {
+        const int pix = v / vpr, c0 = (v % vpr) * 8;
+        load8(raw + static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * C + c0, xv[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (v0 + u * 256 < end) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s += xv[u][i]; ss += xv[u][i] * xv[u][i]; }
+      }
+    }
   }
   red[0][tid] = s; red[1][tid] = ss;
   __syncthreads();
-  if (tid < 8) {
-    // thread j's vector column is j % vpr (begin is a multiple of vpr); group = column / (vpr/8)
+  {
+    // thread j's vector column is j % vpr (begin is a multiple of vpr); group = column / (vpr/8).
+    // Warp w gathers group w: fixed lane order, then a fixed shuffle tree.
+    const int w = tid >> 5, lane = tid & 31, vpg = vpr / 8;
     double a = 0.0, q = 0.0;
-    const int vpg = vpr / 8;
-    for (int j = 0; j < 256; ++j) {
-      if (((j % vpr) / vpg) == tid) { a += red[0][j]; q += red[1][j]; }
+    for (int j = lane; j < 256; j += 32) {
+      if (((j % vpr) / vpg) == w) { a += red[0][j]; q += red[1][j]; }
     }
-    partial[(static_cast<size_t>(b) * gridDim.x + blockIdx.x) * 8 + tid] = make_double2(a, q);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if (lane == 0) partial[(static_cast<size_t>(b) * gridDim.x + blockIdx.x) * 8 + w] = make_double2(a, q);
   }
+}
+
+// Per-group mean / rstd of a sample from the chunk partials of gn8_stats_kernel: warp w (of 8)
+// takes group w, its lanes take the chunks (independent loads), then a fixed shuffle tree.
+__device__ __forceinline__ void gn8_finish_stats(const double2* __restrict__ partial, int b, int n_chunks, double cnt,
+                                                 float* s_mean, float* s_rstd) {
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double a = 0.0, q = 0.0;
+  for (int k = lane; k < n_chunks; k += 32) {
+    const double2 v = partial[(static_cast<size_t>(b) * n_chunks + k) * 8 + w];
+    a += v.x; q += v.y;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) {
+    const double mean = a / cnt;
+    double var = q / cnt - mean * mean;
+    if (var < 0.0) var = 0.0;
+    s_mean[w] = static_cast<float>(mean);
+    s_rstd[w] = static_cast<float>(1.0 / sqrt(var + 1e-5));
+  }
+  __syncthreads();
 }
 
 template <typename T>
@@ -994,20 +1035,7 @@ gn8_apply_gelu_kernel(const T* __restrict__ raw, const double2* __restrict__ par
   __shared__ float s_mean[8], s_rstd[8];
   const int b = blockIdx.y, tid = threadIdx.x;
   const int HW = g.H * g.W;
-  if (tid < 8) {
-    double a = 0.0, q = 0.0;
-    for (int k = 0; k < n_chunks_stats; ++k) {
-      const double2 v = partial[(static_cast<size_t>(b) * n_chunks_stats + k) * 8 + tid];
-      a += v.x; q += v.y;
-    }
-    const double cnt = static_cast<double>(HW) * (C / 8);
-    const double mean = a / cnt;
-    double var = q / cnt - mean * mean;
-    if (var < 0.0) var = 0.0;
-    s_mean[tid] = static_cast<float>(mean);
-    s_rstd[tid] = static_cast<float>(1.0 / sqrt(var + 1e-5));
-  }
-  __syncthreads();
+  gn8_finish_stats(partial, b, n_chunks_stats, static_cast<double>(HW) * (C / 8), s_mean, s_rstd);
   const int vpr = C / 8, vpg = vpr / 8;
   const int total = HW * vpr;
   const int per = (total + gridDim.x - 1) / gridDim.x;
@@ -1070,6 +1098,69 @@ __global__ void pm_to_nchw_kernel(const T* __restrict__ in, Geo g, int C, int ld
 // (oy+1) * Wp + ox (the pad row leads), so the tap shifts are {-Wp, -Wp+1, 0, 1} -- which is what
 // the tcgen05 GEMM already runs: no strided gathers, no zero-padded K.
 // ---------------------------------------------------------------------------
+// enc.0: 3x3 / pad 1 convolution 3 -> 64 with bias, straight from the fp32 NCHW image into a PM
+// activation.  K = 27 is far too short for a tcgen05 pipeline; on the CUDA cores the kernel is
+// bound by FFMA issue and by the shared-memory reads of the weights, so one thread computes TWO
+// horizontally adjacent pixels x 64 channels with packed FFMA2 (fma.rn.f32x2): every weight pair
+// read from shared memory feeds two instructions, each of which does two multiply-adds.
+template <typename T>
+__global__ void __launch_bounds__(128)
+enc_conv_in_kernel(const float* __restrict__ x, const float* __restrict__ w_oihw, const float* __restrict__ bias,
+                   Geo g, T* __restrict__ out) {
+  __shared__ __align__(16) float ws[27 * 64];
+  for (int i = threadIdx.x; i < 27 * 64; i += blockDim.x) {
+    const int k = i / 64, co = i % 64;  // k = ci*9 + ky*3 + kx
+    ws[i] = w_oihw[co * 27 + k];
+  }
+  __syncthreads();
+  const int be = blockIdx.y;
+  const int half_w = g.W / 2;
+  const int pp = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pp >= g.H * half_w) return;
+  const int y = pp / half_w, x0 = 2 * (pp - y * half_w);
+  const float* xs = x + static_cast<size_t>(be) * 3 * g.H * g.W;
+  float in[3][3][4];   // channel, kernel row, column x0-1 .. x0+2
+#pragma unroll
+  for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int iy = y + ky - 1, ix = x0 + j - 1;
+        in[ci][ky][j] = (iy >= 0 && iy < g.H && ix >= 0 && ix < g.W) ? xs[(ci * g.H + iy) * g.W + ix] : 0.f;
+      }
+  float2 acc0[32], acc1[32];
+#pragma unroll
+  for (int c = 0; c < 32; ++c) acc0[c] = acc1[c] = make_float2(bias[2 * c], bias[2 * c + 1]);
+  const float2* ws2 = reinterpret_cast<const float2*>(ws);
+#pragma unroll
+  for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const int k = ci * 9 + ky * 3 + kx;
+        const float2 v0 = make_float2(in[ci][ky][kx], in[ci][ky][kx]);
+        const float2 v1 = make_float2(in[ci][ky][kx + 1], in[ci][ky][kx + 1]);
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          const float2 w2 = ws2[k * 32 + c];
+          acc0[c] = __ffma2_rn(v0, w2, acc0[c]);
+          acc1[c] = __ffma2_rn(v1, w2, acc1[c]);
+        }
+      }
+  T* op = out + static_cast<size_t>(geo_row(g, be, y, x0)) * 64;   // the two pixels are adjacent PM rows
+#pragma unroll
+  for (int c = 0; c < 32; c += 4) {
+    const float a[8] = {acc0[c].x, acc0[c].y, acc0[c + 1].x, acc0[c + 1].y,
+                        acc0[c + 2].x, acc0[c + 2].y, acc0[c + 3].x, acc0[c + 3].y};
+    const float b[8] = {acc1[c].x, acc1[c].y, acc1[c + 1].x, acc1[c + 1].y,
+                        acc1[c + 2].x, acc1[c + 2].y, acc1[c + 3].x, acc1[c + 3].y};
+    store8(op + 2 * c, a);
+    store8(op + 64 + 2 * c, b);
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 gn8_apply_gelu_s2d_kernel(const T* __restrict__ raw, const double2* __restrict__ partial, int n_chunks_stats,
@@ -1077,41 +1168,42 @@ gn8_apply_gelu_s2d_kernel(const T* __restrict__ raw, const double2* __restrict__
                           Geo g2, T* __restrict__ out) {
   __shared__ float s_mean[8], s_rstd[8];
   const int b = blockIdx.y, tid = threadIdx.x;
-  if (tid < 8) {
-    double a = 0.0, q = 0.0;
-    for (int k = 0; k < n_chunks_stats; ++k) {
-      const double2 v = partial[(static_cast<size_t>(b) * n_chunks_stats + k) * 8 + tid];
-      a += v.x; q += v.y;
-    }
-    const double cnt = static_cast<double>(g.H) * g.W * (C / 8);
-    const double mean = a / cnt;
-    double var = q / cnt - mean * mean;
-    if (var < 0.0) var = 0.0;
-    s_mean[tid] = static_cast<float>(mean);
-    s_rstd[tid] = static_cast<float>(1.0 / sqrt(var + 1e-5));
-  }
-  __syncthreads();
+  gn8_finish_stats(partial, b, n_chunks_stats, static_cast<double>(g.H) * g.W * (C / 8), s_mean, s_rstd);
   const int vpr = C / 8, vpg = vpr / 8;
   const int total = g2.S * 4 * vpr;          // every position of the sample, 4 source pixels each
   const int per = (total + gridDim.x - 1) / gridDim.x;
   const int begin = blockIdx.x * per;
   const int end = min(total, begin + per);
-  for (int v = begin + tid; v < end; v += 256) {
-    const int vc = v % vpr, q = (v / vpr) & 3, pos = v / (4 * vpr);
-    const int py = pos / g2.Wp, px = pos - py * g2.Wp;
-    const int y = 2 * py - 1 + (q >> 1), x = 2 * px - 1 + (q & 1);
-    float xv[8];
-    if (y >= 0 && y < g.H && x >= 0 && x < g.W) {
-      const int c0 = vc * 8;
-      const float mean = s_mean[vc / vpg], rstd = s_rstd[vc / vpg];
-      load8(raw + static_cast<size_t>(geo_row(g, b, y, x)) * C + c0, xv);
+  // 256 is a multiple of the vectors per pixel, so a thread's channel vector -- and with it its
+  // gamma / beta / group statistics -- is the same in every iteration; four loads are in flight
+  const int vc = tid % vpr, c0 = vc * 8;
+  const float mean = s_mean[vc / vpg], rstd = s_rstd[vc / vpg];
+  float ga[8], be[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>((xv[i] - mean) * rstd * gamma[c0 + i] + beta[c0 + i]);
-    } else {
+  for (int i = 0; i < 8; ++i) { ga[i] = gamma[c0 + i] * rstd; be[i] = beta[c0 + i] - mean * ga[i]; }
+  constexpr int U = 4;
+  for (int v0 = begin - begin % vpr + tid; v0 < end; v0 += 256 * U) {
+    float xv[U][8];
+    bool inside[U];
+    size_t dst[U];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) xv[i] = 0.f;
+    for (int u = 0; u < U; ++u) {
+      const int v = v0 + u * 256;
+      const int q = (v / vpr) & 3, pos = v / (4 * vpr);
+      const int py = pos / g2.Wp, px = pos - py * g2.Wp;
+      const int y = 2 * py - 1 + (q >> 1), x = 2 * px - 1 + (q & 1);
+      inside[u] = v >= begin && v < end && y >= 0 && y < g.H && x >= 0 && x < g.W;
+      dst[u] = (static_cast<size_t>(b) * g2.S + pos) * (4 * C) + q * C + c0;
+      if (inside[u]) load8(raw + static_cast<size_t>(geo_row(g, b, y, x)) * C + c0, xv[u]);
     }
-    store8(out + (static_cast<size_t>(b) * g2.S + pos) * (4 * C) + q * C + vc * 8, xv);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int v = v0 + u * 256;
+      if (v < begin || v >= end) continue;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xv[u][i] = inside[u] ? gelu_for<T>(fmaf(xv[u][i], ga[i], be[i])) : 0.f;
+      store8(out + dst[u], xv[u]);
+    }
   }
 }
 
@@ -1120,13 +1212,13 @@ gn8_apply_gelu_s2d_kernel(const T* __restrict__ raw, const double2* __restrict__
 // one warp per pixel (lanes split the channels); the KL sum is accumulated in float64 in a
 // fixed order.  kl_sample[b] = 0.5 * sum(exp(logvar) + mu^2 - 1 - logvar) / kl_div.
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(512)
 vae_enc_head_kernel(const T* __restrict__ h, Geo g, int C, const float* __restrict__ w_mu,
                     const float* __restrict__ b_mu, const float* __restrict__ w_lv,
                     const float* __restrict__ b_lv, const float* __restrict__ eps, float scale, float kl_div,
                     float* __restrict__ z, float* __restrict__ mu_out, float* __restrict__ logvar_out,
                     float* __restrict__ kl_sample) {
-  __shared__ double s_kl[8];
+  __shared__ double s_kl[16];
   const int b = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int HW = g.H * g.W;
   const int c0 = lane * 8;   // C == 256: eight channels per lane
@@ -1139,7 +1231,7 @@ vae_enc_head_kernel(const T* __restrict__ h, Geo g, int C, const float* __restri
       wl[o][i] = w_lv[o * C + c0 + i];
     }
   double kl = 0.0;
-  for (int pix = warp; pix < HW; pix += 8) {
+  for (int pix = warp; pix < HW; pix += 16) {
     float xv[8];
     load8(h + static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * C + c0, xv);
     float acc[8];
@@ -1169,14 +1261,14 @@ vae_enc_head_kernel(const T* __restrict__ h, Geo g, int C, const float* __restri
       kl += static_cast<double>(expf(lv)) + static_cast<double>(m) * m - 1.0 - lv;
     }
   }
-  // lanes 0..3 of each warp hold partial sums: fold them, then the eight warps in order
+  // lanes 0..3 of each warp hold partial sums: fold them, then the sixteen warps in order
   kl += __shfl_down_sync(0xffffffffu, kl, 2);
   kl += __shfl_down_sync(0xffffffffu, kl, 1);
   if (lane == 0) s_kl[warp] = kl;
   __syncthreads();
   if (threadIdx.x == 0) {
     double t = 0.0;
-    for (int w = 0; w < 8; ++w) t += s_kl[w];
+    for (int w = 0; w < 16; ++w) t += s_kl[w];
     kl_sample[b] = static_cast<float>(0.5 * t / kl_div);
   }
 }

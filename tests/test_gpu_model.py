@@ -325,3 +325,19 @@ def test_fused_kernels_agree_with_separate_launches(models, switch):
         assert launches[1] - launches[0] == 6, launches
         assert r < 1e-6, r
     assert r < 1e-2, (switch, r)
+
+
+def test_weight_sets_are_independent(golden, models):
+    """Loading the U-Net after the VAE (or the other way round) must not drop the other's weights:
+    decode, reload the U-Net in a fresh context, decode again."""
+    unet, vae, _, _ = models
+    ctx = _fresh_context({})
+    try:
+        z = _t(golden["D_z"]).to(DEV)
+        ctx.ensure_vae(vae)
+        before, _ = ctx.vae_decode(z)
+        ctx.ensure_unet(unet)
+        after, _ = ctx.vae_decode(z)
+        assert torch.equal(before, after)
+    finally:
+        ctx.close()
