@@ -171,3 +171,18 @@ def test_add_noise_asserts_range():
         d.add_noise(x0, torch.tensor([0, 5], device=DEV))
     with pytest.raises(AssertionError):
         d.add_noise(x0, torch.tensor([5, 1001], device=DEV))
+
+
+def test_encode_tf32_mode(enc_golden, vae_pair):
+    """The fp32-storage / TF32-operand mode on the reference-generated vectors.
+    Tolerances: mu / z rel-L2 <= 3e-3, logvar max-abs <= 3e-3."""
+    from dmb200 import context_for
+    vae, _ = vae_pair
+    g = enc_golden
+    ctx = context_for(DEV, "tf32")
+    ctx.ensure_vae_enc(vae)
+    z, kl, mu, logvar = ctx.vae_encode(_t(g["G_x"]).float().to(DEV), _t(g["G_eps"]).to(DEV), want_moments=True)
+    rows = {"mu": rel_l2(mu, _t(g["G_mu"])), "logvar_max_abs": max_abs(logvar, _t(g["G_logvar"])),
+            "z": rel_l2(z, _t(g["G_z"])), "kl_rel": abs(float(kl.mean()) - float(g["G_kl"])) / float(g["G_kl"])}
+    report("vae_encode_golden_tf32", rows)
+    assert rows["mu"] <= 3e-3 and rows["z"] <= 3e-3 and rows["logvar_max_abs"] <= 3e-3 and rows["kl_rel"] <= 3e-3, rows
