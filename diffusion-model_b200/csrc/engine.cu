@@ -294,6 +294,7 @@ class Engine : public IEngine {
       if (const char* e = getenv("DMB200_PIX_MAXHW")) pix_max_hw_ = atoi(e);
       const char* re = getenv("DMB200_ROW3");   // 0: nine separate A tiles per K chunk
       row3_ = re ? atoi(re) : 1;
+      if (const char* e = getenv("DMB200_ENC_IN_MMA")) enc_in_mma_ = atoi(e) != 0;
     }
     const char* pe = getenv("DMB200_PAIRS");
     use_pairs_ = pe ? (pe[0] - '0') : 1;
@@ -502,6 +503,7 @@ class Engine : public IEngine {
   void build_vae_enc_plan(VaeEncPlan& p, int B);
   Pool wpool_vae_enc_;
   bool vae_enc_loaded_ = false;
+  bool enc_in_mma_ = true;   // DMB200_ENC_IN_MMA=0: enc.0 on the CUDA cores (FFMA2) instead of mma.sync TF32
 
   void count(int n = 1) {
     if (counting_) launches_ += n;
@@ -1596,7 +1598,8 @@ void Engine<T>::build_vae_enc_plan(VaeEncPlan& P, int n) {
     const float* b0 = f("venc.enc.0.bias");
     ops.tag("vae-enc conv_in 3->64 @224", 2.0 * n * 224.0 * 224 * 27 * 64);
     ops.push_back([this, r0, w0, b0, pp, n](cudaStream_t s) {
-      enc_conv_in_kernel<T><<<dim3(cdiv(224 * 112, 128), n), 128, 0, s>>>(pp->img, w0, b0, r0.g, r0.p);
+      if (enc_in_mma_) enc_conv_in_mma_kernel<T><<<dim3(49, n), 256, 0, s>>>(pp->img, w0, b0, r0.g, r0.p);
+      else enc_conv_in_kernel<T><<<dim3(cdiv(224 * 112, 128), n), 128, 0, s>>>(pp->img, w0, b0, r0.g, r0.p);
       DMB_CHECK_LAUNCH();
       count();
     });

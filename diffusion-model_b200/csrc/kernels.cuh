@@ -1162,6 +1162,99 @@ enc_conv_in_kernel(const float* __restrict__ x, const float* __restrict__ w_oihw
   }
 }
 
+// enc.0 on the warp-level tensor-core path (mma.sync m16n8k8, TF32 operands, fp32 accumulate):
+// K = 3 channels x 9 taps = 27, padded to 32, is far too short for a tcgen05 pipeline, and the
+// CUDA-core version above is bound by FFMA issue.  One warp = tiles of 16 horizontally adjacent
+// pixels x 64 output channels; the B fragments (the whole 32 x 64 weight matrix) sit in shared
+// memory in fragment order, and the im2col A fragments are gathered straight
+// from the fp32 image (L1-resident: every input value is read by nine taps).  TF32 keeps 10
+// mantissa bits of the image and the weights: below the bf16 rounding of the output.
+__device__ __forceinline__ uint32_t to_tf32(float v) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return r;
+}
+template <typename T>
+__global__ void __launch_bounds__(256, 2)
+enc_conv_in_mma_kernel(const float* __restrict__ x, const float* __restrict__ w_oihw, const float* __restrict__ bias,
+                       Geo g, T* __restrict__ out) {
+  const int be = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int gq = lane >> 2, t = lane & 3;   // fragment row group / thread in group
+  // B fragments in shared memory, one 8-byte entry per (k step, n tile, lane), read back conflict-free:
+  // b0 = W[k = 8 ks + t][n = 8 nt + gq], b1 = W[k + 4][n]; W[k][n] = w[n][k], zero for k >= 27.
+  // (Held in registers they cost 64 per thread and leave one CTA per SM.)
+  __shared__ uint2 bsm[4 * 8 * 32];
+  for (int e = threadIdx.x; e < 4 * 8 * 32; e += 256) {
+    const int el = e & 31, nt = (e >> 5) & 7, ks = e >> 8;
+    const int k = ks * 8 + (el & 3), n = nt * 8 + (el >> 2);
+    bsm[e] = make_uint2(to_tf32(k < 27 ? w_oihw[n * 27 + k] : 0.f), to_tf32(k + 4 < 27 ? w_oihw[n * 27 + k + 4] : 0.f));
+  }
+  __syncthreads();
+  // this thread's eight K indices (j = 2 ks + h  ->  k = 8 ks + t + 4 h) as image offsets
+  int koff[8], kdy[8], kdx[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = (j >> 1) * 8 + t + (j & 1) * 4;
+    const int ci = k / 9, ky = (k - ci * 9) / 3, kx = k - ci * 9 - ky * 3;
+    kdy[j] = k < 27 ? ky - 1 : 1 << 20;      // (out of range for every pixel -> contributes zero)
+    kdx[j] = kx - 1;
+    koff[j] = k < 27 ? ci * g.H * g.W + (ky - 1) * g.W + (kx - 1) : 0;
+  }
+  float2 bia[8];
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) bia[nt] = make_float2(bias[nt * 8 + 2 * t], bias[nt * 8 + 2 * t + 1]);
+  const float* xs = x + static_cast<size_t>(be) * 3 * g.H * g.W;
+  const int tiles_per_row = g.W / 16;
+  const int n_tiles = g.H * tiles_per_row;
+  auto gather = [&](int tile, float (&v)[16]) {
+    const int y = tile / tiles_per_row, xa = (tile - y * tiles_per_row) * 16 + gq, xb = xa + 8;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int iy = y + kdy[j];
+      const bool row_ok = iy >= 0 && iy < g.H;
+      const int ixa = xa + kdx[j], ixb = xb + kdx[j];
+      v[2 * j] = (row_ok && ixa >= 0 && ixa < g.W) ? __ldg(xs + koff[j] + y * g.W + xa) : 0.f;
+      v[2 * j + 1] = (row_ok && ixb >= 0 && ixb < g.W) ? __ldg(xs + koff[j] + y * g.W + xb) : 0.f;
+    }
+  };
+  for (int tile = blockIdx.x * 8 + warp; tile < n_tiles; tile += gridDim.x * 8) {
+    const int y = tile / tiles_per_row, xa = (tile - y * tiles_per_row) * 16 + gq;
+    float cur[16];
+    gather(tile, cur);
+    uint32_t af[4][4];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      af[j >> 1][(j & 1) * 2] = to_tf32(cur[2 * j]);           // a0 / a2: row gq
+      af[j >> 1][(j & 1) * 2 + 1] = to_tf32(cur[2 * j + 1]);   // a1 / a3: row gq + 8
+    }
+    float acc[8][4];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) { acc[nt][0] = acc[nt][2] = bia[nt].x; acc[nt][1] = acc[nt][3] = bia[nt].y; }
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks)
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const uint2 bb = bsm[(ks * 8 + nt) * 32 + lane];
+        asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                     : "+f"(acc[nt][0]), "+f"(acc[nt][1]), "+f"(acc[nt][2]), "+f"(acc[nt][3])
+                     : "r"(af[ks][0]), "r"(af[ks][1]), "r"(af[ks][2]), "r"(af[ks][3]), "r"(bb.x), "r"(bb.y));
+      }
+    T* pa = out + static_cast<size_t>(geo_row(g, be, y, xa)) * 64 + 2 * t;
+    T* pb = pa + 8 * 64;   // pixel xb = xa + 8: eight PM rows further
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      if constexpr (sizeof(T) == 2) {
+        *reinterpret_cast<__nv_bfloat162*>(pa + nt * 8) = __floats2bfloat162_rn(acc[nt][0], acc[nt][1]);
+        *reinterpret_cast<__nv_bfloat162*>(pb + nt * 8) = __floats2bfloat162_rn(acc[nt][2], acc[nt][3]);
+      } else {
+        *reinterpret_cast<float2*>(pa + nt * 8) = make_float2(acc[nt][0], acc[nt][1]);
+        *reinterpret_cast<float2*>(pb + nt * 8) = make_float2(acc[nt][2], acc[nt][3]);
+      }
+    }
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 gn8_apply_gelu_s2d_kernel(const T* __restrict__ raw, const double2* __restrict__ partial, int n_chunks_stats,

@@ -186,3 +186,34 @@ def test_encode_tf32_mode(enc_golden, vae_pair):
             "z": rel_l2(z, _t(g["G_z"])), "kl_rel": abs(float(kl.mean()) - float(g["G_kl"])) / float(g["G_kl"])}
     report("vae_encode_golden_tf32", rows)
     assert rows["mu"] <= 3e-3 and rows["z"] <= 3e-3 and rows["logvar_max_abs"] <= 3e-3 and rows["kl_rel"] <= 3e-3, rows
+
+
+def test_input_conv_paths_agree(enc_golden, vae_pair):
+    """enc.0 on the CUDA cores (DMB200_ENC_IN_MMA=0, exact fp32 FFMA2) and on mma.sync TF32 (the
+    default): both against the oracle's enc.0 output, tolerance 3e-3 (bf16 rounding of the output)."""
+    from dmb200.native import Context
+    vae, vsd = vae_pair
+    x = _t(enc_golden["G_x"]).float()
+    eps = _t(enc_golden["G_eps"])
+    taps = {}
+    with torch.no_grad():
+        R.vae_encode(vsd, x, eps, taps=taps)
+    rows = {}
+    for flag in ("0", "1"):
+        old = os.environ.get("DMB200_ENC_IN_MMA")
+        os.environ["DMB200_ENC_IN_MMA"] = flag
+        try:
+            ctx = Context(DEV, "bf16")
+        finally:
+            if old is None:
+                os.environ.pop("DMB200_ENC_IN_MMA", None)
+            else:
+                os.environ["DMB200_ENC_IN_MMA"] = old
+        try:
+            ctx.ensure_vae_enc(vae)
+            ctx.vae_encode(x.to(DEV), eps.to(DEV))
+            rows[f"mma{flag}"] = rel_l2(ctx.get_tap("venc.0"), taps["venc.0"])
+        finally:
+            ctx.close()
+    report("vae_encode_input_conv", rows)
+    assert max(rows.values()) <= 3e-3, rows
