@@ -1618,11 +1618,15 @@ void Engine<T>::build_vae_enc_plan(VaeEncPlan& P, int n) {
     const float* wl = f("venc.to_logvar.weight");
     const float* bl = f("venc.to_logvar.bias");
     ops.tag("vae-enc to_mu/to_logvar + reparameterise + KL", 2.0 * n * kLatH * kLatW * 256 * 8);
-    ops.push_back([this, a, wm, bm, wl, bl, pp, n](cudaStream_t s) {
-      vae_enc_head_kernel<T><<<n, 512, 0, s>>>(a.p, a.g, a.C, wm, bm, wl, bl, pp->eps, 0.18215f, 224.0f * 224.0f,
-                                               pp->z, pp->mu, pp->logvar, pp->kl);
+    constexpr int kParts = 4;   // CTAs per sample
+    double* kl_part = pool.alloc_n<double>(static_cast<size_t>(n) * kParts);
+    ops.push_back([this, a, wm, bm, wl, bl, pp, n, kl_part](cudaStream_t s) {
+      vae_enc_head_kernel<T><<<dim3(n, kParts), 512, 0, s>>>(a.p, a.g, a.C, wm, bm, wl, bl, pp->eps, 0.18215f,
+                                                            pp->z, pp->mu, pp->logvar, kl_part);
       DMB_CHECK_LAUNCH();
-      count();
+      vae_enc_kl_finish_kernel<<<cdiv(n, 32), 32, 0, s>>>(kl_part, kParts, n, 224.0f * 224.0f, pp->kl);
+      DMB_CHECK_LAUNCH();
+      count(2);
     });
   }
 }
