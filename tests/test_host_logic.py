@@ -153,6 +153,23 @@ def test_no_cpu_fallback(seeded_models):
         unet.inc(x)  # parameter holders do not compute
 
 
+def test_no_cpu_fallback_for_encode_and_add_noise(seeded_models):
+    """The N3 extension follows the same rule; argument checks still come first, as in the reference."""
+    from dmb200 import NativeError
+    from diff import Diffuser
+    _, vae = seeded_models
+    with pytest.raises(NativeError):
+        vae.encode(torch.zeros(1, 3, 224, 224))
+    with pytest.raises(ValueError):
+        vae.encode(torch.zeros(1, 3, 32, 32))
+    d = Diffuser(num_timesteps=1000, device="cpu")
+    x0 = torch.zeros(2, 4, 28, 28)
+    with pytest.raises(NativeError):
+        d.add_noise(x0, torch.tensor([1, 1000]))
+    with pytest.raises(AssertionError):
+        d.add_noise(x0, torch.tensor([0, 5]))
+
+
 def test_product_does_not_import_oracle():
     import re
     root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "diffusion-model_b200")
