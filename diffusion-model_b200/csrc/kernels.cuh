@@ -1042,16 +1042,34 @@ gn8_apply_gelu_kernel(const T* __restrict__ raw, const double2* __restrict__ par
   const int per = (total + gridDim.x - 1) / gridDim.x;
   const int begin = blockIdx.x * per;
   const int end = min(total, begin + per);
-  for (int v = begin + tid; v < end; v += 256) {
-    const int pix = v / vpr, vc = v % vpr, c0 = vc * 8;
-    const int grp = vc / vpg;
-    const float mean = s_mean[grp], rstd = s_rstd[grp];
-    const size_t off = static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * C + c0;
-    float xv[8];
-    load8(raw + off, xv);
+  // 256 is a multiple of the vectors per pixel: a thread keeps its channel vector (gamma, beta,
+  // group statistics folded into one multiply-add) for every iteration; four loads in flight
+  const int vsh = 31 - __clz(vpr);   // vpr is a power of two (C = 64 .. 256)
+  const int vc = (begin + tid) & (vpr - 1), c0 = vc * 8;
+  const float mean = s_mean[vc / vpg], rstd = s_rstd[vc / vpg];
+  float ga[8], be[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>((xv[i] - mean) * rstd * gamma[c0 + i] + beta[c0 + i]);
-    store8(out + off, xv);
+  for (int i = 0; i < 8; ++i) { ga[i] = gamma[c0 + i] * rstd; be[i] = beta[c0 + i] - mean * ga[i]; }
+  constexpr int U = 4;
+  for (int v0 = begin + tid; v0 < end; v0 += 256 * U) {
+    float xv[U][8];
+    size_t off[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int v = v0 + u * 256;
+      if (v < end) {
+        off[u] = static_cast<size_t>(geo_row_of_pixel(g, b, v >> vsh)) * C + c0;
+        load8(raw + off[u], xv[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (v0 + u * 256 < end) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) xv[u][i] = gelu_for<T>(fmaf(xv[u][i], ga[i], be[i]));
+        store8(out + off[u], xv[u]);
+      }
+    }
   }
 }
 
