@@ -2,13 +2,14 @@
 reference-generated golden vectors.  All calls go through the drop-in Python modules, i.e.
 through the C ABI.
 
-Stated tolerances (bf16 mode = bf16 activations/weights, fp32 accumulate; measured values are
-written to gpurun_out/parity_report.jsonl):
-  per-layer taps            rel-L2 <= 3e-2
-  per-step eps (CFG)        rel-L2 <= 2e-2, max-abs <= 6e-2 * max|eps|
-  one-step x_{t-1}          max-abs <= 2e-2 * max|x|
-  decoded image             max-abs <= 2e-2 (range [0,1]);  u8 |diff| <= 4 levels
-  T=20 trajectory latent    rel-L2 <= 3e-2; binarised-mask IoU vs oracle >= 0.97
+Stated tolerances (bf16 mode = bf16 activations/weights, fp32 accumulate; about 1.5x the values
+measured on B200, which are written to gpurun_out/parity_report.jsonl):
+  per-layer taps            rel-L2 <= 1.8e-2
+  per-step eps (CFG)        rel-L2 <= 1.6e-2, max-abs <= 2.2e-2 * max|eps|
+  one-step x_{t-1}          max-abs <= 6e-4 * max|x|
+  decoded image             max-abs <= 6e-3 (range [0,1]);  u8 |diff| <= 3 levels
+  T=20 trajectory latent    rel-L2 <= 6e-3; binarised-mask IoU vs the reference's mask >= 0.99
+  T=1000 trajectory         see tests/test_gpu_parity_configs.py
 """
 import numpy as np
 import pytest
@@ -40,33 +41,58 @@ def _t(a):
     return torch.from_numpy(np.asarray(a))
 
 
+def _fresh_context(env):
+    """A private native context created under the given experiment switches (read once, in the
+    engine constructor)."""
+    import os
+    from dmb200.native import Context
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        return Context(torch.device("cuda", 0), "bf16")
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
 def test_forward_taps_and_outputs(golden, models):
+    """Per-layer parity.  The un-normalised stage outputs are debug taps the product never stores,
+    so this test (and only this test) runs a private context under DMB200_KEEP_TAPS=1; the eps of
+    the product context (no switch) must be bit-identical to it."""
     unet, _, sd, _ = models
     x, t, y = _t(golden["A_x"]), _t(golden["A_t"]), _t(golden["A_y"])
     vals, mask = _t(golden["A_vals"]), _t(golden["A_mask"])
     taps = {}
     with torch.no_grad():
         eps_ref, geom_ref = R.unet_forward(sd, x, t, y, vals, mask, taps=taps)
-    eps, geom = unet(x.to(DEV), t.to(DEV), y.to(DEV), cond_vals=vals.to(DEV), cond_mask=mask.to(DEV))
-    from dmb200 import context_for
-    ctx = context_for(DEV)
-    rows = {}
-    emb = ctx.get_tap("emb")[:, :, 0, 0]
-    rows["emb"] = rel_l2(emb, taps["emb"])
-    for n in TAPS:
-        got = ctx.get_tap(n)
-        assert tuple(got.shape) == tuple(taps[n].shape), n
-        rows[n] = rel_l2(got, taps[n])
+    eps_product, _ = unet(x.to(DEV), t.to(DEV), y.to(DEV), cond_vals=vals.to(DEV), cond_mask=mask.to(DEV))
+    ctx = _fresh_context({"DMB200_KEEP_TAPS": "1"})
+    try:
+        ctx.ensure_unet(unet)
+        eps, geom = ctx.unet_forward(x.to(DEV), t.to(DEV), y.to(DEV), vals.to(DEV), mask.to(DEV))
+        rows = {}
+        emb = ctx.get_tap("emb")[:, :, 0, 0]
+        rows["emb"] = rel_l2(emb, taps["emb"])
+        for n in TAPS:
+            got = ctx.get_tap(n)
+            assert tuple(got.shape) == tuple(taps[n].shape), n
+            rows[n] = rel_l2(got, taps[n])
+    finally:
+        ctx.close()
+    assert torch.equal(eps, eps_product)
     rows["eps"] = rel_l2(eps, eps_ref)
     rows["geom"] = rel_l2(geom, geom_ref)
     report("forward_taps", rows)
     print(rows)
     assert rows["emb"] < 1e-5
-    for n in TAPS:
-        assert rows[n] < 3e-2, (n, rows)
-    assert rows["eps"] < 2e-2 and rows["geom"] < 3e-2, rows
+    for n in TAPS:   # measured 4.6e-3 (inc) ... 1.15e-2 (bot3)
+        assert rows[n] < 1.8e-2, (n, rows)
+    assert rows["eps"] < 1e-2 and rows["geom"] < 6e-3, rows   # measured 5.9e-3 / 2.9e-3
     # and against the reference's own numbers
-    assert rel_l2(eps, _t(golden["A_eps"])) < 2e-2
+    assert rel_l2(eps, _t(golden["A_eps"])) < 1e-2
 
 
 def test_forward_without_numeric_condition(golden, models):
@@ -90,7 +116,7 @@ def test_teacher_forced_step_golden(golden, models, tt):
     ref = _t(golden[f"B_xout_{tt}"])
     m = max_abs(out, ref)
     report(f"step_golden_t{tt}", {"max_abs": m, "ref_max": float(ref.abs().max()), "rel_l2": rel_l2(out, ref)})
-    assert m <= 2e-2 * float(ref.abs().max())
+    assert m <= 3e-4 * float(ref.abs().max())   # measured 0.7e-4 ... 1.5e-4 of max|x|
 
 
 def test_config2_batch16_step_eps_parity(models):
@@ -118,10 +144,10 @@ def test_config2_batch16_step_eps_parity(models):
                           "x_ref_max": float(x_ref.abs().max())}
     report("config2_b16_step", rows)
     print(rows)
-    for k, r in rows.items():
-        assert r["eps_rel_l2"] < 2e-2, (k, r)
-        assert r["eps_max_abs"] < 6e-2 * r["eps_ref_max"], (k, r)
-        assert r["x_max_abs"] < 2e-2 * r["x_ref_max"], (k, r)
+    for k, r in rows.items():   # measured: 1.06e-2, 1.4e-2 * max|eps|, 3.1e-4 * max|x|
+        assert r["eps_rel_l2"] < 1.6e-2, (k, r)
+        assert r["eps_max_abs"] < 2.2e-2 * r["eps_ref_max"], (k, r)
+        assert r["x_max_abs"] < 6e-4 * r["x_ref_max"], (k, r)
 
 
 def test_config2_batch16_step_eps_parity_tf32_mode(models):
@@ -150,10 +176,10 @@ def test_config2_batch16_step_eps_parity_tf32_mode(models):
                           "eps_ref_max": float(eps_ref.abs().max()), "x_max_abs": max_abs(out, x_ref),
                           "x_ref_max": float(x_ref.abs().max())}
     report("config2_b16_step_tf32", rows)
-    for k, r in rows.items():
-        assert r["eps_rel_l2"] < 3e-3, (k, r)
-        assert r["eps_max_abs"] < 1.5e-2 * r["eps_ref_max"], (k, r)
-        assert r["x_max_abs"] < 3e-3 * r["x_ref_max"], (k, r)
+    for k, r in rows.items():   # measured: 1.09e-3, 1.3e-3 * max|eps|, 2.5e-5 * max|x|
+        assert r["eps_rel_l2"] < 1.7e-3, (k, r)
+        assert r["eps_max_abs"] < 2.5e-3 * r["eps_ref_max"], (k, r)
+        assert r["x_max_abs"] < 6e-5 * r["x_ref_max"], (k, r)
 
 
 def test_vae_decode_golden(golden, models):
@@ -166,8 +192,8 @@ def test_vae_decode_golden(golden, models):
     u8 = vae.decode_u8(z).cpu().numpy()
     du8 = np.abs(u8.astype(int) - golden["D_u8"].astype(int))
     report("vae_decode", {"max_abs": m, "u8_max_diff": int(du8.max()), "u8_frac_diff": float((du8 > 0).mean())})
-    assert m < 2e-2
-    assert du8.max() <= 4
+    assert m < 6e-3            # measured 3.6e-3
+    assert du8.max() <= 3      # measured 2 levels
     # u8 output equals truncation of the float output
     assert (u8 == (img * 255).clamp(0, 255).to(torch.uint8).cpu().numpy()).all()
 
@@ -194,8 +220,8 @@ def test_short_trajectory_through_public_api(golden, models):
         ious.append(m["iou"])
     report("trajectory_T20", {"latent_rel_l2": r, "iou": ious,
                               "u8_frac_diff": float((u8 != golden["C_img_u8"]).mean())})
-    assert r < 3e-2
-    assert min(ious) >= 0.97, ious
+    assert r < 6e-3            # measured 3.8e-3
+    assert min(ious) >= 0.99, ious   # measured 0.9943 / 0.9955 (>= 0.99 in bf16 mode)
 
 
 def test_graph_loop_equals_eager_steps(models):
@@ -271,23 +297,6 @@ def test_strided_ddim_extension_matches_oracle(models):
     r = rel_l2(got, ref[order])
     report("strided_ddim_K10", {"latent_rel_l2": r})
     assert r < 3e-2
-
-
-def _fresh_context(env):
-    """A private native context created under the given experiment switches (read once, in the
-    engine constructor)."""
-    import os
-    from dmb200.native import Context
-    old = {k: os.environ.get(k) for k in env}
-    os.environ.update(env)
-    try:
-        return Context(torch.device("cuda", 0), "bf16")
-    finally:
-        for k, v in old.items():
-            if v is None:
-                os.environ.pop(k, None)
-            else:
-                os.environ[k] = v
 
 
 @pytest.mark.parametrize("switch", ["DMB200_FUSED_TAIL", "DMB200_ROW3", "DMB200_FUSE_LN1"])

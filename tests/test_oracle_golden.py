@@ -165,3 +165,29 @@ def test_add_noise_oracle_matches_reference(enc_golden):
     _, _, alpha_bars = R.schedule(1000)
     x_t = R.add_noise(_t(enc_golden["H_x0"]), _t(enc_golden["H_t"]), _t(enc_golden["H_noise"]), alpha_bars)
     assert torch.equal(x_t, _t(enc_golden["H_xt"]))
+
+
+def test_t1000_trajectory_fixture_pins_the_oracle_step(golden, seeded_models):
+    """tests/golden/golden_t1000.npz (the unmodified reference's T = 1000 run, B = 2): the oracle's
+    step function reproduces the recorded x_999 from x_1000 and x_1 -> x_0 (t = 1: no noise, the
+    clamped alpha_bar_prev), teacher-forced from the reference's own states; the scorer reproduces
+    its metrics from its masks."""
+    import os
+    G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_t1000.npz"))
+    assert str(G["torch_version"]) == torch.__version__
+    sd = seeded_models[0].state_dict()
+    T = 1000
+    x_T, noise = synth.noise_bank(T, (2, 4, 28, 28), seed=int(G["seed"]))
+    rec = {int(t): _t(x) for t, x in zip(G["record_t"], G["record_x"])}
+    assert torch.equal(rec[1000], x_T)
+    _, alphas, abars = R.schedule(T)
+    vals, mask, y = _t(golden["A_vals"]), _t(golden["A_mask"]), torch.tensor([1, 3])
+    with torch.no_grad():
+        for t_from, ref_next in ((1000, rec[999]), (2, rec[1]), (1, _t(G["latent"]))):
+            t = torch.full((2,), t_from, dtype=torch.long)
+            nxt, _ = R.denoise_cond(sd, rec[t_from], t, y, 3.0, 0, vals, mask, noise[T - t_from], alphas, abars)
+            scale = float(ref_next.abs().max())
+            np.testing.assert_allclose(nxt.numpy(), ref_next.numpy(), rtol=0, atol=2e-5 * scale, err_msg=str(t_from))
+    m = R.compute_metrics(G["masks"][0], G["masks"][1])
+    np.testing.assert_allclose([m[k] for k in sorted(m)], G["metric_vals"], rtol=1e-12)
+    assert [str(k) for k in G["metric_keys"]] == sorted(m)
