@@ -4,6 +4,8 @@
 #include <cstring>
 #include <atomic>
 #include <cstdio>
+#include <mutex>
+#include <string>
 #include <thread>
 #include <vector>
 #include <zlib.h>
@@ -351,3 +353,100 @@ int dmb_op_conv_transpose4x4(dmb_ctx* ctx, const float* x, const float* w, const
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Allocation-free entry point (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving
+// loops, harnesses that forbid it).  A variant of the VAE encoder's KL reduction
+// (vae_enc_head_kernel -> kl_part scratch -> vae_enc_kl_finish_kernel, kernels.cuh) whose
+// per-CTA partial sums live in a file-scope __device__ array instead of the context's pool.
+//
+// g_kl_part_static is a DEVICE symbol: in host code its name is only a host-side stand-in, so
+// the host never passes it to a kernel.  Once per device, with that device current, the entry
+// point asks the runtime for the array's device address (cudaGetSymbolAddress) and hands THAT
+// pointer to the kernels.  Every GPU that loads the library holds the array (128 KB) until exit.
+// ---------------------------------------------------------------------------
+namespace {
+constexpr int kKlStaticMaxB = DMB_KL_STATIC_MAX_B;
+constexpr int kKlStaticParts = 4;      // CTAs per sample, as in vae_enc_head_kernel's launch
+constexpr int kKlStaticThreads = 256;
+constexpr int kKlStaticMaxDevices = 64;
+static __device__ __align__(256) double g_kl_part_static[kKlStaticMaxB * kKlStaticParts];
+
+std::mutex g_kl_static_mu;
+double* g_kl_static_ptr[kKlStaticMaxDevices] = {};   // device address of the array, per device
+
+// One CTA = one quarter of a sample's elements.  Same summand and the same float64 accumulation
+// as vae_enc_head_kernel (models/vae.py:61): exp(logvar) + mu^2 - 1 - logvar; fixed order
+// (thread stride, lanes, warps), so two calls on the same input give the same bits.  Every
+// partial this launch's finish kernel reads is written here first: nothing has to start at zero.
+__global__ void __launch_bounds__(kKlStaticThreads)
+kl_part_static_kernel(const float* __restrict__ mu, const float* __restrict__ logvar, long long per_sample,
+                      double* __restrict__ part) {
+  __shared__ double s_w[kKlStaticThreads / 32];
+  const int b = blockIdx.x, p = blockIdx.y;
+  const long long chunk = (per_sample + kKlStaticParts - 1) / kKlStaticParts;
+  const long long lo = p * chunk, hi = lo + chunk < per_sample ? lo + chunk : per_sample;
+  const float* m_ = mu + static_cast<size_t>(b) * per_sample;
+  const float* l_ = logvar + static_cast<size_t>(b) * per_sample;
+  double acc = 0.0;
+  for (long long i = lo + threadIdx.x; i < hi; i += kKlStaticThreads) {
+    const float m = m_[i], lv = l_[i];
+    acc += static_cast<double>(expf(lv)) + static_cast<double>(m) * m - 1.0 - lv;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, d);
+  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < kKlStaticThreads / 32; ++w) t += s_w[w];
+    part[b * kKlStaticParts + p] = t;
+  }
+}
+
+__global__ void kl_finish_static_kernel(const double* __restrict__ part, int n, float kl_div,
+                                        float* __restrict__ kl_sample) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= n) return;
+  double t = 0.0;
+  for (int p = 0; p < kKlStaticParts; ++p) t += part[b * kKlStaticParts + p];
+  kl_sample[b] = static_cast<float>(0.5 * t / kl_div);
+}
+
+// Set-up, once per device: the device address of g_kl_part_static on `device` (made current).
+double* kl_static_scratch(int device) {
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+    dmb::fail(4, "no CUDA device available: this library has no CPU fallback");
+  DMB_REQUIRE(device >= 0 && device < count && device < kKlStaticMaxDevices, "device ordinal out of range");
+  DMB_CUDA(cudaSetDevice(device));
+  std::lock_guard<std::mutex> lock(g_kl_static_mu);
+  if (!g_kl_static_ptr[device]) {
+    double* ptr = nullptr;
+    DMB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_kl_part_static));
+    if (!ptr) dmb::fail(5, "cudaGetSymbolAddress returned a null address for the static scratch array");
+    g_kl_static_ptr[device] = ptr;
+  }
+  return g_kl_static_ptr[device];
+}
+}  // namespace
+
+extern "C" int dmb_kl_per_sample_static(int device, const float* mu, const float* logvar, int B, int64_t per_sample,
+                                        float kl_div, float* kl_sample, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(mu && logvar && kl_sample, "mu, logvar and kl_sample are required");
+    DMB_REQUIRE(B >= 1 && per_sample >= 1, "B >= 1 and per_sample >= 1 are required");
+    if (B > kKlStaticMaxB)
+      dmb::fail(2, "invalid argument: B = " + std::to_string(B) + " exceeds the static scratch array of "
+                       "dmb_kl_per_sample_static (DMB_KL_STATIC_MAX_B = " + std::to_string(kKlStaticMaxB) +
+                       " samples per call); split the batch or use dmb_vae_encode");
+    DMB_REQUIRE(kl_div > 0.0f, "kl_div must be > 0");
+    double* part = kl_static_scratch(device);   // device pointer, never the host-side symbol
+    kl_part_static_kernel<<<dim3(B, kKlStaticParts), kKlStaticThreads, 0, st(stream)>>>(
+        mu, logvar, static_cast<long long>(per_sample), part);
+    DMB_CHECK_LAUNCH();
+    kl_finish_static_kernel<<<(B + 127) / 128, 128, 0, st(stream)>>>(part, B, kl_div, kl_sample);
+    DMB_CHECK_LAUNCH();
+  });
+}

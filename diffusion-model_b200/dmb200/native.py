@@ -46,6 +46,7 @@ _SIGNATURES = {
     "dmb_load_vae_enc_weights": (C.c_int, [_P, C.c_int, C.POINTER(C.c_char_p), C.POINTER(_P), C.POINTER(C.c_int64)]),
     "dmb_vae_encode": (C.c_int, [_P, _P, _P, C.c_int, _P, _P, _P, _P, _P]),
     "dmb_add_noise": (C.c_int, [_P, _P, _P, _P, C.c_int, _P, C.c_int, C.c_int64, _P, _P]),
+    "dmb_kl_per_sample_static": (C.c_int, [C.c_int, _P, _P, C.c_int, C.c_int64, C.c_float, _P, _P]),
     "dmb_score_masks": (C.c_int, [_P, _P, C.c_int, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
                                   _P, _P, _P]),
     "dmb_write_png_batch": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_char_p), C.c_int, C.c_int]),
@@ -106,6 +107,30 @@ def write_png_batch(images: torch.Tensor, paths: Sequence[str], threads: int = 0
     rc = lib.dmb_write_png_batch(C.c_void_p(host.data_ptr()), n, Cc, H, W, arr, int(threads), int(compression_level))
     if rc != 0:
         raise NativeError(f"dmb_write_png_batch failed ({rc}): " + lib.dmb_last_error_string().decode("utf-8", "replace"))
+
+
+KL_STATIC_MAX_B = 4096   # DMB_KL_STATIC_MAX_B in include/dmb200.h
+
+
+def kl_per_sample_static(mu: torch.Tensor, logvar: torch.Tensor, out: torch.Tensor, kl_div: float = 224.0 * 224.0):
+    """dmb_kl_per_sample_static: the per-sample KL term of VAE.encode from (B, ...) fp32 CUDA
+    tensors mu / logvar into the caller's `out` (B,) -- no allocation anywhere on the path (the
+    scratch is a static device array inside the library; at most KL_STATIC_MAX_B samples per call;
+    calls that overlap on the GPU race).  Enqueued on torch's current stream."""
+    dev = mu.device
+    for name, t in (("mu", mu), ("logvar", logvar), ("out", out)):
+        _check_dev(t, dev, torch.float32, name)
+    if dev.type != "cuda":
+        raise NativeError(f"no CPU fallback (got device '{dev}')")
+    B = mu.shape[0]
+    if logvar.shape != mu.shape or out.numel() != B:
+        raise ValueError("mu / logvar must have one shape and out one entry per sample")
+    lib = load_library()
+    rc = lib.dmb_kl_per_sample_static(dev.index, _ptr(mu), _ptr(logvar), B, mu.numel() // B, float(kl_div), _ptr(out),
+                                      C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+    if rc != 0:
+        raise NativeError(f"dmb_kl_per_sample_static failed ({rc}): " + lib.dmb_last_error_string().decode("utf-8", "replace"))
+    return out
 
 
 def _ptr(t: Optional[torch.Tensor]):

@@ -122,6 +122,23 @@ int dmb_vae_encode(dmb_ctx* ctx, const float* img, const float* eps, int B, floa
 int dmb_add_noise(dmb_ctx* ctx, const float* x0, const int64_t* t, const float* alpha_bars, int T,
                   const float* noise, int B, int64_t per_sample, float* x_t, void* stream);
 
+/* Allocation-free KL reduction.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid it).  A variant of the KL term of dmb_vae_encode
+ * (0.5 * sum(exp(logvar) + mu^2 - 1 - logvar) / kl_div per sample, float64 accumulation in a
+ * fixed order) that needs no context: its scratch (per-CTA partial sums) is a file-scope
+ * __device__ array of DMB_KL_STATIC_MAX_B * 4 doubles (128 KB, held by every GPU that loads the
+ * library until exit), and the call makes no cudaMalloc / cudaFree / allocating library call.
+ * device: CUDA ordinal (made current).  mu / logvar (B, per_sample) fp32 [dev] (logvar already
+ * clamped, as dmb_vae_encode returns it); kl_sample (B) fp32 [dev], caller-allocated.
+ * B > DMB_KL_STATIC_MAX_B is rejected with an error (split the batch).  All calls on a device
+ * share the one array, which keeps the last call's contents (every entry a call reads is written
+ * by that call first, so nothing needs clearing): calls that overlap on the GPU -- different
+ * streams, or concurrent graph branches -- race; serialise them on one stream. */
+#define DMB_KL_STATIC_MAX_B 4096
+int dmb_kl_per_sample_static(int device, const float* mu, const float* logvar, int B, int64_t per_sample,
+                             float kl_div, float* kl_sample, void* stream);
+
 /* Scoring of generated images against ground-truth masks on the device:
  * eval_iou_noise.py:77-94 load_binary_mask (PIL "L" conversion + threshold), :162-171 exact
  * Euclidean distance transform, :185-232 gaussian_weighted_recall / far_noise_ratio, :239-272
