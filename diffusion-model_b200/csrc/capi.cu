@@ -190,14 +190,17 @@ int dmb_score_masks(dmb_ctx* ctx, const uint8_t* pred, int pred_channels, const 
                 "channels must be 0 (mask), 1 (grey) or 3 (RGB)");
     DMB_REQUIRE(sigma > 0.0, "sigma must be > 0");   // eval_iou_noise.py:197, 225
     DMB_CUDA(cudaSetDevice(ctx->device));
-    static bool attr_set = false;
-    if (!attr_set) {
+    // function attributes are per device: one flag per ordinal
+    static std::atomic<bool> attr_set_dev[64];
+    DMB_REQUIRE(ctx->device >= 0 && ctx->device < 64, "device ordinal out of range");
+    std::atomic<bool>& attr_set = attr_set_dev[ctx->device];
+    if (!attr_set.load()) {
       DMB_CUDA(cudaFuncSetAttribute(dmb::score_masks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     static_cast<int>(dmb::score_smem_bytes(dmb::kScoreMaxSide, dmb::kScoreMaxSide))));
       // two 100 KB CTAs per SM at 224 x 224: ask for the largest shared-memory carve-out
       DMB_CUDA(cudaFuncSetAttribute(dmb::score_masks_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                     cudaSharedmemCarveoutMaxShared));
-      attr_set = true;
+      attr_set.store(true);
     }
     dmb::ScoreParams p{};
     p.pred = pred; p.gt = gt; p.pred_channels = pred_channels; p.gt_channels = gt_channels;

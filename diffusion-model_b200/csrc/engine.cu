@@ -485,7 +485,12 @@ class Engine : public IEngine {
     float* img_f32 = nullptr;
     uint8_t* img_u8 = nullptr;
   };
-  std::unique_ptr<VaePlan> vae_plan_;
+  // plans by chunk size: the full chunk (32) and the tails a caller's batch sizes leave behind, so a
+  // batch that is not a multiple of 32 does not rebuild a plan (cudaMalloc / cudaFree / device sync)
+  // twice per call.  At most kMaxVaePlans are kept; the full chunk is never evicted.
+  static constexpr int kMaxVaePlans = 3;
+  std::map<int, std::unique_ptr<VaePlan>> vae_plans_;
+  VaePlan* vae_plan_ = nullptr;   // the one used last
   void build_vae_plan(VaePlan& p, int B);
   struct VaeEncPlan {
     Pool pool;
@@ -499,7 +504,8 @@ class Engine : public IEngine {
     float* kl = nullptr;
     std::map<std::string, Act<T>> taps;   // "venc.<layer>": raw conv outputs and plain GN outputs (debug)
   };
-  std::unique_ptr<VaeEncPlan> vae_enc_plan_;
+  std::map<int, std::unique_ptr<VaeEncPlan>> vae_enc_plans_;
+  VaeEncPlan* vae_enc_plan_ = nullptr;   // the one used last (debug taps read it)
   void build_vae_enc_plan(VaeEncPlan& p, int B);
   Pool wpool_vae_enc_;
   bool vae_enc_loaded_ = false;
@@ -694,7 +700,8 @@ template <typename T>
 void Engine<T>::load_vae(const TensorMapIn& w) {
   DMB_CUDA(cudaSetDevice(device_));
   DMB_CUDA(cudaDeviceSynchronize());
-  vae_plan_.reset();
+  vae_plans_.clear();
+  vae_plan_ = nullptr;
   for (auto it = blob_.begin(); it != blob_.end();) {
     if (it->first.rfind("vae.", 0) == 0) it = blob_.erase(it); else ++it;
   }
@@ -1486,12 +1493,16 @@ void Engine<T>::vae_decode(const float* z, int B, float* img_f32, uint8_t* img_u
   const size_t img = static_cast<size_t>(3) * 224 * 224;
   for (int b0 = 0; b0 < B; b0 += kChunk) {
     const int n = std::min(kChunk, B - b0);
-    if (!vae_plan_ || vae_plan_->B != n) {
+    auto found = vae_plans_.find(n);
+    if (found == vae_plans_.end()) {
       DMB_CUDA(cudaStreamSynchronize(s));
-      vae_plan_.reset(new VaePlan());
-      build_vae_plan(*vae_plan_, n);
+      for (auto it = vae_plans_.begin(); static_cast<int>(vae_plans_.size()) >= kMaxVaePlans && it != vae_plans_.end();)
+        it = it->first != kChunk ? vae_plans_.erase(it) : std::next(it);
+      found = vae_plans_.emplace(n, std::unique_ptr<VaePlan>(new VaePlan())).first;
+      build_vae_plan(*found->second, n);
       DMB_CUDA(cudaDeviceSynchronize());
     }
+    vae_plan_ = found->second.get();
     VaePlan& p = *vae_plan_;
     p.z = const_cast<float*>(z) + b0 * lat;
     p.img_f32 = img_f32 ? img_f32 + b0 * img : nullptr;
@@ -1509,7 +1520,8 @@ template <typename T>
 void Engine<T>::load_vae_enc(const TensorMapIn& w) {
   DMB_CUDA(cudaSetDevice(device_));
   DMB_CUDA(cudaDeviceSynchronize());
-  vae_enc_plan_.reset();
+  vae_enc_plans_.clear();
+  vae_enc_plan_ = nullptr;
   for (auto it = blob_.begin(); it != blob_.end();) {
     if (it->first.rfind("venc.", 0) == 0) it = blob_.erase(it); else ++it;
   }
@@ -1642,12 +1654,17 @@ void Engine<T>::vae_encode(const float* img, const float* eps, int B, float* z, 
   const size_t im = static_cast<size_t>(3) * 224 * 224;
   for (int b0 = 0; b0 < B; b0 += kChunk) {
     const int n = std::min(kChunk, B - b0);
-    if (!vae_enc_plan_ || vae_enc_plan_->B != n) {
+    auto found = vae_enc_plans_.find(n);
+    if (found == vae_enc_plans_.end()) {
       DMB_CUDA(cudaStreamSynchronize(s));
-      vae_enc_plan_.reset(new VaeEncPlan());
-      build_vae_enc_plan(*vae_enc_plan_, n);
+      for (auto it = vae_enc_plans_.begin();
+           static_cast<int>(vae_enc_plans_.size()) >= kMaxVaePlans && it != vae_enc_plans_.end();)
+        it = it->first != kChunk ? vae_enc_plans_.erase(it) : std::next(it);
+      found = vae_enc_plans_.emplace(n, std::unique_ptr<VaeEncPlan>(new VaeEncPlan())).first;
+      build_vae_enc_plan(*found->second, n);
       DMB_CUDA(cudaDeviceSynchronize());
     }
+    vae_enc_plan_ = found->second.get();
     VaeEncPlan& p = *vae_enc_plan_;
     p.img = img + b0 * im;
     p.eps = eps + b0 * lat;

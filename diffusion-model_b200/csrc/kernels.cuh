@@ -92,7 +92,10 @@ emb_kernel(EmbWeights w, const long long* __restrict__ t_vec, const long long* _
       const float pe = (tid < 128) ? sinf(arg) : cosf(arg);
       for (int hf = 0; hf < halves; ++hf) {
         // doubled: effective sample hf * B + b; half 0 carries the null label (diff.py:147-150)
-        const long long yv = (doubled && hf == 0) ? static_cast<long long>(null_label) : y[b];
+        // labels outside class_emb's 4 rows never index memory (nn.Embedding raises for them, and so
+        // does the Python layer before the launch): clamped here as a last line of defence
+        long long yv = (doubled && hf == 0) ? static_cast<long long>(null_label) : y[b];
+        yv = yv < 0 ? 0 : (yv > 3 ? 3 : yv);
         const int be = doubled ? hf * B + b : b;
         float e = pe + w.class_emb[yv * kEmbDim + tid];
         if (has_cond) e = e + cond[s];
@@ -841,7 +844,10 @@ cfg_step_kernel(const T* __restrict__ feat, Geo g, int B, const StepParams* __re
   }
   const long long t = p.t_vec[b];
   const int slot = (p.slot_t0 - static_cast<int>(t)) / p.t_stride;
-  const float c1 = p.coef[(t - 1) * 3 + 0], sqrt_a = p.coef[(t - 1) * 3 + 1], sigma = p.coef[(t - 1) * 3 + 2];
+  // the Python layer asserts 1 <= t <= T like the reference (diff.py:140); the row index is clamped
+  // as well so that a raw C-ABI caller with a bad t cannot read outside the table
+  const long long tr = t < 1 ? 0 : (t > p.T ? p.T - 1 : t - 1);
+  const float c1 = p.coef[tr * 3 + 0], sqrt_a = p.coef[tr * 3 + 1], sigma = p.coef[tr * 3 + 2];
   float nz[kLatC] = {0.f, 0.f, 0.f, 0.f};
   if (t != 1) {
     if (p.noise) {

@@ -100,7 +100,14 @@ class Diffuser:
                      cond_mask=None, *, noise=None):
         """One DDPM step with classifier-free guidance (diff.py:127-162)."""
         T = self.num_timesteps
-        assert (t >= 1).all() and (t <= T).all()
+        # the reference's range assertion (diff.py:140) and nn.Embedding's index check, one sync
+        ok = [((t >= 1) & (t <= T)).all()]
+        if y is not None:
+            ok.append(((y >= 0) & (y <= 3)).all().to(ok[0].device))
+        ok = torch.stack(ok).tolist()
+        assert ok[0]
+        if not all(ok):
+            raise IndexError("index out of range in self")
         if not (guidance_scale and y is not None and guidance_scale > 0):
             # The reference has no working non-CFG branch here: with y given it never assigns
             # eps (diff.py:152-156), with y=None it multiplies a tensor by the model's tuple.
@@ -217,6 +224,8 @@ class Diffuser:
         for cls, num in items:
             y_list += [cls] * num
         B = len(y_list)
+        if any(c < 0 or c > 3 for c in y_list) or not (0 <= int(null_label) <= 3):
+            raise IndexError("index out of range in self")     # nn.Embedding(num_classes + 1) in the reference
         y = torch.tensor(y_list, device=device, dtype=torch.long)
 
         if key_order is None:

@@ -209,6 +209,15 @@ class Context:
         sd = module.state_dict(keep_vars=True)
         return tuple((k, sd[k].data_ptr(), sd[k]._version) for k in keys)
 
+    def invalidate(self, module: Optional[torch.nn.Module] = None):
+        """Forget the uploaded weights of `module` (all modules if None): the next call re-uploads
+        and repacks them.  Needed only after writes that bypass the parameters' version counters
+        (`p.data.copy_(...)`, EMA updates through `.data`); load_state_dict / .to() are detected."""
+        for name in ("_unet_token", "_vae_token", "_vae_enc_token"):
+            tok = getattr(self, name)
+            if tok is not None and (module is None or tok[0] == id(module)):
+                setattr(self, name, None)
+
     def ensure_unet(self, module: torch.nn.Module):
         """Upload (repack) the U-Net's parameters if they changed since the last call."""
         sd = module.state_dict(keep_vars=True)
@@ -416,6 +425,12 @@ class Context:
 
 
 _contexts: Dict[Tuple[int, str], Context] = {}
+
+
+def invalidate_module(module: Optional[torch.nn.Module] = None) -> None:
+    """Context.invalidate on every live context of this process."""
+    for ctx in _contexts.values():
+        ctx.invalidate(module)
 
 
 def default_precision() -> str:

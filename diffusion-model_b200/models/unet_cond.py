@@ -98,10 +98,19 @@ class UnetCond(nn.Module):
         ctx.ensure_unet(self)
         return ctx
 
+    def refresh_native(self):
+        """Rebuild the repacked device copy of the weights at the next call.  load_state_dict,
+        Utils.loadModel and .to() are detected automatically; call this after writing parameters
+        through `.data` (no version counter moves)."""
+        from dmb200.native import invalidate_module
+        invalidate_module(self)
+
     def _run(self, x, t, y, cond_vals, cond_mask, want_geom):
         ctx = self._native(x)
         if (cond_vals is None) or (cond_mask is None):
             cond_vals = cond_mask = None  # the reference adds the numeric term only when both are given
+        if bool(((y < 0) | (y > self.num_classes)).any()):
+            raise IndexError("index out of range in self")     # what nn.Embedding raises (unet_cond.py:121)
         with torch.no_grad():
             return ctx.unet_forward(x.float(), t, y, cond_vals, cond_mask, want_geom=want_geom)
 

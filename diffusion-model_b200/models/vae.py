@@ -55,6 +55,11 @@ class VAE(nn.Module):
         ctx.ensure_vae(self)
         return ctx
 
+    def refresh_native(self):
+        """Rebuild the device copy of the weights at the next call (see UnetCond.refresh_native)."""
+        from dmb200.native import invalidate_module
+        invalidate_module(self)
+
     def decode(self, z):
         """z / scale -> decoder -> sigmoid; (B,3,224,224) fp32 in [0,1]  (vae.py:64-69)."""
         with torch.no_grad():
