@@ -56,7 +56,21 @@ def parse_args():
     ap.add_argument("--cpu-sample-steps", type=int, default=3,
                     help="CFG steps timed on the host CPU for the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config4-batch", type=int, default=4096,
+                    help="global batch of the BASELINE config-4 block (sharded over the ranks); 0 skips it")
+    ap.add_argument("--config4-chunk", type=int, default=512, help="samples per plan launch inside config 4")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the tf32 block, the batch-1 eager figure and the config-1 CPU run")
     return ap.parse_args()
+
+
+def host_threads() -> int:
+    """All the host threads this process may use.  torchrun exports OMP_NUM_THREADS=1 to its
+    workers; the CPU legs set the torch thread count explicitly so they do not collapse to one."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
 
 def load_peaks():
@@ -123,18 +137,20 @@ class ClockSampler:
 # ---------------------------------------------------------------------------- CPU baseline
 def cpu_reference_sample(batch: int, n_steps: int, T: int, guidance: float):
     """Times the oracle port (oracle/ref_torch.py -- the reference's algorithm on torch CPU fp32;
-    the reference itself is Python and cannot travel to the GPU box) on the host cores:
-    `n_steps` CFG denoise steps at `batch` plus one VAE decode of 4 (the reference's decode
-    chunk, diff.py:353), extrapolated to T steps."""
+    the reference itself is Python and cannot travel to the GPU box) on ALL the host threads:
+    `n_steps` CFG denoise steps at `batch` mixed line/circle/arc conditions (the native arm's
+    recipe) plus one VAE decode of 4 (the reference's decode chunk, diff.py:353), extrapolated to
+    T steps."""
     import torch
     from oracle import ref_torch as R
     from oracle import synth
     from models.unet_cond_geom import UnetCondWithGeomHead
     from models.vae import VAE
+    torch.set_num_threads(host_threads())
     torch.manual_seed(0)
     sd = UnetCondWithGeomHead().state_dict()
     vsd = VAE().state_dict()
-    y, vals, mask = synth.line_conditions(batch, seed=0)
+    y, vals, mask, _ = synth.mixed_conditions(batch, seed=0)
     x_T, noise = synth.noise_bank(n_steps + 1, (batch, 4, 28, 28), seed=1234)
     _, alphas, abars = R.schedule(T)
     x = x_T
@@ -153,17 +169,56 @@ def cpu_reference_sample(batch: int, n_steps: int, T: int, guidance: float):
         dec_s = (time.perf_counter() - t0) / nd
     total_s = T * step_s + batch * dec_s
     return {"value": batch / total_s, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-            "host_cpus": os.cpu_count(), "step_ms": step_s * 1e3, "decode_ms_per_sample": dec_s * 1e3,
-            "sample": f"{n_steps} CFG denoise steps at batch {batch} + VAE decode of {nd}, oracle port "
-                      f"(torch CPU fp32), extrapolated to T={T}"}
+            "host_cpus": os.cpu_count(), "omp_num_threads_env": os.environ.get("OMP_NUM_THREADS"),
+            "step_ms": step_s * 1e3, "decode_ms_per_sample": dec_s * 1e3,
+            "sample": f"{n_steps} CFG denoise steps at batch {batch} (mixed line/circle/arc) + VAE decode of {nd}, "
+                      f"oracle port (torch CPU fp32, {torch.get_num_threads()} threads), extrapolated to T={T}"}
+
+
+def cpu_config1(T: int, guidance: float, n_steps=None):
+    """BASELINE config 1: batch 1, one line condition, the reference's algorithm on the host CPU.
+    n_steps None = the whole T-step trajectory run outright (about a minute),
+    otherwise `n_steps` consecutive steps after two warm-up steps."""
+    import torch
+    from oracle import ref_torch as R
+    from oracle import synth
+    from models.unet_cond_geom import UnetCondWithGeomHead
+    from models.vae import VAE
+    torch.set_num_threads(host_threads())
+    torch.manual_seed(0)
+    sd = UnetCondWithGeomHead().state_dict()
+    vsd = VAE().state_dict()
+    y, vals, mask = synth.line_conditions(1, seed=0)
+    n = T if n_steps is None else n_steps
+    x_T, noise = synth.noise_bank(n + 2, (1, 4, 28, 28), seed=1234)
+    _, alphas, abars = R.schedule(T)
+    x = x_T
+    with torch.no_grad():
+        for i in range(2):
+            R.denoise_cond(sd, x, torch.full((1,), T, dtype=torch.long), y, guidance, 0, vals, mask, noise[i], alphas, abars)
+        t0 = time.perf_counter()
+        for i in range(n):
+            t = torch.full((1,), T - i, dtype=torch.long)
+            x, _ = R.denoise_cond(sd, x, t, y, guidance, 0, vals, mask, noise[i + 2], alphas, abars)
+        loop_s = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        R.vae_decode(vsd, x)
+        dec_s = time.perf_counter() - t0
+    total = loop_s * (T / n) + dec_s
+    return {"ms_per_denoise_step": 1e3 * loop_s / n, "samples_per_s": 1.0 / total, "decode_ms": dec_s * 1e3,
+            "steps_run": n, "T": T, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": ("whole trajectory run outright" if n_steps is None else f"{n} steps, extrapolated to T={T}")
+                      + f", batch 1, one line condition, oracle port on {torch.get_num_threads()} host threads"}
 
 
 def run_reference(args):
-    """--impl reference: the reference algorithm on the host CPU (oracle port), rank 0 only."""
+    """--impl reference: the reference algorithm on the host CPU (oracle port), rank 0 only, on all
+    host threads whatever the launcher exported."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import torch
+    torch.set_num_threads(host_threads())
     batch = min(args.batch, 32)  # CPU throughput is flat beyond ~16; keeps the sample bounded
     vals = []
     for _ in range(max(0, args.warmup)):
@@ -174,19 +229,211 @@ def run_reference(args):
     wall = time.perf_counter() - t0
     v = statistics.median([r["value"] for r in vals])
     cb = dict(vals[-1]); cb["value"] = v
+    config1 = None
+    if not args.no_extras:
+        # config 1 outright at N=1 (about a minute); a bounded sample when launched for N > 1
+        config1 = cpu_config1(args.T, args.guidance, None if args.gpus == 1 else 20)
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * wall / max(1, args.steps), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"reference algorithm on host CPU: CFG DDPM sampling T={args.T}, batch {batch} line "
-                               "conditions, random-init weights; each step = bounded sample extrapolated to T",
+        "config": {"workload": f"reference algorithm on host CPU: CFG DDPM sampling T={args.T}, batch {batch} = "
+                               f"min(native batch {args.batch}, 32) of mixed line/circle/arc conditions "
+                               "(the native arm's recipe), random-init weights seed 0; each step = "
+                               f"{args.cpu_sample_steps} CFG steps + decode, extrapolated to T",
                    "batch_per_gpu": batch, "T": args.T, "guidance_scale": args.guidance,
-                   "threads": torch.get_num_threads()},
+                   "threads": torch.get_num_threads(), "omp_num_threads_env": os.environ.get("OMP_NUM_THREADS")},
         "cpu_baseline": cb,
+        "config1_batch1": config1,
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------- BASELINE config 4
+def run_config4(args, ctx, dev, world, rank, T, coef, barrier):
+    """BASELINE config 4: a global batch of 4096 synthetic conditions sharded contiguously over the
+    ranks (4096 / N per GPU, run as plan launches of `--config4-chunk` samples), the u8 images
+    gathered with ONE NCCL all-gather, then (rank 0, outside the timed region):
+      gather_check     whole chunks that OTHER ranks produced are recomputed on rank 0 and compared
+                       byte for byte with the gathered images (noise is keyed by the global sample
+                       index, so the N-rank result must equal the 1-rank result);
+      eval_iou_parity  eval_iou_noise scoring of all gathered images on the device
+                       (dmb_score_masks) against a deterministic pseudo ground truth rendered from
+                       the conditions, with the oracle's compute_metrics on 16 of them as the checker.
+    Returns the block for the JSON line (rank 0) or None."""
+    import random
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from oracle import synth
+    from dmb200.sharding import gather_shards, shard_range
+    G, chunk = args.config4_batch, args.config4_chunk
+    y_all, vals_all, mask_all, counts = synth.mixed_conditions(G, seed=4)
+    yd, vd, md = y_all.to(dev), vals_all.to(dev), mask_all.to(dev)
+    b, e = shard_range(G, rank, world)
+
+    def run_chunk(g0, n, steps=T, t_start=T):
+        x = ctx.philox_normal(n, seed=777, sample_offset=g0, t=0)
+        ctx.sample_loop(x, yd[g0:g0 + n], 0, vd[g0:g0 + n], md[g0:g0 + n], args.guidance, coef, t_start, steps,
+                        seed=888, sample_offset=g0)
+        _, u8 = ctx.vae_decode(x, want_f32=False, want_u8=True)
+        return u8
+
+    run_chunk(b, min(chunk, e - b), steps=20)          # plan + graph + decoder warm-up
+    import torch.cuda as tc
+    e0, e1 = tc.Event(enable_timing=True), tc.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    parts = [run_chunk(g0, min(chunk, e - g0)) for g0 in range(b, e, chunk)]
+    local = parts[0] if len(parts) == 1 else torch.cat(parts, 0)
+    full = gather_shards(local, G) if world > 1 else local
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    if rank != 0:
+        return None
+    block = {"global_batch": G, "batch_per_gpu": e - b, "chunk": chunk, "n_gpus": world, "T": T, "ms": ms,
+             "samples_per_s": G / (ms * 1e-3), "scaling": "strong (total work fixed at 4096 samples)",
+             "collective": "one all_gather_into_tensor of (4096/N, 3, 224, 224) u8 per rank" if world > 1 else "none"}
+    # ---- gather_check: recompute chunks of other ranks (any chunk at N=1: determinism)
+    starts = [g0 for g0 in range(0, G, chunk) if world == 1 or not (b <= g0 < e)]
+    pick = sorted(random.Random(0).sample(starts, min(2, len(starts))))
+    equal, n_checked = True, 0
+    for g0 in pick:
+        n = min(chunk, G - g0)
+        again = run_chunk(g0, n)
+        equal = equal and bool(torch.equal(again, full[g0:g0 + n]))
+        n_checked += n
+    block["gather_check"] = {"n": n_checked, "global_chunk_starts": pick, "equal": equal,
+                             "what": "chunks produced by other ranks recomputed on rank 0, byte equality with "
+                                     "the gathered u8 images" if world > 1 else
+                                     "chunks recomputed on the same GPU (determinism), byte equality"}
+    # ---- eval_iou_parity
+    import eval_iou_noise as E
+    from oracle import ref_torch as R
+    gt = synth.render_gt(y_all.numpy(), vals_all.numpy())
+    gt_dev = torch.from_numpy(gt).to(dev)[:, None].contiguous()
+    E.compute_metrics_batch(gt_dev[:8], full[:8])
+    tc.synchronize()
+    t0 = time.perf_counter()
+    metrics = E.compute_metrics_batch(gt_dev, full, sigma=2.0)
+    tc.synchronize()
+    score_ms = (time.perf_counter() - t0) * 1e3
+    idx = sorted(random.Random(1).sample(range(G), 16))
+    worst = {"iou": 0.0, "gt_iou": 0.0, "far_noise_ratio": 0.0, "gauss_recall": 0.0}
+    t0 = time.perf_counter()
+    for i in idx:
+        ref = R.compute_metrics(gt[i] < 128, R.binarise(full[i].cpu().numpy()), sigma=2.0)
+        for k in worst:
+            worst[k] = max(worst[k], abs(ref[k] - metrics[i][k]))
+    oracle_ms_per_image = (time.perf_counter() - t0) * 1e3 / len(idx)
+    block["eval_iou_parity"] = {
+        "n_scored": G, "score_ms_incl_d2h": score_ms, "n_checked_against_oracle": len(idx), "indices": idx,
+        "max_abs_diff": worst, "equal": all(v <= 1e-12 for v in worst.values()),
+        "oracle_ms_per_image": oracle_ms_per_image,
+        "mean": {k: float(np.mean([m[k] for m in metrics])) for k in worst},
+        "ground_truth": "oracle.synth.render_gt: the condition's entity drawn 2 px wide on a white sheet "
+                        "(random-init weights: the scores say nothing about image quality, only that the "
+                        "device scorer and the reference's scorer agree on the gathered batch)"}
+    return block
+
+
+def step_parity(ctx, dev, unet_sd, y, vals, mask, coef, T, guidance):
+    """Teacher-forced CFG step at t = T/2 on the TIMED batch, checked against the oracle port on four
+    of its samples (checker only; outside every timed region)."""
+    import torch
+    from oracle import ref_torch as R
+    B = y.shape[0]
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn((B, 4, 28, 28), generator=g) * 3.0
+    nz = torch.randn((B, 4, 28, 28), generator=g)
+    tt = torch.full((B,), max(1, T // 2), dtype=torch.long)
+    out, eps = ctx.denoise_cond_step(x.to(dev), tt.to(dev), y, 0, vals, mask, guidance, coef, noise=nz.to(dev),
+                                     want_eps=True)
+    pick = torch.tensor(sorted({0, B // 3, (2 * B) // 3, B - 1}))
+    _, alphas, abars = R.schedule(T)
+    with torch.no_grad():
+        x_ref, eps_ref = R.denoise_cond(unet_sd, x[pick], tt[pick], y.cpu()[pick], guidance, 0, vals.cpu()[pick],
+                                        mask.cpu()[pick], nz[pick], alphas, abars)
+    eps, out = eps.cpu()[pick].double(), out.cpu()[pick].double()
+    return {"t": int(tt[0]), "samples": pick.tolist(),
+            "eps_rel_l2": float((eps - eps_ref.double()).norm() / eps_ref.double().norm()),
+            "eps_max_abs_over_max": float((eps - eps_ref.double()).abs().max() / eps_ref.abs().max()),
+            "x_max_abs_over_max": float((out - x_ref.double()).abs().max() / x_ref.abs().max()),
+            "checker": "oracle port (torch CPU fp32) on 4 samples of the timed batch"}
+
+
+def tf32_block(args, dev, unet, T, y, vals, mask, coef, peaks):
+    """fp32-storage / TF32-operand mode on the benched batch: ms per denoise step inside the graph
+    loop (200 steps), samples/s extrapolated, and the fraction of a TF32 peak measured here
+    (cuBLAS fp32 matmul with TF32 allowed, 8192^3: best of 10 and sustained over ~1 s)."""
+    import torch
+    from dmb200 import context_for
+    B = y.shape[0]
+    ctx = context_for(dev, "tf32")
+    ctx.ensure_unet(unet)
+    n = min(T, 200)
+    x = ctx.philox_normal(B, seed=3, sample_offset=0, t=0)
+    ctx.sample_loop(x, y, 0, vals, mask, args.guidance, coef, T, 20, seed=5)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    ctx.sample_loop(x, y, 0, vals, mask, args.guidance, coef, T, n, seed=6)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_step = e0.elapsed_time(e1) / n
+    # TF32 peak
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    N = 8192
+    a = torch.randn((N, N), device=dev)
+    b = torch.randn((N, N), device=dev)
+    c = torch.empty((N, N), device=dev)
+    for _ in range(3):
+        torch.matmul(a, b, out=c)
+    best = 1e9
+    for _ in range(10):
+        e0.record(); torch.matmul(a, b, out=c); e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    reps = 60
+    e0.record()
+    for _ in range(reps):
+        torch.matmul(a, b, out=c)
+    e1.record(); torch.cuda.synchronize()
+    sustained = e0.elapsed_time(e1) / reps
+    torch.backends.cuda.matmul.allow_tf32 = old
+    del a, b, c
+    fl = 2.0 * N ** 3
+    peak_burst, peak_sus = fl / (best * 1e-3) / 1e12, fl / (sustained * 1e-3) / 1e12
+    sps = B / (ms_step * 1e-3 * T)
+    ach = sps * flop_per_sample(T) / 1e12
+    return {"ms_per_denoise_step": ms_step, "samples_per_s_T_extrapolated": sps, "steps_timed": n, "batch": B,
+            "whole_job_tflops": ach, "tf32_peak_tflops_burst": peak_burst, "tf32_peak_tflops_sustained": peak_sus,
+            "whole_job_frac_of_sustained_tf32_peak": ach / peak_sus,
+            "peak_how": "torch.matmul fp32 8192^3 with allow_tf32 (cuBLAS), best of 10 / 60 back to back, CUDA events",
+            "note": "decode excluded (loop only); bf16 is the headline mode"}
+
+
+def batch1_eager(d, unet, dev, T, guidance, y1, v1, m1, n=200):
+    """What generate_steps.py:180-189 does: Diffuser.denoise_cond called from Python once per step at
+    batch 1 (the reference's range assertion syncs every step, as it does in the reference)."""
+    import torch
+    x = torch.randn((1, 4, 28, 28), device=dev)
+    for i in range(5):
+        t = torch.full((1,), T - i, device=dev, dtype=torch.long)
+        x = d.denoise_cond(unet, x, t, y=y1, guidance_scale=guidance, null_label=0, cond_vals=v1, cond_mask=m1)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(n):
+        t = torch.full((1,), T - i, device=dev, dtype=torch.long)
+        x = d.denoise_cond(unet, x, t, y=y1, guidance_scale=guidance, null_label=0, cond_vals=v1, cond_mask=m1)
+    torch.cuda.synchronize()
+    return (time.perf_counter() - t0) * 1e3 / n
 
 
 def run_native(args):
@@ -317,10 +564,20 @@ def run_native(args):
     step_ms_eager = sum(r["ms"] for r in rows) / reps
     achieved = g_fl / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
     peak = peaks["bf16_tflops_sustained"]
-    traffic = None
+    traffic, traffic_note = None, "no ncu capture of this build's GEMM kernel is committed"
     try:
+        import hashlib
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
-            traffic = json.load(f).get("gemm_tc_kernel_dram_bytes_per_launch")
+            tj = json.load(f)
+        h = hashlib.sha256()
+        for fn in ("gemm_tc.cuh", "engine.cu"):
+            with open(os.path.join(PRODUCT, "csrc", fn), "rb") as f:
+                h.update(f.read())
+        if tj.get("source_sha16") == h.hexdigest()[:16]:
+            traffic = tj.get("gemm_tc_kernel_dram_bytes_per_launch")
+            traffic_note = tj.get("note", "")
+        else:
+            traffic_note = "profiles/roofline_traffic.json was captured on another build (source hash differs): null"
     except Exception:
         pass
     groups = {}
@@ -333,7 +590,7 @@ def run_native(args):
         "kernel": "gemm_tc_kernel (tcgen05 implicit-GEMM: 3x3 convs + attention-block linears)",
         "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
         "peak_source": peak_src + ", sustained bf16 figure (kernel timed inside a long step)",
-        "traffic": traffic,
+        "traffic": traffic, "traffic_note": traffic_note,
         "flops_per_launch": g_fl / max(g_n, 1), "avg_launch_us": 1e3 * g_ms / max(g_n, 1),
         "launches_per_step": g_n // reps, "share_of_step": g_ms / reps / step_ms_eager,
         "whole_job": {"achieved": value / world * flop_per_sample(T) / 1e12, "unit": "TFLOP/s",
@@ -364,9 +621,30 @@ def run_native(args):
         batch1 = {"ms_per_denoise_step": res["plain"], "ms_per_denoise_step_with_latent_dump": res["with_latent_dump"],
                   "steps_timed": n1, "note": "batch 1, CFG pair = 2 U-Net passes per step, CUDA-graph loop"}
 
-    cpu = None
+        if not args.no_extras:
+            batch1["eager_ms_per_step"] = batch1_eager(d, unet, dev, T, args.guidance, y1, v1, m1)
+            batch1["eager_note"] = ("Diffuser.denoise_cond called from Python once per step (generate_steps.py:180-189), "
+                                    "wall clock over 200 steps, includes the reference's per-step range assertion sync")
+
+    parity = tf32 = None
+    if rank == 0:
+        unet_sd = {k: v.detach().cpu().clone() for k, v in unet.state_dict().items()}
+        parity = step_parity(ctx, dev, unet_sd, y, vals, mask, coef, T, args.guidance)
+        if not args.no_extras:
+            tf32 = tf32_block(args, dev, unet, T, y, vals, mask, coef, peaks)
+
+    config4 = None
+    if args.config4_batch > 0:
+        config4 = run_config4(args, ctx, dev, world, rank, T, coef, barrier)
+
+    cpu = cpu_b1 = None
     if rank == 0 and not args.no_cpu_baseline:
         cpu = cpu_reference_sample(min(B, 16), args.cpu_sample_steps, T, args.guidance)
+        if not args.no_extras:
+            # config 1 run outright on a 1-GPU launch (about a minute); bounded under torchrun
+            cpu_b1 = cpu_config1(T, args.guidance, None if world == 1 else 20)
+            if batch1 is not None:
+                batch1["cpu_ms_per_denoise_step"] = cpu_b1["ms_per_denoise_step"]
 
     if rank == 0:
         line = {
@@ -392,8 +670,12 @@ def run_native(args):
             "clocks": clock_info,
             "roofline": roofline,
             "cpu_baseline": cpu,
+            "cpu_baseline_b1": cpu_b1,
             "ms_per_denoise_step": ms_total / args.steps / T,
             "batch1": batch1,
+            "parity": parity,
+            "tf32": tf32,
+            "config4": config4,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

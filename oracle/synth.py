@@ -60,3 +60,45 @@ def noise_bank(T: int, shape, seed: int = 1234):
     x_T = torch.randn(shape, generator=g)
     noise = torch.randn((T,) + tuple(shape), generator=g)
     return x_T, noise
+
+
+def render_gt(y, vals, size: int = 224, half_width: float = 1.0, chunk: int = 64) -> np.ndarray:
+    """Pseudo ground truth for the scoring configs: the entity of each condition row drawn as a dark
+    stroke (0) on a white (255) `size` x `size` grey sheet, (N, size, size) uint8 -- what
+    eval_iou_noise.load_binary_mask(invert=True) turns into a thin foreground mask.  Conditions are
+    the normalised (N,12) vectors of entityCsvSampler.py:101-163 (x/W, 1 - y/H, r/W, angle/360), so
+    pixel x = v_x * size and pixel row = v_y * size (the Y flip of the condition puts the sheet's
+    origin at the bottom; an image row counts from the top, which is the same flip again).
+    A pixel is stroke if its centre lies within `half_width` of the entity.  Deterministic; no RNG."""
+    y = np.asarray(y)
+    vals = np.asarray(vals, dtype=np.float64)
+    n = y.shape[0]
+    out = np.full((n, size, size), 255, np.uint8)
+    py, px = np.meshgrid(np.arange(size) + 0.5, np.arange(size) + 0.5, indexing="ij")
+    for b0 in range(0, n, chunk):
+        yy = y[b0:b0 + chunk]
+        v = vals[b0:b0 + chunk] * size
+        d = np.full((len(yy), size, size), 1e9)
+        X, Y = px[None], py[None]
+        ln = yy == 1
+        if ln.any():
+            x1, y1, x2, y2 = (v[ln, i][:, None, None] for i in range(4))
+            dx, dy = x2 - x1, y2 - y1
+            L2 = np.maximum(dx * dx + dy * dy, 1e-12)
+            u = np.clip(((X - x1) * dx + (Y - y1) * dy) / L2, 0.0, 1.0)
+            d[ln] = np.hypot(X - (x1 + u * dx), Y - (y1 + u * dy))
+        ci = yy == 2
+        if ci.any():
+            cx, cy, r = (v[ci, i][:, None, None] for i in (4, 5, 6))
+            d[ci] = np.abs(np.hypot(X - cx, Y - cy) - r)
+        ar = yy == 3
+        if ar.any():
+            ax, ay, r = (v[ar, i][:, None, None] for i in (7, 8, 9))
+            th1 = vals[b0:b0 + chunk][ar, 10][:, None, None] * 360.0
+            th2 = vals[b0:b0 + chunk][ar, 11][:, None, None] * 360.0
+            ang = np.degrees(np.arctan2(-(Y - ay), X - ax)) % 360.0      # counter-clockwise, sheet orientation
+            span = (th2 - th1) % 360.0
+            inside = ((ang - th1) % 360.0) <= span
+            d[ar] = np.where(inside, np.abs(np.hypot(X - ax, Y - ay) - r), 1e9)
+        out[b0:b0 + chunk][d <= half_width] = 0
+    return out
