@@ -3,6 +3,7 @@
 //   T = float         : fp32 activations / weights, tcgen05 kind::tf32, fp32 accumulate
 #include "engine.cuh"
 #include "attention_tc.cuh"
+#include "attention_mma.cuh"
 #include "attn_tail.cuh"
 
 #include <type_traits>
@@ -323,6 +324,17 @@ class Engine : public IEngine {
     g_allow_bn256 = !(bn && bn[0] == '0');
     const char* env = getenv("DMB200_CUDA_CORE_ATTENTION");
     use_tc_attention_ = !(env && env[0] == '1');
+    if (const char* e = getenv("DMB200_ATTN_MMA")) use_mma_attention_ = e[0] != '0';    // 0: the tcgen05 kernel
+    if (const char* e = getenv("DMB200_ATTN_POLY")) attn_poly_ = e[0] != '0';           // 0: every exp2 on MUFU
+    if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+      const int am_smem = 110 * 1024;
+      if (const char* e = getenv("DMB200_ATTN_VAR")) attn_var_ = atoi(e) & 3;
+#define DMB_AM_ATTR(D, P, V) DMB_CUDA(cudaFuncSetAttribute(attention_mma_kernel<D, P, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, am_smem))
+      DMB_AM_ATTR(16, -1, 0); DMB_AM_ATTR(16, -1, 1); DMB_AM_ATTR(16, -1, 2); DMB_AM_ATTR(16, -1, 3); DMB_AM_ATTR(16, 3, 3);
+      DMB_AM_ATTR(32, -1, 0); DMB_AM_ATTR(32, -1, 1); DMB_AM_ATTR(32, -1, 2); DMB_AM_ATTR(32, -1, 3); DMB_AM_ATTR(32, 3, 3);
+      DMB_AM_ATTR(64, -1, 0); DMB_AM_ATTR(64, -1, 1); DMB_AM_ATTR(64, -1, 2); DMB_AM_ATTR(64, -1, 3); DMB_AM_ATTR(64, 3, 3);
+#undef DMB_AM_ATTR
+    }
   }
   ~Engine() override {
     if (ev_fork_) cudaEventDestroy(ev_fork_);
@@ -451,6 +463,9 @@ class Engine : public IEngine {
   long long launches_ = 0;
   bool counting_ = true;
   bool use_tc_attention_ = true;
+  bool use_mma_attention_ = true;   // warp-level MMA attention (attention_mma.cuh) for maps > 3x3 in bf16 mode
+  int attn_var_ = 1;                // experiment bits of attention_mma_kernel (DMB200_ATTN_VAR)
+  bool attn_poly_ = false;          // DMB200_ATTN_POLY=1: a quarter of its exponentials on the FMA pipe (measured slower: issue-bound)
   cudaStream_t side_ = nullptr;
   cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
   bool use_pdl_ = false;   // DMB200_PDL=1: programmatic dependent launch (measured: no gain at batch 1, -1.6 % at 256)
@@ -1061,6 +1076,32 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.push_back([this, qkv, av, C](cudaStream_t s) {
       const int L = qkv.g.H * qkv.g.W, D = C / 4;
       if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+        if (use_mma_attention_ && use_tc_attention_ && L > 16) {
+          // one CTA per (sample, head) with up to 7 warps, each owning 16-row query tiles; when the
+          // batch is too small to fill the chip twice the tiles are spread over more CTAs
+          const int ntiles = cdiv(L, 16);
+          const int nw = std::min(7, ntiles);
+          const int splits = std::max(1, std::min(cdiv(ntiles, nw), cdiv(2 * num_sms_, 4 * qkv.g.n)));
+          const int tpc = cdiv(ntiles, splits);
+          const dim3 grid(cdiv(ntiles, tpc), 4, qkv.g.n);
+          const size_t smem = attention_mma_smem_bytes(L, D);
+          const int threads = 32 * std::min(nw, tpc);
+#define DMB_AM_LAUNCH(P, V)                                                                                         \
+  do {                                                                                                              \
+    if (D == 16) launch(attention_mma_kernel<16, P, V>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p, tpc);       \
+    else if (D == 32) launch(attention_mma_kernel<32, P, V>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p, tpc);  \
+    else launch(attention_mma_kernel<64, P, V>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p, tpc);               \
+  } while (0)
+          if (attn_poly_) DMB_AM_LAUNCH(3, 3);
+          else if (attn_var_ == 0) DMB_AM_LAUNCH(-1, 0);
+          else if (attn_var_ == 1) DMB_AM_LAUNCH(-1, 1);
+          else if (attn_var_ == 2) DMB_AM_LAUNCH(-1, 2);
+          else DMB_AM_LAUNCH(-1, 3);
+#undef DMB_AM_LAUNCH
+          DMB_CHECK_LAUNCH();
+          count();
+          return;
+        }
         if (use_tc_attention_ && L > 16) {   // tiny maps (3x3): a 128-row MMA tile would be > 90 % padding
           // whole (sample, head) per CTA when there are enough of them to fill the chip twice
           // over; otherwise the query blocks are spread over more CTAs

@@ -299,7 +299,8 @@ def test_strided_ddim_extension_matches_oracle(models):
     assert r < 3e-2
 
 
-@pytest.mark.parametrize("switch", ["DMB200_FUSED_TAIL", "DMB200_ROW3", "DMB200_FUSE_LN1"])
+@pytest.mark.parametrize("switch", ["DMB200_FUSED_TAIL", "DMB200_ROW3", "DMB200_FUSE_LN1", "DMB200_ATTN_MMA",
+                                    "DMB200_ATTN_POLY"])
 def test_fused_kernels_agree_with_separate_launches(models, switch):
     """The fused attention-block tail (attn_tail_kernel) and the kernel-row A windows of the 3x3
     convs (kRow3) are re-schedulings of the same arithmetic: the U-Net output must agree with the
