@@ -206,8 +206,8 @@ struct Act {  // an activation in padded pixel-matrix layout
   CUtensorMap tmap_samples; // 3D (channel, row of the sample, sample) view: pixel-major conv mode on small maps
   bool has_samples_map = false;
   CUtensorMap tmap_halo;    // box of kHaloRows rows: the shared A window of a 3x3 kernel row (gemm_tc.cuh, kRow3)
-  float2* stats = nullptr;  // [n_stat_tiles][rows_alloc] GroupNorm row partials (conv outputs only)
-  int n_stat_tiles = 0;
+  long long* sstat = nullptr;  // [2 * n] fixed-point (sum, sumsq) per sample for the following GroupNorm(1, C)
+                               // (conv outputs only; a slice of the plan's statistics arena, cleared once per step)
 };
 
 using Op = std::function<void(cudaStream_t)>;
@@ -416,7 +416,7 @@ class Engine : public IEngine {
     cfg.numAttrs = use_pdl_ ? 1 : 0;
     DMB_CUDA(cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...));
   }
-  Act<T> new_act(Pool& pool, int n, int H, int W, int C, bool with_stats, int stat_tiles = 0);
+  Act<T> new_act(Pool& pool, int n, int H, int W, int C, bool with_stats);
   // N tile of a launch: the weight's own tile, halved (down to 32) while the launch would leave
   // SMs without a tile -- at small batch the GEMMs are bound by streaming the weights, and more,
   // narrower tiles spread that stream over more SMs.
@@ -462,6 +462,8 @@ class Engine : public IEngine {
   int num_sms_ = 148;
   long long launches_ = 0;
   bool counting_ = true;
+  long long* stat_arena_cur_ = nullptr;   // bump cursor into the statistics arena of the plan being built
+  size_t stat_arena_left_ = 0;
   bool use_tc_attention_ = true;
   bool use_mma_attention_ = true;   // warp-level MMA attention (attention_mma.cuh) for maps > 3x3 in bf16 mode
   int attn_var_ = 1;                // experiment bits of attention_mma_kernel (DMB200_ATTN_VAR)
@@ -749,7 +751,7 @@ namespace dmb {
 // Launch helpers
 // ---------------------------------------------------------------------------
 template <typename T>
-Act<T> Engine<T>::new_act(Pool& pool, int n, int H, int W, int C, bool with_stats, int stat_tiles) {
+Act<T> Engine<T>::new_act(Pool& pool, int n, int H, int W, int C, bool with_stats) {
   Act<T> a;
   a.C = C;
   a.g = make_geo(n, H, W);
@@ -763,8 +765,11 @@ Act<T> Engine<T>::new_act(Pool& pool, int n, int H, int W, int C, bool with_stat
     }
   }
   if (with_stats) {
-    a.n_stat_tiles = stat_tiles;
-    a.stats = pool.alloc_n<float2>(static_cast<size_t>(stat_tiles) * a.g.rows_alloc);
+    const size_t need = 2 * static_cast<size_t>(n);
+    if (stat_arena_left_ < need) fail(1, "internal error: GroupNorm statistics arena exhausted");
+    a.sstat = stat_arena_cur_;
+    stat_arena_cur_ += need;
+    stat_arena_left_ -= need;
   }
   return a;
 }
@@ -800,7 +805,6 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     while (narrow_tiles_ && bn > 64 && HW * cdiv(a.g.n, kTileM) * (w.rows_per_tap / bn) * 100 < num_sms_ * pix_fill_pct_) bn >>= 1;
   }
   p.block_n = bn;
-  p.stat_cols = std::min(bn, ElemTraits<T>::kChunkK);
   p.n_tiles = w.rows_per_tap / bn;
   // CTA pairs (256-row tiles) when there is enough work to keep every pair busy
   const int m_tiles1 = pix ? HW * cdiv(a.g.n, kTileM) : cdiv(a.g.rows_valid, kTileM);
@@ -859,7 +863,6 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM * ctas, bn);
   p.tmem_cols = tmem_cols_for(bn * n_acc / 2);
   p.geo = a.g;
-  p.rows_alloc = a.g.rows_alloc;
   p.n_valid = w.N;
   const int smem = p.stages * stage_bytes + staging + 1024;
   const CUtensorMap& tout = pix ? out_act->tmap_samples : (p.tma_store ? out_act->tmap : a.tmap);
@@ -909,7 +912,7 @@ Op Engine<T>::op_conv(const Act<T>& in, const GemmW<T>& w, const Act<T>& out) {
     ep.epi = EPI_STORE;
     ep.out = out.p; ep.ldc = out.C;
     ep.bias = w.bias;
-    ep.rowstats = out.stats;
+    ep.sample_stats = out.sstat;
     gemm(in, w, 0, shifts, 9, ep, s, &out);
   };
 }
@@ -947,6 +950,17 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   P.eps = pool.alloc_n<float>(static_cast<size_t>(B) * kLatC * kLatH * kLatW);
   P.geom = pool.alloc_n<float>(B * 12);
   auto& ops = P.ops;
+
+  {  // GroupNorm statistics arena: two 64-bit fixed-point sums per sample for each of the 32 convs that
+     // feed a GroupNorm(1, C); one memset at the head of every step clears all of them
+    constexpr int kStatActs = 40;
+    const size_t words = static_cast<size_t>(kStatActs) * 2 * n;
+    long long* arena = pool.alloc_n<long long>(words);
+    stat_arena_cur_ = arena;
+    stat_arena_left_ = words;
+    ops.tag("stat clear");
+    ops.push_back([arena, words](cudaStream_t s) { DMB_CUDA(cudaMemsetAsync(arena, 0, words * sizeof(long long), s)); });
+  }
 
   {  // embedding + six projections
     const EmbWeights ew = embw_;
@@ -1008,14 +1022,14 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.push_back([this, raw, out, gamma, beta, mode, res, embproj, emb_off, splits, fuse_ln, ln_w, ln_b, pre](cudaStream_t s) {
       const dim3 grid(splits, out.g.n);
       if (fuse_ln) {
-        launch(gn1_apply_kernel<T, GN_ADD_EMB, true>, grid, 256, 0, s, raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc,
+        launch(gn1_apply_kernel<T, GN_ADD_EMB, true>, grid, 256, 0, s, raw.p, raw.sstat,
                gamma, beta, res, embproj, emb_off, out.g, raw.C, out.p, raw.g.n,
                1.0 / (static_cast<double>(raw.g.H) * raw.g.W * raw.C), ln_w, ln_b, pre);
         DMB_CHECK_LAUNCH();
         count();
         return;
       }
-#define DMB_GN_ARGS raw.p, raw.stats, raw.n_stat_tiles, raw.g.rows_alloc, gamma, beta, res, embproj, emb_off, out.g, raw.C, out.p, raw.g.n, 1.0 / (static_cast<double>(raw.g.H) * raw.g.W * raw.C), static_cast<const float*>(nullptr), static_cast<const float*>(nullptr), static_cast<T*>(nullptr)
+#define DMB_GN_ARGS raw.p, raw.sstat, gamma, beta, res, embproj, emb_off, out.g, raw.C, out.p, raw.g.n, 1.0 / (static_cast<double>(raw.g.H) * raw.g.W * raw.C), static_cast<const float*>(nullptr), static_cast<const float*>(nullptr), static_cast<T*>(nullptr)
       if (mode == GN_GELU) launch(gn1_apply_kernel<T, GN_GELU>, grid, 256, 0, s, DMB_GN_ARGS);
       else if (mode == GN_RES_GELU) launch(gn1_apply_kernel<T, GN_RES_GELU>, grid, 256, 0, s, DMB_GN_ARGS);
       else if (mode == GN_ADD_EMB) launch(gn1_apply_kernel<T, GN_ADD_EMB>, grid, 256, 0, s, DMB_GN_ARGS);
@@ -1028,7 +1042,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   };
   auto conv = [&](const Act<T>& in, const std::string& wname) {
     const GemmW<T>& w = gw_.at(wname);
-    Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, true, w.rows_per_tap / std::min(effective_bn(w, in.g.rows_valid), ElemTraits<T>::kChunkK));
+    Act<T> out = new_act(pool, in.g.n, in.g.H, in.g.W, w.N, true);
     ops.tag("conv3x3 " + std::to_string(w.K) + "->" + std::to_string(w.N) + " @" + std::to_string(in.g.H),
             2.0 * in.g.n * in.g.H * in.g.W * 9.0 * w.K * w.N);
     ops.push_back(op_conv(in, w, out));
@@ -1202,7 +1216,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   // 2B at down1's embedding add; up3 reads the shared inc output as its skip tensor.
   const int n0 = B;
   // inc: the 4->64 conv runs on CUDA cores straight from the fp32 latent.
-  Act<T> r0 = new_act(pool, n0, kLatH, kLatW, 64, true, 1);
+  Act<T> r0 = new_act(pool, n0, kLatH, kLatW, 64, true);
   {
     const float* w0 = f("inc.double_conv.0.weight");
     Plan<T>* pp = &P;
@@ -1210,10 +1224,10 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.push_back([this, r0, w0, pp, B](cudaStream_t s) {
       if constexpr (std::is_same<T, __nv_bfloat16>::value)
         launch(conv_in_mma_kernel, dim3(r0.g.n, 1), kConvInThreads, 0, s, pp->x_state, B, w0, nullptr, 1.0f, r0.g, 64,
-                                                                      r0.p, r0.stats);
+                                                                      r0.p, r0.sstat);
       else
         conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), r0.g.n, 1), 128, 0, s>>>(pp->x_state, B, w0, nullptr, 1.0f,
-                                                                                    r0.g, 64, r0.p, r0.stats);
+                                                                                    r0.g, 64, r0.p, r0.sstat);
       DMB_CHECK_LAUNCH();
       count();
     });
@@ -1787,7 +1801,12 @@ void Engine<T>::op_conv3x3(const float* x, const float* w, int B, int Cin, int C
   GemmW<T> gw = make_conv3x3_from_ptr(wd, Cout, Cin, pool);
   Act<T> in = new_act(pool, B, H, W, Cin, false);
   const int cpad = gw.rows_per_tap;
-  Act<T> o = new_act(pool, B, H, W, cpad, true, gw.rows_per_tap / std::min(effective_bn(gw, make_geo(B, H, W).rows_valid), ElemTraits<T>::kChunkK));
+  // (the epilogue's GroupNorm statistics run as in the network: a private two-words-per-sample arena)
+  stat_arena_cur_ = pool.alloc_n<long long>(2 * static_cast<size_t>(B));
+  stat_arena_left_ = 2 * static_cast<size_t>(B);
+  DMB_CUDA(cudaMemset(stat_arena_cur_, 0, 2 * static_cast<size_t>(B) * sizeof(long long)));
+  Act<T> o = new_act(pool, B, H, W, cpad, true);
+  stat_arena_left_ = 0;
   DMB_CUDA(cudaDeviceSynchronize());
   const long long tin = static_cast<long long>(B) * Cin * H * W;
   nchw_to_pm_kernel<T><<<cdiv(tin, 256), 256, 0, s>>>(x, in.g, Cin, in.p);

@@ -17,8 +17,8 @@
 //                            (multicast to both CTAs) and to tmem_full[a]
 //   warp 2    TMEM allocator
 //   warps 4-7 / 8-11  two epilogue warpgroups, one per TMEM accumulator stage (tile parity):
-//                            tcgen05.ld lane == row, bias / GELU / residual, GroupNorm row
-//                            statistics per aligned column group, then the tile goes through the
+//                            tcgen05.ld lane == row, bias / GELU / residual, GroupNorm
+//                            statistics (fixed-point per-sample sums), then the tile goes through the
 //                            warpgroup's own 128B-swizzled staging buffer and out with one TMA
 //                            store per 128-byte column block (pad-pixel rows are stored as zeros).
 // Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1 and the
@@ -58,9 +58,8 @@ struct GemmParams {
   const float* bias;      // [n_valid] or null
   int act;                // 0 none, 1 GELU(erf)
   const void* residual;   // T [rows, ldc] or null (added after the activation)
-  float2* rowstats;       // [N / stat_cols][rows_alloc] (sum, sum of squares) or null
-  int stat_cols;          // columns per statistics group: min(block_n, 128-byte K chunk)
-  int rows_alloc;
+  long long* sample_stats;  // [2 * samples] fixed-point (sum, sum of squares) of the output per sample for the
+                            // following GroupNorm(1, C) (StatAcc / stat_commit, common.cuh), or null
   int map_mode;           // 0 identity; 1 = out pixel (2y+up_a, 2x+up_b) of geo_out
   Geo geo_out;
   int up_a, up_b;
@@ -417,20 +416,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       bool valid;
       if (pix) {   // rows of the tile are samples; r = the output pixel's PM row
         valid = r < p.geo.n;
+        b = r;
         r = r * p.geo.S + prow;
       } else {
         valid = geo_decode(p.geo, r, b, y, x);
       }
+      StatAcc sacc;   // this row's share of its sample's GroupNorm statistics (all columns of the tile)
 
       const uint32_t aph = (tile_count / kAcc) & 1;
       mbar_wait(&tmem_full_bar[as], aph);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * p.block_n;
-      // GroupNorm partials of this row: one (sum, sumsq) per aligned group of
-      // p.stat_cols = min(block_n, kSubN) columns, each the aligned binary tree of its 16-column
-      // units; gn1_apply joins the groups in the same tree (common.cuh, StatTree), so the
-      // statistics do not depend on the N tile of the launch.
-      float2* stat_row = p.rowstats ? p.rowstats + static_cast<size_t>(n0 / p.stat_cols) * p.rows_alloc + r : nullptr;
+      // GroupNorm statistics: every aligned 16-column unit of the row is summed in fp32 (stat_unit16),
+      // converted to fixed point and added as integers, so the per-sample totals do not depend on the
+      // N tile of the launch, on the tile order or on the batch (common.cuh, StatAcc).
 
       if (p.tma_store) {
         // kP columns are in registers at a time: a whole 128-byte sub-tile with two epilogue
@@ -474,13 +473,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                   for (int i = 0; i < 8; ++i) v[8 * j + i] += rv[i];
                 }
               }
-              if constexpr (kHalves == 1) {   // (launches with row statistics use two warpgroups)
-                if (stat_row) {   // block_n >= kSubN here: one group per sub-tile
-                  float2 u[kSubN / 16];
+              if constexpr (kHalves == 1) {   // (launches with statistics use two warpgroups)
+                if (p.sample_stats) {
 #pragma unroll
-                  for (int j = 0; j < kSubN / 16; ++j) u[j] = stat_unit16(v + 16 * j);
-                  if constexpr (kSubN == 64) stat_row[static_cast<size_t>(k) * p.rows_alloc] = StatTree::join(StatTree::join(u[0], u[1]), StatTree::join(u[2], u[3]));
-                  else stat_row[static_cast<size_t>(k) * p.rows_alloc] = StatTree::join(u[0], u[1]);
+                  for (int j = 0; j < kSubN / 16; ++j) sacc.add(stat_unit16(v + 16 * j));
                 }
               }
             } else {
@@ -520,6 +516,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             tma_store_commit();
           }
         }
+        if (p.sample_stats) stat_commit(p.sample_stats, b, valid, sacc.s1, sacc.s2);
       } else if (p.epi == EPI_IMAGE) {
         float v[16];
         tmem_ld16(t_row, v);
@@ -538,7 +535,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       } else {
         int out_r = r;
         if (p.map_mode == 1 && valid) out_r = geo_row(p.geo_out, b, 2 * y + p.up_a, 2 * x + p.up_b);
-        float2 stat_hold = make_float2(0.f, 0.f);
         for (int c0 = 0; c0 < p.block_n; c0 += 32) {
           float v[32];
           if (p.block_n - c0 >= 32) {
@@ -573,16 +569,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
               }
             }
-            if (stat_row) {   // block_n is a multiple of 16: whole units only
-              float2 g32 = stat_unit16(v);
-              if (ncols > 16) g32 = StatTree::join(g32, stat_unit16(v + 16));
-              if (p.stat_cols <= 32) {
-                stat_row[static_cast<size_t>(c0 / p.stat_cols) * p.rows_alloc] = g32;
-              } else if ((c0 & 32) == 0) {   // 64-column groups: left half now, joined with the right half next
-                stat_hold = g32;
-              } else {
-                stat_row[static_cast<size_t>(c0 / 64) * p.rows_alloc] = StatTree::join(stat_hold, g32);
-              }
+            if (p.sample_stats) {   // block_n is a multiple of 16: whole units only
+              sacc.add(stat_unit16(v));
+              if (ncols > 16) sacc.add(stat_unit16(v + 16));
             }
             T* op = out + static_cast<size_t>(out_r) * p.ldc + col0;
 #pragma unroll
@@ -592,6 +581,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           }
         }
         release_tmem();
+        if (p.sample_stats) stat_commit(p.sample_stats, b, valid, sacc.s1, sacc.s2);
       }
     }
     if (store_thread) tma_store_wait_all<0>();

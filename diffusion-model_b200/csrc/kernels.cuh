@@ -137,7 +137,7 @@ template <typename T>
 __global__ void __launch_bounds__(128)
 conv_in_kernel(const float* __restrict__ x, int B_src, const float* __restrict__ w_oihw,
                const float* __restrict__ bias, float in_div, Geo g, int cout,
-               T* __restrict__ out, float2* __restrict__ rowstats) {
+               T* __restrict__ out, long long* __restrict__ sample_stats) {
   __shared__ float ws[36 * 64];
   const int co0 = blockIdx.z * 64;
   for (int i = threadIdx.x; i < 36 * 64; i += blockDim.x) {
@@ -146,8 +146,9 @@ conv_in_kernel(const float* __restrict__ x, int B_src, const float* __restrict__
   }
   __syncthreads();
   const int be = blockIdx.y;
-  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
-  if (pix >= g.H * g.W) return;
+  const int pix_raw = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool pix_ok = pix_raw < g.H * g.W;   // (no early return: the statistics are committed by whole warps)
+  const int pix = pix_ok ? pix_raw : 0;
   const int y = pix / g.W, xx = pix % g.W;
   const float* xs = x + static_cast<size_t>(be % B_src) * kLatC * g.H * g.W;
   float in[36];
@@ -173,14 +174,16 @@ conv_in_kernel(const float* __restrict__ x, int B_src, const float* __restrict__
   }
   const int r = geo_row(g, be, y, xx);
   T* op = out + static_cast<size_t>(r) * cout + co0;
-  float s = 0.f, ss = 0.f;
+  if (pix_ok) {
 #pragma unroll
-  for (int co = 0; co < 64; co += 8) {
-    store8(op + co, acc + co);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { s += acc[co + i]; ss += acc[co + i] * acc[co + i]; }
+    for (int co = 0; co < 64; co += 8) store8(op + co, acc + co);
   }
-  if (rowstats) rowstats[r] = make_float2(s, ss);
+  if (sample_stats) {
+    StatAcc sa;
+#pragma unroll
+    for (int co = 0; co < 64; co += 16) sa.add(stat_unit16(acc + co));
+    stat_commit(sample_stats, be, pix_ok, sa.s1, sa.s2);
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -207,7 +210,7 @@ constexpr int kConvInThreads = 256;
 static __global__ void __launch_bounds__(kConvInThreads)
 conv_in_mma_kernel(const float* __restrict__ x, int B_src, const float* __restrict__ w_oihw,
                    const float* __restrict__ bias, float in_div, Geo g, int cout,
-                   __nv_bfloat16* __restrict__ out, float2* __restrict__ rowstats) {
+                   __nv_bfloat16* __restrict__ out, long long* __restrict__ sample_stats) {
   pdl_trigger();
   pdl_wait();
   constexpr int PW = kLatW + 2, PH = kLatH + 2, PLANE = PW * PH;   // zero-bordered latent plane
@@ -258,6 +261,7 @@ conv_in_mma_kernel(const float* __restrict__ x, int B_src, const float* __restri
   }
 
   constexpr int NPIX = kLatH * kLatW;
+  StatAcc sacc;   // this lane's share of the sample's GroupNorm statistics
   for (int mt = warp; mt * 16 < NPIX; mt += kConvInThreads / 32) {
     const int p0 = mt * 16 + gq, p1 = p0 + 8;
     const bool v0 = p0 < NPIX, v1 = p1 < NPIX;
@@ -290,24 +294,18 @@ conv_in_mma_kernel(const float* __restrict__ x, int B_src, const float* __restri
       if (v0) *reinterpret_cast<uint32_t*>(o0 + nt * 8) = pack_bf16x2(acc[nt][0], acc[nt][1]);
       if (v1) *reinterpret_cast<uint32_t*>(o1 + nt * 8) = pack_bf16x2(acc[nt][2], acc[nt][3]);
     }
-    if (rowstats) {
-#pragma unroll
-      for (int o = 1; o <= 2; o <<= 1) {
-        s0 += __shfl_xor_sync(0xffffffffu, s0, o); q0 += __shfl_xor_sync(0xffffffffu, q0, o);
-        s1 += __shfl_xor_sync(0xffffffffu, s1, o); q1 += __shfl_xor_sync(0xffffffffu, q1, o);
-      }
-      if (tq == 0) {
-        if (v0) rowstats[r0] = make_float2(s0, q0);
-        if (v1) rowstats[r1] = make_float2(s1, q1);
-      }
+    if (sample_stats) {
+      // this lane's 16 values of each of its two rows (fp32, fixed order) -> fixed point
+      if (v0) sacc.add(make_float2(s0, q0));
+      if (v1) sacc.add(make_float2(s1, q1));
     }
   }
+  if (sample_stats) stat_commit(sample_stats, be, true, sacc.s1, sacc.s2);   // one CTA = one sample
 }
 
 // ---------------------------------------------------------------------------
-// GroupNorm(1, C) application.  The producing conv left per-row (sum, sumsq) partials;
-// each CTA first reduces its sample's partials in a fixed order (double), then normalises
-// its slice.  mode: 0 affine only, 1 GELU, 2 GELU(residual + .), 3 + emb[b, c].
+// GroupNorm(1, C) application.  The producing conv left the sample's (sum, sumsq) as two
+// fixed-point integers (common.cuh, StatAcc); each CTA normalises its slice.  mode: 0 affine only, 1 GELU, 2 GELU(residual + .), 3 + emb[b, c].
 // models/unet_cond.py:18-28, 67-70, 98-100.
 // ---------------------------------------------------------------------------
 enum GnMode : int { GN_NONE = 0, GN_GELU = 1, GN_RES_GELU = 2, GN_ADD_EMB = 3 };
@@ -324,7 +322,7 @@ enum GnMode : int { GN_NONE = 0, GN_GELU = 1, GN_RES_GELU = 2, GN_ADD_EMB = 3 };
 // is stored to `out_pre` only when the caller keeps it for inspection (taps).
 template <typename T, int MODE, bool kLN = false>
 __global__ void __launch_bounds__(256, 3)
-gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats, int n_stat_tiles, int rows_alloc,
+gn1_apply_kernel(const T* __restrict__ raw, const long long* __restrict__ sample_stats,
                  const float* __restrict__ gamma, const float* __restrict__ beta,
                  const T* __restrict__ residual, const float* __restrict__ embproj,
                  int emb_off, Geo g, int C, T* __restrict__ out, int n_src, double inv_cnt,
@@ -342,10 +340,6 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
   const int rows_per_iter = 256 / vpr;
   const int cv = tid % vpr;
   const int c0 = cv * 8;
-  // ---- statistics: the producing conv left per-row (sum, sumsq) partials; every CTA of the
-  // sample reduces them in the same fixed order (double), so the result does not depend on
-  // the sample's position in the batch nor on how the batch is sharded.
-  __shared__ double red[2][8];
   // affine parameters (and the embedding row) do not depend on the statistics: their loads are
   // issued first, so they are in flight together with the partials below
   float gm[8], bt[8];
@@ -360,59 +354,14 @@ gn1_apply_kernel(const T* __restrict__ raw, const float2* __restrict__ rowstats,
       bt[0] += ea.x; bt[1] += ea.y; bt[2] += ea.z; bt[3] += ea.w; bt[4] += eb.x; bt[5] += eb.y; bt[6] += eb.z; bt[7] += eb.w;
     }
   }
+  // ---- statistics: two fixed-point sums per sample, left by the producing conv (StatAcc):
+  // every thread reads them itself -- no reduction, no barrier in front of the streaming loop
   float mean, rstd;
   {
-    double s1 = 0.0, s2 = 0.0;
-    const size_t sbase = static_cast<size_t>(b_src) * g.S;
-    const int rows_iter = (g.S - g.Wp + 255) >> 8;   // rows per thread
-    if (rows_iter * n_stat_tiles <= 8) {
-      // all partials of the thread are loaded before any is used: one memory latency instead of
-      // one per row (this phase is a fixed cost in front of every CTA's streaming loop)
-      float2 v[8];
-      bool okv[8];
-      int it = 0, tn = 0;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const int sr = g.Wp + tid + (it << 8);
-        okv[k] = it < rows_iter && sr < g.S && geo_is_pixel(g, sr);
-        if (okv[k]) v[k] = rowstats[sbase + sr + static_cast<size_t>(tn) * rows_alloc];
-        if (++tn == n_stat_tiles) { tn = 0; ++it; }
-      }
-      StatTree acc;   // the groups of a row join in the same aligned tree as the units inside a group
-      tn = 0;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        if (okv[k]) acc.add(v[k]);
-        if (++tn == n_stat_tiles) {
-          if (acc.n) { const float2 a = acc.total(); s1 += a.x; s2 += a.y; }
-          acc.n = 0;
-          tn = 0;
-        }
-      }
-    } else {
-      for (int rr = g.Wp + tid; rr < g.S; rr += 256) {
-        if (!geo_is_pixel(g, rr)) continue;
-        StatTree acc;
-        const float2* rs = rowstats + sbase + rr;
-        for (int tn = 0; tn < n_stat_tiles; ++tn) acc.add(rs[static_cast<size_t>(tn) * rows_alloc]);
-        const float2 a = acc.total();
-        s1 += a.x; s2 += a.y;
-      }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-    }
-    if ((tid & 31) == 0) { red[0][tid >> 5] = s1; red[1][tid >> 5] = s2; }
-    __syncthreads();
-    // every thread finishes the reduction itself (same order): no second barrier
-    double t1 = 0.0, t2 = 0.0;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) { t1 += red[0][w]; t2 += red[1][w]; }
+    const long long s1 = sample_stats[2 * b_src], s2 = sample_stats[2 * b_src + 1];
     // inv_cnt = 1 / (H W C) from the host: no double-precision division on this path
-    const double dmean = t1 * inv_cnt;
-    double var = t2 * inv_cnt - dmean * dmean;
+    const double dmean = static_cast<double>(s1) * kStatInv1 * inv_cnt;
+    double var = static_cast<double>(s2) * kStatInv2 * inv_cnt - dmean * dmean;
     if (var < 0.0) var = 0.0;
     mean = static_cast<float>(dmean);
     rstd = rsqrtf(static_cast<float>(var) + 1e-5f);
