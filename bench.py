@@ -59,6 +59,7 @@ def parse_args():
     ap.add_argument("--config4-batch", type=int, default=4096,
                     help="global batch of the BASELINE config-4 block (sharded over the ranks); 0 skips it")
     ap.add_argument("--config4-chunk", type=int, default=512, help="samples per plan launch inside config 4")
+    ap.add_argument("--cpu-leg", default=None, help=argparse.SUPPRESS)   # internal: run one CPU leg and print its JSON
     ap.add_argument("--no-extras", action="store_true",
                     help="skip the tf32 block, the batch-1 eager figure and the config-1 CPU run")
     return ap.parse_args()
@@ -135,6 +136,37 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------- CPU baseline
+def cpu_env():
+    """Environment for a CPU leg: every host thread for OpenMP / MKL whatever the launcher exported
+    (torchrun sets OMP_NUM_THREADS=1), and no GPU."""
+    env = dict(os.environ)
+    n = str(host_threads())
+    env.update(OMP_NUM_THREADS=n, MKL_NUM_THREADS=n, CUDA_VISIBLE_DEVICES="", DMB_BENCH_CPU_ENV="1")
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "TORCHELASTIC_RUN_ID",
+              "GROUP_RANK", "LOCAL_WORLD_SIZE", "ROLE_RANK", "ROLE_WORLD_SIZE"):
+        env.pop(k, None)
+    return env
+
+
+def cpu_leg(kind: str, **kw):
+    """Runs one CPU leg (`baseline` = cpu_reference_sample, `config1` = cpu_config1) in a FRESH process:
+    inside a process that holds a CUDA context and an NCCL communicator under torchrun the OpenMP
+    pool, created with one thread, ran the same code 100x slower even after set_num_threads
+    (measured: 1794 vs 17 ms per batch-1 step on a 24-thread host)."""
+    cmd = [sys.executable, os.path.abspath(__file__), "--cpu-leg", json.dumps({"kind": kind, **kw})]
+    out = subprocess.run(cmd, env=cpu_env(), capture_output=True, text=True, timeout=1200)
+    if out.returncode != 0:
+        raise RuntimeError(f"CPU leg {kind} failed: {out.stderr[-2000:]}")
+    return json.loads([ln for ln in out.stdout.splitlines() if ln.startswith("{")][-1])
+
+
+def run_cpu_leg(spec: str):
+    kw = json.loads(spec)
+    kind = kw.pop("kind")
+    fn = {"baseline": cpu_reference_sample, "config1": cpu_config1}[kind]
+    print(json.dumps(fn(**kw)), flush=True)
+
+
 def cpu_reference_sample(batch: int, n_steps: int, T: int, guidance: float):
     """Times the oracle port (oracle/ref_torch.py -- the reference's algorithm on torch CPU fp32;
     the reference itself is Python and cannot travel to the GPU box) on ALL the host threads:
@@ -217,6 +249,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if os.environ.get("DMB_BENCH_CPU_ENV") != "1":
+        # same process image, clean environment (all host threads, no GPU, no rendezvous variables)
+        sys.stdout.flush()
+        os.execve(sys.executable, [sys.executable, os.path.abspath(__file__)] + sys.argv[1:], cpu_env())
     import torch
     torch.set_num_threads(host_threads())
     batch = min(args.batch, 32)  # CPU throughput is flat beyond ~16; keeps the sample bounded
@@ -639,10 +675,10 @@ def run_native(args):
 
     cpu = cpu_b1 = None
     if rank == 0 and not args.no_cpu_baseline:
-        cpu = cpu_reference_sample(min(B, 16), args.cpu_sample_steps, T, args.guidance)
+        cpu = cpu_leg("baseline", batch=min(B, 16), n_steps=args.cpu_sample_steps, T=T, guidance=args.guidance)
         if not args.no_extras:
             # config 1 run outright on a 1-GPU launch (about a minute); bounded under torchrun
-            cpu_b1 = cpu_config1(T, args.guidance, None if world == 1 else 20)
+            cpu_b1 = cpu_leg("config1", T=T, guidance=args.guidance, n_steps=None if world == 1 else 20)
             if batch1 is not None:
                 batch1["cpu_ms_per_denoise_step"] = cpu_b1["ms_per_denoise_step"]
 
@@ -685,7 +721,9 @@ def run_native(args):
 
 def main():
     args = parse_args()
-    if args.impl == "reference":
+    if args.cpu_leg:
+        run_cpu_leg(args.cpu_leg)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_native(args)

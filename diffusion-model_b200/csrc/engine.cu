@@ -248,9 +248,12 @@ struct Plan {
   Act<T> feat;            // sa6 output
   cudaGraphExec_t exec_one = nullptr;
   cudaGraphExec_t exec_chunk = nullptr;
+  cudaGraphExec_t exec_eager = nullptr;   // one eager CFG step (dmb_denoise_cond_step) as a graph
   int chunk = 0;
   int launches_per_step = 0;
+  int launches_eager = 0;
   ~Plan() {
+    if (exec_eager) cudaGraphExecDestroy(exec_eager);
     if (exec_one) cudaGraphExecDestroy(exec_one);
     if (exec_chunk) cudaGraphExecDestroy(exec_chunk);
   }
@@ -325,6 +328,7 @@ class Engine : public IEngine {
     const char* env = getenv("DMB200_CUDA_CORE_ATTENTION");
     use_tc_attention_ = !(env && env[0] == '1');
     if (const char* e = getenv("DMB200_ATTN_MMA")) use_mma_attention_ = e[0] != '0';    // 0: the tcgen05 kernel
+    if (const char* e = getenv("DMB200_EAGER_GRAPH")) eager_graph_ = e[0] != '0';
     if (const char* e = getenv("DMB200_ATTN_POLY")) attn_poly_ = e[0] != '0';           // 0: every exp2 on MUFU
     if constexpr (std::is_same<T, __nv_bfloat16>::value) {
       const int am_smem = 110 * 1024;
@@ -465,6 +469,7 @@ class Engine : public IEngine {
   long long* stat_arena_cur_ = nullptr;   // bump cursor into the statistics arena of the plan being built
   size_t stat_arena_left_ = 0;
   bool use_tc_attention_ = true;
+  bool eager_graph_ = true;         // DMB200_EAGER_GRAPH=0: dmb_denoise_cond_step launches its kernels one by one
   bool use_mma_attention_ = true;   // warp-level MMA attention (attention_mma.cuh) for maps > 3x3 in bf16 mode
   int attn_var_ = 1;                // experiment bits of attention_mma_kernel (DMB200_ATTN_VAR)
   bool attn_poly_ = false;          // DMB200_ATTN_POLY=1: a quarter of its exponentials on the FMA pipe (measured slower: issue-bound)
@@ -1347,6 +1352,38 @@ void Engine<T>::cfg_step(const float* x_in, const long long* t, const long long*
   sp.sample_offset = sample_offset; sp.eps_out = eps_out; sp.x_dump = nullptr; sp.dump_step_stride = 0;
   sp.w_out = f("out.weight"); sp.b_out = f("out.bias");
   DMB_CUDA(cudaMemcpyAsync(&p.dyn->step, &sp, sizeof(sp), cudaMemcpyHostToDevice, s));
+  // One eager step = ~100 launches; generate_steps.py calls this once per timestep from Python
+  // (generate_steps.py:180-189), so outside the per-kernel timing mode the step runs as ONE graph
+  // launch (same kernels, same order: everything that varies is read from device memory).
+  if (!timing_ && eager_graph_) {
+    if (!p.exec_eager) {
+      cudaStream_t cs;
+      DMB_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+      cudaGraph_t graph = nullptr;
+      const long long before = launches_;
+      try {
+        DMB_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+        run_ops(p, cs);
+        launch(cfg_step_kernel<T>, dim3(cdiv(kLatH * kLatW, 128), B), 128, 0, cs, p.feat.p, p.feat.g, B, &p.dyn->step);
+        DMB_CHECK_LAUNCH();
+        count();
+        DMB_CUDA(cudaStreamEndCapture(cs, &graph));
+        DMB_CUDA(cudaGraphInstantiate(&p.exec_eager, graph, 0));
+      } catch (...) {
+        launches_ = before;
+        if (graph) cudaGraphDestroy(graph);
+        cudaStreamDestroy(cs);
+        throw;
+      }
+      p.launches_eager = static_cast<int>(launches_ - before);
+      launches_ = before;
+      cudaGraphDestroy(graph);
+      cudaStreamDestroy(cs);
+    }
+    DMB_CUDA(cudaGraphLaunch(p.exec_eager, s));
+    launches_ += p.launches_eager;
+    return;
+  }
   run_ops(p, s);
   OpList tail;
   tail.tag("cfg_step (out conv + CFG + DDPM)", 0, static_cast<double>(B) * kLatH * kLatW * (2 * 64 * sizeof(T) + 4 * 4 * 3));

@@ -98,11 +98,25 @@ class UnetCond(nn.Module):
         ctx.ensure_unet(self)
         return ctx
 
+    # ---- weight-change tracking for the native copy (dmb200.native.Context._params)
+    _native_epoch = 0
+
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        self._native_epoch += 1
+        return out
+
+    def load_state_dict(self, *args, **kwargs):
+        out = super().load_state_dict(*args, **kwargs)
+        self._native_epoch += 1
+        return out
+
     def refresh_native(self):
         """Rebuild the repacked device copy of the weights at the next call.  load_state_dict,
         Utils.loadModel and .to() are detected automatically; call this after writing parameters
         through `.data` (no version counter moves)."""
         from dmb200.native import invalidate_module
+        self._native_epoch += 1
         invalidate_module(self)
 
     def _run(self, x, t, y, cond_vals, cond_mask, want_geom):

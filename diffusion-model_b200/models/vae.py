@@ -55,9 +55,23 @@ class VAE(nn.Module):
         ctx.ensure_vae(self)
         return ctx
 
+    # ---- weight-change tracking for the native copy (dmb200.native.Context._params)
+    _native_epoch = 0
+
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        self._native_epoch += 1
+        return out
+
+    def load_state_dict(self, *args, **kwargs):
+        out = super().load_state_dict(*args, **kwargs)
+        self._native_epoch += 1
+        return out
+
     def refresh_native(self):
         """Rebuild the device copy of the weights at the next call (see UnetCond.refresh_native)."""
         from dmb200.native import invalidate_module
+        self._native_epoch += 1
         invalidate_module(self)
 
     def decode(self, z):
