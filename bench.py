@@ -606,14 +606,14 @@ def run_native(args):
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
             tj = json.load(f)
         h = hashlib.sha256()
-        for fn in ("gemm_tc.cuh", "engine.cu"):
-            with open(os.path.join(PRODUCT, "csrc", fn), "rb") as f:
-                h.update(f.read())
-        if tj.get("source_sha16") == h.hexdigest()[:16]:
+        with open(os.path.join(PRODUCT, "csrc", "gemm_tc.cuh"), "rb") as f:   # the kernel's source
+            h.update(f.read())
+        # ... and the same launch schedule (tile selection lives in engine.cu): the GEMM launch count of a step
+        if tj.get("source_sha16") == h.hexdigest()[:16] and tj.get("launches_per_step") == g_n // reps:
             traffic = tj.get("gemm_tc_kernel_dram_bytes_per_launch")
             traffic_note = tj.get("note", "")
         else:
-            traffic_note = "profiles/roofline_traffic.json was captured on another build (source hash differs): null"
+            traffic_note = "profiles/roofline_traffic.json was captured on another build (kernel source hash or launch count differs): null"
     except Exception:
         pass
     groups = {}

@@ -57,6 +57,21 @@ __device__ __forceinline__ float am_ex2_poly(float x) {
   return __uint_as_float(__float_as_uint(p) + (__float_as_uint(t) << 23));
 }
 
+// the same for two scores at once on packed fp32x2 instructions (FADD2 / FFMA2, sm_100): 5 issue
+// slots per score instead of 8
+__device__ __forceinline__ float2 am_ex2_poly2(float2 x) {
+  x.x = fmaxf(x.x, -120.0f); x.y = fmaxf(x.y, -120.0f);
+  const float2 magic = make_float2(12582912.0f, 12582912.0f);
+  const float2 t = __fadd2_rn(x, magic);
+  const float2 r = __fadd2_rn(t, make_float2(-12582912.0f, -12582912.0f));
+  const float2 f = __ffma2_rn(r, make_float2(-1.0f, -1.0f), x);
+  float2 p = __ffma2_rn(f, make_float2(0.05517145f, 0.05517145f), make_float2(0.24261062f, 0.24261062f));
+  p = __ffma2_rn(p, f, make_float2(0.69326097f, 0.69326097f));
+  p = __ffma2_rn(p, f, make_float2(0.9999281f, 0.9999281f));
+  return make_float2(__uint_as_float(__float_as_uint(p.x) + (__float_as_uint(t.x) << 23)),
+                     __uint_as_float(__float_as_uint(p.y) + (__float_as_uint(t.y) << 23)));
+}
+
 inline size_t attention_mma_smem_bytes(int L, int D) {
   const int lpad = (L + kAmKeys - 1) / kAmKeys * kAmKeys;
   return 2ull * lpad * D * 2 + 16;
@@ -75,14 +90,15 @@ __device__ __forceinline__ uint32_t am_off(int r, int c) {
 // kVar (experiment bits): 1 = raise the running maximum only when a step exceeds it by more than 2^8
 // (P <= 2^8 stays exact in bf16 / fp32; the rescale of O and its two MUFU then almost never run);
 // 2 = row sum by FADD of the fp32 exponentials instead of an all-ones MMA tile, with the truncation
-// of P de-biased (see kDebias).
+// of P de-biased (see kDebias); 4 = packed fp32x2 arithmetic for the exponent (and for the FMA-pipe
+// exp2 when kPolyMask >= 0).
 template <int D, int kPolyMask, int kVar>
 __global__ void __launch_bounds__(kAmMaxWarps * 32, (D == 16) ? 3 : 2)
 attention_mma_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_bfloat16* __restrict__ out,
                      int tiles_per_cta) {
   extern __shared__ uint8_t am_smem_raw[];
   constexpr int CPR = D / 8;      // 16-byte chunks per key row
-  constexpr bool kLazy = (kVar & 1) != 0, kFaddSum = (kVar & 2) != 0;
+  constexpr bool kLazy = (kVar & 1) != 0, kFaddSum = (kVar & 2) != 0, kPacked = (kVar & 4) != 0;
   constexpr int NO = D / 8 + (kFaddSum ? 0 : 1);   // output n-tiles: D / 8 of V (+ the all-ones tile = row sum)
   // kFaddSum: P is truncated to bf16, which loses 2^-9 of its value on average.  The exponent gets
   // log2(1 + 2^-9) added (folded into the per-row constant, free), so the truncated P is an unbiased
@@ -237,11 +253,28 @@ attention_mma_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_b
       for (int kk = 0; kk < 4; ++kk) {   // 16 keys per K step
         if (!kTail || kk < ng) {
           float e[8];
+          if constexpr (kPacked) {
+            // two scores per FFMA2 (the accumulator pairs of a row sit in adjacent registers); with
+            // kPolyMask >= 0 the pair kPolyMask of each group of four takes the packed FMA-pipe exp2
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int n = 2 * kk + (i >> 2), q = i & 3;
-            const float x = fmaf(s[n][q], c2, (q < 2) ? cA : cB);
-            e[i] = (kPolyMask >= 0 && ((kk * 8 + i) & 3) == kPolyMask) ? am_ex2_poly(x) : ex2_approx(x);
+            for (int pr = 0; pr < 4; ++pr) {
+              const int n = 2 * kk + (pr >> 1), q = (pr & 1) * 2;
+              const float cc = (pr & 1) ? cB : cA;
+              const float2 x = __ffma2_rn(make_float2(s[n][q], s[n][q + 1]), make_float2(c2, c2), make_float2(cc, cc));
+              if (kPolyMask >= 0 && pr == (kPolyMask & 3)) {
+                const float2 r = am_ex2_poly2(x);
+                e[2 * pr] = r.x; e[2 * pr + 1] = r.y;
+              } else {
+                e[2 * pr] = ex2_approx(x.x); e[2 * pr + 1] = ex2_approx(x.y);
+              }
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int n = 2 * kk + (i >> 2), q = i & 3;
+              const float x = fmaf(s[n][q], c2, (q < 2) ? cA : cB);
+              e[i] = (kPolyMask >= 0 && ((kk * 8 + i) & 3) == kPolyMask) ? am_ex2_poly(x) : ex2_approx(x);
+            }
           }
           if (kFaddSum) { rsA += (e[0] + e[1]) + (e[4] + e[5]); rsB += (e[2] + e[3]) + (e[6] + e[7]); }
           uint32_t pa[4];

@@ -332,11 +332,11 @@ class Engine : public IEngine {
     if (const char* e = getenv("DMB200_ATTN_POLY")) attn_poly_ = e[0] != '0';           // 0: every exp2 on MUFU
     if constexpr (std::is_same<T, __nv_bfloat16>::value) {
       const int am_smem = 110 * 1024;
-      if (const char* e = getenv("DMB200_ATTN_VAR")) attn_var_ = atoi(e) & 3;
+      if (const char* e = getenv("DMB200_ATTN_VAR")) attn_var_ = atoi(e) & 7;
 #define DMB_AM_ATTR(D, P, V) DMB_CUDA(cudaFuncSetAttribute(attention_mma_kernel<D, P, V>, cudaFuncAttributeMaxDynamicSharedMemorySize, am_smem))
-      DMB_AM_ATTR(16, -1, 0); DMB_AM_ATTR(16, -1, 1); DMB_AM_ATTR(16, -1, 2); DMB_AM_ATTR(16, -1, 3); DMB_AM_ATTR(16, 3, 3);
-      DMB_AM_ATTR(32, -1, 0); DMB_AM_ATTR(32, -1, 1); DMB_AM_ATTR(32, -1, 2); DMB_AM_ATTR(32, -1, 3); DMB_AM_ATTR(32, 3, 3);
-      DMB_AM_ATTR(64, -1, 0); DMB_AM_ATTR(64, -1, 1); DMB_AM_ATTR(64, -1, 2); DMB_AM_ATTR(64, -1, 3); DMB_AM_ATTR(64, 3, 3);
+      DMB_AM_ATTR(16, -1, 0); DMB_AM_ATTR(16, -1, 1); DMB_AM_ATTR(16, -1, 5); DMB_AM_ATTR(16, 3, 5); DMB_AM_ATTR(16, 3, 1);
+      DMB_AM_ATTR(32, -1, 0); DMB_AM_ATTR(32, -1, 1); DMB_AM_ATTR(32, -1, 5); DMB_AM_ATTR(32, 3, 5); DMB_AM_ATTR(32, 3, 1);
+      DMB_AM_ATTR(64, -1, 0); DMB_AM_ATTR(64, -1, 1); DMB_AM_ATTR(64, -1, 5); DMB_AM_ATTR(64, 3, 5); DMB_AM_ATTR(64, 3, 1);
 #undef DMB_AM_ATTR
     }
   }
@@ -1111,11 +1111,11 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     else if (D == 32) launch(attention_mma_kernel<32, P, V>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p, tpc);  \
     else launch(attention_mma_kernel<64, P, V>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p, tpc);               \
   } while (0)
-          if (attn_poly_) DMB_AM_LAUNCH(3, 3);
+          if (attn_poly_ && attn_var_ == 5) DMB_AM_LAUNCH(3, 5);
+          else if (attn_poly_) DMB_AM_LAUNCH(3, 1);
           else if (attn_var_ == 0) DMB_AM_LAUNCH(-1, 0);
-          else if (attn_var_ == 1) DMB_AM_LAUNCH(-1, 1);
-          else if (attn_var_ == 2) DMB_AM_LAUNCH(-1, 2);
-          else DMB_AM_LAUNCH(-1, 3);
+          else if (attn_var_ == 5) DMB_AM_LAUNCH(-1, 5);
+          else DMB_AM_LAUNCH(-1, 1);
 #undef DMB_AM_LAUNCH
           DMB_CHECK_LAUNCH();
           count();
