@@ -426,16 +426,30 @@ gn1_apply_kernel(const T* __restrict__ raw, const long long* __restrict__ sample
       if (ok[u]) {
         float xv[8];
         xr[u].unpack(xv);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) xv[i] = fmaf(xv[i], sc[i], sh[i]);
-        if (MODE == GN_GELU) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>(xv[i]);
-        } else if (MODE == GN_RES_GELU) {
+        if constexpr (sizeof(T) == 2 && (MODE == GN_GELU || MODE == GN_RES_GELU)) {
+          // bf16 mode: affine, residual add and GELU on packed fp32x2 instructions (same operations,
+          // same order, same bits as the scalar form below)
           float rv[8];
-          rs[u].unpack(rv);
+          if (MODE == GN_RES_GELU) rs[u].unpack(rv);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>(rv[i] + xv[i]);
+          for (int i = 0; i < 8; i += 2) {
+            float2 v = __ffma2_rn(make_float2(xv[i], xv[i + 1]), make_float2(sc[i], sc[i + 1]), make_float2(sh[i], sh[i + 1]));
+            if (MODE == GN_RES_GELU) v = __fadd2_rn(make_float2(rv[i], rv[i + 1]), v);
+            v = gelu_fast2(v);
+            xv[i] = v.x; xv[i + 1] = v.y;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) xv[i] = fmaf(xv[i], sc[i], sh[i]);
+          if (MODE == GN_GELU) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>(xv[i]);
+          } else if (MODE == GN_RES_GELU) {
+            float rv[8];
+            rs[u].unpack(rv);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xv[i] = gelu_for<T>(rv[i] + xv[i]);
+          }
         }
         if constexpr (kLN) {
           // (the lanes of a row take this branch together: ok[u] depends on the row only)
