@@ -333,7 +333,10 @@ gn1_apply_kernel(const T* __restrict__ raw, const long long* __restrict__ sample
   // `raw` holds n_src samples; output sample b reads raw sample b mod n_src (n_src < gridDim.y
   // only where the classifier-free-guidance pair still shares its activations, see
   // build_unet_plan).
-  const int b = blockIdx.y;
+  // Samples are walked from the LAST to the first: the producing conv wrote its tiles in ascending
+  // row order, so the highest samples are the ones still in the 126 MB L2; this pass leaves the
+  // lowest samples most recently written, which is where the next conv (ascending) starts.
+  const int b = gridDim.y - 1 - blockIdx.y;
   const int b_src = b >= n_src ? b - n_src : b;
   const int tid = threadIdx.x;
   const int vpr = C >> 3;                  // vectors per row: 8, 16, 32 or 64
