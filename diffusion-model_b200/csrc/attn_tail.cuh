@@ -303,4 +303,265 @@ attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_const
   }
 }
 
+// ---------------------------------------------------------------------------
+// The same tail for C = 256 (sa2 on 7x7 maps, sa3 on 3x3 maps): the three weight matrices (3 x 128
+// KB) do not fit next to a tile, so ONE matrix is resident at a time.  Its four 32 KB K chunks are
+// loaded by TMA as soon as the previous GEMM's MMAs have retired, i.e. they land while the epilogue
+// between two GEMMs runs; o (the residual of the block) stays in registers as packed bf16 and x_ln
+// is read straight from global memory, so shared memory holds only the A tile (64 KB) and the
+// current weight (128 KB).  One chain per CTA: eight warpgroups share the 256 columns of a 128-row
+// tile (32 columns per thread).  Replaces three Linear launches and one LayerNorm launch per block
+// (sa2: 62 + 15 us, sa3: 37 + 15 us at batch 256; four ~5 us launches each at batch 1).
+// ---------------------------------------------------------------------------
+constexpr int kTail256Threads = 1024;
+constexpr int attn_tail256_smem_bytes() { return 4 * 128 * 128 + 4 * 256 * 128 + 1024; }
+
+__global__ void __launch_bounds__(kTail256Threads, 1)
+attn_tail256_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_constant__ CUtensorMap tmap_wp,
+                    const __grid_constant__ CUtensorMap tmap_w1, const __grid_constant__ CUtensorMap tmap_w2,
+                    const __grid_constant__ CUtensorMap tmap_out, const __nv_bfloat16* __restrict__ xl,
+                    const TailParams p) {
+  constexpr int C = 256, kSplit = 8, kKC = 4;
+  constexpr uint32_t kChunkBytes = 128 * 128;   // one 128-row x 128-byte sub-tile of A
+  constexpr uint32_t kWChunkBytes = C * 128;    // one K chunk of a weight: 256 rows x 128 bytes
+  constexpr uint32_t kTmemCols = 256;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t w_bar;
+  __shared__ __align__(8) uint64_t ld_bar;
+  __shared__ __align__(8) uint64_t mma_bar;
+  __shared__ uint32_t tmem_base_smem;
+
+  pdl_trigger();
+  const int warp = threadIdx.x >> 5;
+  const int split = warp >> 2;                  // which 32 columns of the row this thread owns
+  const int q = warp & 3;                       // TMEM lane quadrant of this warp
+  const bool lead = warp == 0;                  // issues every TMA and MMA
+  const int t = q * 32 + (threadIdx.x & 31);    // row of the tile
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  uint8_t* bufA = smem;                          // [4][128 rows][128 B]: av -> h -> f1 -> out
+  uint8_t* wsm = smem + kKC * kChunkBytes;       // [4][256 rows][128 B]: the current weight
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmap_av); tma_prefetch_desc(&tmap_out);
+    tma_prefetch_desc(&tmap_wp); tma_prefetch_desc(&tmap_w1); tma_prefetch_desc(&tmap_w2);
+    mbar_init(&w_bar, 1); mbar_init(&ld_bar, 1); mbar_init(&mma_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(&tmem_base_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t d_tmem = tmem_base_smem;
+  pdl_wait();
+
+  const uint32_t idesc = umma_idesc(1u, 128, C);
+  const int col0 = split * kTailCols;
+  const uint32_t t_row = d_tmem + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(col0);
+  const uint32_t a_addr = smem_u32(bufA), w_addr = smem_u32(wsm);
+  const int sw = t & 7;
+  const uint32_t row_off = (col0 >> 6) * kChunkBytes + t * 128;
+  const int j0 = (col0 & 63) >> 3;
+  uint8_t* rowA = bufA + row_off;
+  float2* scratch = reinterpret_cast<float2*>(bufA);
+  uint32_t ph_ld = 0, ph_mma = 0, ph_w = 0;
+
+  auto load_w = [&](const CUtensorMap* tm) {   // all four K chunks of one weight matrix
+    if (lead) {
+      if (elect_one()) {
+        mbar_expect_tx(&w_bar, kKC * kWChunkBytes);
+#pragma unroll
+        for (int kc = 0; kc < kKC; ++kc) tma_load_2d(wsm + kc * kWChunkBytes, tm, &w_bar, kc * 64, 0);
+      }
+      __syncwarp();
+    }
+  };
+  auto issue_gemm = [&]() {   // D = A(bufA) * W(current)^T
+    if (lead) {
+      mbar_wait(&w_bar, ph_w);
+      tc_fence_after();
+      if (elect_one()) {
+#pragma unroll
+        for (int kc = 0; kc < kKC; ++kc) {
+          const uint64_t ad = umma_desc_sw128(a_addr + kc * kChunkBytes);
+          const uint64_t bd = umma_desc_sw128(w_addr + kc * kWChunkBytes);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_ss<false>(d_tmem, ad + (k * 2), bd + (k * 2), idesc, (kc > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&mma_bar);
+      }
+      __syncwarp();
+    }
+    ph_w ^= 1;
+  };
+  auto wait_gemm = [&]() {
+    mbar_wait(&mma_bar, ph_mma);
+    ph_mma ^= 1;
+    tc_fence_after();
+  };
+  auto load_vec8 = [&](const float* src, float* dst) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(src + 4));
+    dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; dst[3] = a.w; dst[4] = b.x; dst[5] = b.y; dst[6] = b.z; dst[7] = b.w;
+  };
+
+  if (static_cast<int>(blockIdx.x) < p.m_tiles) load_w(&tmap_wp);
+  for (int tile = blockIdx.x; tile < p.m_tiles; tile += gridDim.x) {
+    const int m0 = tile * 128;
+    int b = 0, y = 0, x = 0;
+    const bool valid = geo_decode(p.geo, m0 + t, b, y, x);
+    if (lead) {
+      if (elect_one()) {
+        tma_store_wait_read<0>();   // the previous tile's store has read bufA
+        mbar_expect_tx(&ld_bar, kKC * kChunkBytes);
+#pragma unroll
+        for (int kc = 0; kc < kKC; ++kc) tma_load_2d(bufA + kc * kChunkBytes, &tmap_av, &ld_bar, kc * 64, m0);
+      }
+      __syncwarp();
+    }
+    // this thread's 32 columns of x_ln (the residual of the block), straight from global memory
+    uint4 xr[4];
+    {
+      const uint4* xp = reinterpret_cast<const uint4*>(xl + static_cast<size_t>(m0 + t) * C + col0);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) xr[j] = __ldg(xp + j);
+    }
+    mbar_wait(&ld_bar, ph_ld);
+    ph_ld ^= 1;
+    issue_gemm();
+    wait_gemm();
+    load_w(&tmap_w1);
+
+    // ---- o = acc + bp + x_ln (kept in registers as packed bf16); h = LayerNorm(o) -> A
+    uint32_t ob[16];
+    {
+      float s = 0.f, ss = 0.f;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {   // 16 accumulator columns at a time: 64 registers per thread
+        float o[16];
+        tmem_ld16(t_row + 16 * half, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          const int j = 2 * half + jj;
+          const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&xr[j]);
+          float bv[8];
+          load_vec8(p.bp + col0 + 8 * j, bv);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 xv = __bfloat1622float2(hp[i]);
+            const __nv_bfloat162 o2 = __floats2bfloat162_rn(o[8 * jj + 2 * i] + bv[2 * i] + xv.x,
+                                                            o[8 * jj + 2 * i + 1] + bv[2 * i + 1] + xv.y);
+            ob[4 * j + i] = *reinterpret_cast<const uint32_t*>(&o2);
+            const float2 of = __bfloat1622float2(o2);   // LayerNorm sees the rounded o, as it would from HBM
+            s += of.x + of.y;
+            ss = fmaf(of.x, of.x, fmaf(of.y, of.y, ss));
+          }
+        }
+      }
+      scratch[split * 128 + t] = make_float2(s, ss);   // (GEMM 0 has retired: bufA is idle)
+      named_bar_sync(1, kTail256Threads);
+      float ts = 0.f, tss = 0.f;
+#pragma unroll
+      for (int g = 0; g < kSplit; ++g) {   // the same order in every thread of the row
+        const float2 v = scratch[g * 128 + t];
+        ts += v.x; tss += v.y;
+      }
+      const float mean = ts * (1.0f / C);
+      const float rstd = rsqrtf(fmaxf(tss * (1.0f / C) - mean * mean, 0.f) + 1e-5f);
+      named_bar_sync(1, kTail256Threads);   // the partials are read: A may be overwritten
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float wv[8], bv[8];
+        load_vec8(p.ln_w + col0 + 8 * j, wv);
+        load_vec8(p.ln_b + col0 + 8 * j, bv);
+        uint4 w4;
+        __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 of = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ob[4 * j + i]));
+          wp[i] = __floats2bfloat162_rn((of.x - mean) * rstd * wv[2 * i] + bv[2 * i],
+                                        (of.y - mean) * rstd * wv[2 * i + 1] + bv[2 * i + 1]);
+        }
+        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
+      }
+    }
+    fence_async_proxy();
+    tc_fence_before();
+    named_bar_sync(1, kTail256Threads);
+    issue_gemm();
+    wait_gemm();
+    load_w(&tmap_w2);
+
+    // ---- f1 = GELU(acc + b1) -> A
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      float v[16];
+      tmem_ld16(t_row + 16 * half, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj) {
+        const int j = 2 * half + jj;
+        float bv[8];
+        load_vec8(p.b1 + col0 + 8 * j, bv);
+        uint4 w4;
+        __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          wp[i] = __floats2bfloat162_rn(gelu_fast(v[8 * jj + 2 * i] + bv[2 * i]), gelu_fast(v[8 * jj + 2 * i + 1] + bv[2 * i + 1]));
+        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
+      }
+    }
+    fence_async_proxy();
+    tc_fence_before();
+    named_bar_sync(1, kTail256Threads);
+    issue_gemm();
+    wait_gemm();
+    if (tile + static_cast<int>(gridDim.x) < p.m_tiles) load_w(&tmap_wp);   // the next tile's first weight
+
+    // ---- out = acc + b2 + o -> A -> TMA store (pad pixels are stored as zeros)
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      float v[16];
+      tmem_ld16(t_row + 16 * half, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int jj = 0; jj < 2; ++jj) {
+        const int j = 2 * half + jj;
+        uint4 w4 = make_uint4(0u, 0u, 0u, 0u);
+        if (valid) {
+          float bv[8];
+          load_vec8(p.b2 + col0 + 8 * j, bv);
+          __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 of = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ob[4 * j + i]));
+            wp[i] = __floats2bfloat162_rn(v[8 * jj + 2 * i] + bv[2 * i] + of.x, v[8 * jj + 2 * i + 1] + bv[2 * i + 1] + of.y);
+          }
+        }
+        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
+      }
+    }
+    fence_async_proxy();
+    tc_fence_before();
+    named_bar_sync(1, kTail256Threads);
+    if (lead) {
+      if (elect_one()) {
+#pragma unroll
+        for (int kc = 0; kc < kKC; ++kc) tma_store_2d(&tmap_out, bufA + kc * kChunkBytes, kc * 64, m0);
+        tma_store_commit();
+      }
+      __syncwarp();
+    }
+  }
+  if (lead) tma_store_wait_all<0>();
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(d_tmem, kTmemCols);
+  }
+}
+
 }  // namespace dmb

@@ -312,6 +312,7 @@ class Engine : public IEngine {
       DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
       DMB_CUDA(cudaFuncSetAttribute(attention_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+      DMB_CUDA(cudaFuncSetAttribute(attn_tail256_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail256_smem_bytes()));
       DMB_CUDA(cudaFuncSetAttribute(attn_tail_kernel<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail_smem_bytes<64, 4>()));
       DMB_CUDA(cudaFuncSetAttribute(attn_tail_kernel<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail_smem_bytes<128, 2>()));
     }
@@ -329,6 +330,7 @@ class Engine : public IEngine {
     use_tc_attention_ = !(env && env[0] == '1');
     if (const char* e = getenv("DMB200_ATTN_MMA")) use_mma_attention_ = e[0] != '0';    // 0: the tcgen05 kernel
     if (const char* e = getenv("DMB200_EAGER_GRAPH")) eager_graph_ = e[0] != '0';
+    if (const char* e = getenv("DMB200_TAIL256")) use_tail256_ = e[0] != '0';
     if (const char* e = getenv("DMB200_ATTN_POLY")) attn_poly_ = e[0] != '0';           // 0: every exp2 on MUFU
     if constexpr (std::is_same<T, __nv_bfloat16>::value) {
       const int am_smem = 110 * 1024;
@@ -469,6 +471,7 @@ class Engine : public IEngine {
   long long* stat_arena_cur_ = nullptr;   // bump cursor into the statistics arena of the plan being built
   size_t stat_arena_left_ = 0;
   bool use_tc_attention_ = true;
+  bool use_tail256_ = true;         // DMB200_TAIL256=0: the C = 256 attention blocks keep their separate Linear / LayerNorm launches
   bool eager_graph_ = true;         // DMB200_EAGER_GRAPH=0: dmb_denoise_cond_step launches its kernels one by one
   bool use_mma_attention_ = true;   // warp-level MMA attention (attention_mma.cuh) for maps > 3x3 in bf16 mode
   int attn_var_ = 1;                // experiment bits of attention_mma_kernel (DMB200_ATTN_VAR)
@@ -1149,6 +1152,27 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       count();
     });
     if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+      if (use_fused_tail_ && use_tail256_ && C == 256) {
+        // the same chain with one weight matrix resident at a time (attn_tail256_kernel)
+        Act<T> out = new_act(pool, nn, H, W, C, false);
+        const GemmW<T>&wp = gw_.at(p + ".proj"), &w1 = gw_.at(p + ".ff1"), &w2 = gw_.at(p + ".ff2");
+        TailParams tp{};
+        tp.geo = av.g;
+        tp.m_tiles = cdiv(av.g.rows_valid, kTileM);
+        tp.bp = wp.bias; tp.b1 = w1.bias; tp.b2 = w2.bias;
+        tp.ln_w = f(p + ".ff_self.0.weight");
+        tp.ln_b = f(p + ".ff_self.0.bias");
+        DMB_REQUIRE(tp.bp && tp.b1 && tp.b2, "attention-block linears carry biases");
+        ops.tag("attn_tail 256 @" + std::to_string(H), 6.0 * tok * C * C, 3.0 * tok * C * sizeof(T));
+        ops.push_back([this, av, xl, out, wp, w1, w2, tp](cudaStream_t s) {
+          const int grid = std::min(tp.m_tiles, num_sms_);
+          launch(attn_tail256_kernel, grid, kTail256Threads, attn_tail256_smem_bytes(), s, av.tmap, wp.tmap_for(256),
+                 w1.tmap_for(256), w2.tmap_for(256), out.tmap, reinterpret_cast<const __nv_bfloat16*>(xl.p), tp);
+          DMB_CHECK_LAUNCH();
+          count();
+        });
+        return out;
+      }
       if (use_fused_tail_ && (C == 64 || C == 128)) {
         // out_proj + residual, LayerNorm, ff1 + GELU, ff2 + residual on chip (attn_tail.cuh)
         Act<T> out = new_act(pool, nn, H, W, C, false);

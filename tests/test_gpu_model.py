@@ -300,7 +300,7 @@ def test_strided_ddim_extension_matches_oracle(models):
 
 
 @pytest.mark.parametrize("switch", ["DMB200_FUSED_TAIL", "DMB200_ROW3", "DMB200_FUSE_LN1", "DMB200_ATTN_MMA",
-                                    "DMB200_ATTN_POLY"])
+                                    "DMB200_ATTN_POLY", "DMB200_TAIL256"])
 def test_fused_kernels_agree_with_separate_launches(models, switch):
     """The fused attention-block tail (attn_tail_kernel) and the kernel-row A windows of the 3x3
     convs (kRow3) are re-schedulings of the same arithmetic: the U-Net output must agree with the
@@ -329,8 +329,10 @@ def test_fused_kernels_agree_with_separate_launches(models, switch):
             ctx.close()
     r = rel_l2(outs[0], outs[1])
     report(f"variant_{switch}", {"rel_l2": r, "launches": launches})
-    if switch == "DMB200_FUSED_TAIL":   # the switch took effect: 4 fused blocks x 3 launches saved
-        assert launches[1] - launches[0] == 12, launches
+    if switch == "DMB200_FUSED_TAIL":   # the switch took effect: 6 fused blocks x 3 launches saved
+        assert launches[1] - launches[0] == 18, launches
+    if switch == "DMB200_TAIL256":      # sa2 and sa3: 3 Linear + 1 LayerNorm launches -> 1, twice
+        assert launches[1] - launches[0] == 6, launches
     if switch == "DMB200_FUSE_LN1":     # 6 LayerNorm launches saved; same arithmetic in the same order
         assert launches[1] - launches[0] == 6, launches
         assert r < 1e-6, r
