@@ -669,6 +669,39 @@ def run_native(args):
         if not args.no_extras:
             tf32 = tf32_block(args, dev, unet, T, y, vals, mask, coef, peaks)
 
+    # ---- extension N1: the strided deterministic schedule, 10 steps + decode, where the
+    # VAE decoder is no longer negligible (device-resident inputs, like `value`)
+    strided = None
+    if rank == 0 and not args.no_extras and T % 10 == 0:
+        coef10, stride10 = d.strided_coefficients(10)
+        def strided_pass(i):
+            x = ctx.philox_normal(B, seed=50 + i, sample_offset=0, t=0)
+            ctx.sample_loop(x, y, 0, vals, mask, args.guidance, coef10, T, 10, seed=60 + i, t_stride=stride10)
+            return ctx.vae_decode(x, want_f32=False, want_u8=True)[1]
+        for i in range(3):
+            strided_pass(i)
+        torch.cuda.synchronize()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for i in range(10):
+            strided_pass(10 + i)
+        s1.record()
+        torch.cuda.synchronize()
+        ms10 = s0.elapsed_time(s1) / 10
+        z = ctx.philox_normal(B, seed=1, sample_offset=0, t=0)
+        ctx.vae_decode(z, want_f32=False, want_u8=True)
+        torch.cuda.synchronize()
+        s0.record()
+        for _ in range(5):
+            ctx.vae_decode(z, want_f32=False, want_u8=True)
+        s1.record()
+        torch.cuda.synchronize()
+        dec_ms = s0.elapsed_time(s1) / 5
+        strided = {"sample_steps": 10, "batch": B, "ms_per_batch": ms10, "samples_per_s": B / (ms10 * 1e-3),
+                   "vae_decode_ms_per_batch": dec_ms, "decode_share": dec_ms / ms10,
+                   "note": "dmb_sample_loop_strided (DDIM eta = 0, 10 of 1000 timesteps) + VAE decode to u8; "
+                           "an opt-in extension, not the reference's schedule"}
+
     config4 = None
     if args.config4_batch > 0:
         config4 = run_config4(args, ctx, dev, world, rank, T, coef, barrier)
@@ -711,6 +744,7 @@ def run_native(args):
             "batch1": batch1,
             "parity": parity,
             "tf32": tf32,
+            "strided10": strided,
             "config4": config4,
         }
         print(json.dumps(line), flush=True)

@@ -1252,7 +1252,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.tag("conv_in 4->64 @28", 2.0 * n0 * kLatH * kLatW * 36.0 * 64);
     ops.push_back([this, r0, w0, pp, B](cudaStream_t s) {
       if constexpr (std::is_same<T, __nv_bfloat16>::value)
-        launch(conv_in_mma_kernel, dim3(r0.g.n, 1), kConvInThreads, 0, s, pp->x_state, B, w0, nullptr, 1.0f, r0.g, 64,
+        launch(conv_in_mma_kernel, dim3(r0.g.n, 1, r0.g.n >= 64 ? 1 : 7), kConvInThreads, 0, s, pp->x_state, B, w0, nullptr, 1.0f, r0.g, 64,
                                                                       r0.p, r0.sstat);
       else
         conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), r0.g.n, 1), 128, 0, s>>>(pp->x_state, B, w0, nullptr, 1.0f,

@@ -262,7 +262,9 @@ conv_in_mma_kernel(const float* __restrict__ x, int B_src, const float* __restri
 
   constexpr int NPIX = kLatH * kLatW;
   StatAcc sacc;   // this lane's share of the sample's GroupNorm statistics
-  for (int mt = warp; mt * 16 < NPIX; mt += kConvInThreads / 32) {
+  // gridDim.z CTAs share the 49 pixel tiles of a sample (small batches: one CTA per sample would be the
+  // whole latency of this launch)
+  for (int mt = warp + (kConvInThreads / 32) * blockIdx.z; mt * 16 < NPIX; mt += (kConvInThreads / 32) * gridDim.z) {
     const int p0 = mt * 16 + gq, p1 = p0 + 8;
     const bool v0 = p0 < NPIX, v1 = p1 < NPIX;
     const int y0 = v0 ? p0 / kLatW : 0, x0 = v0 ? p0 - y0 * kLatW : 0;
