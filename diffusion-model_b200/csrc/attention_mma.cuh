@@ -318,4 +318,157 @@ attention_mma_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_b
   }
 }
 
+// ---------------------------------------------------------------------------
+// The same kernel for the fp32-storage / TF32-operand mode (DMB200_PRECISION=tf32), where the
+// CUDA-core attention took 5.8 of the step's 10.4 ms: mma.sync.m16n8k8 with TF32 operands (the
+// tensor core reads the upper 19 bits of the fp32 words), fp32 accumulate, fp32 softmax.  K and V sit
+// in shared memory as fp32 rows of D + 4 words (the padding makes the per-lane fragment loads
+// conflict-free: lane (g, t) reads word key * (D + 4) + d with key = 8 n + g or 2 t).  For P V the
+// key order inside an 8-key step is permuted (A column t <-> key 2 t, column t + 4 <-> key 2 t + 1) so
+// that the score fragments ARE the A fragments; V rows are loaded in the matching order.  The row
+// sum again comes from the tensor core (B = ones) from exactly the truncated P that enters P V.
+// ---------------------------------------------------------------------------
+constexpr int kAfMaxWarps = 14;
+
+__device__ __forceinline__ void am_mma_tf32(float* d, const uint32_t* a, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+inline size_t attention_mma_f32_smem_bytes(int L, int D) {
+  const int lpad = (L + kAmKeys - 1) / kAmKeys * kAmKeys;
+  return 2ull * lpad * (D + 4) * 4 + 16;
+}
+
+template <int D>
+__global__ void __launch_bounds__(kAfMaxWarps * 32, 1)
+attention_mma_f32_kernel(const float* __restrict__ qkv, Geo g, int E, float* __restrict__ out, int tiles_per_cta) {
+  extern __shared__ uint8_t am_smem_raw[];
+  constexpr int LD = D + 4;       // words per key row in shared memory
+  constexpr int NO = D / 8 + 1;   // output n-tiles: D / 8 of V plus the all-ones tile (row sum)
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nw = blockDim.x >> 5;
+  const int L = g.H * g.W;
+  const int nch = (L + kAmKeys - 1) / kAmKeys;
+  const int lpad = nch * kAmKeys;
+  const int ntiles = (L + 15) >> 4;
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int ld = 3 * E;
+  const uint32_t sraw = smem_u32(am_smem_raw);
+  float* Ks = reinterpret_cast<float*>(am_smem_raw + ((16u - (sraw & 15u)) & 15u));
+  float* Vs = Ks + static_cast<size_t>(lpad) * LD;
+
+  // ---- stage K and V of the (sample, head): 16-byte loads
+  {
+    constexpr int VPK = D / 4;   // float4 per key
+    const int total = lpad * VPK;
+    for (int idx = tid; idx < total; idx += blockDim.x) {
+      const int key = idx / VPK, c = idx - key * VPK;
+      float4 kv = make_float4(0.f, 0.f, 0.f, 0.f), vv = kv;
+      if (key < L) {
+        const float* rp = qkv + static_cast<size_t>(geo_row_of_pixel(g, b, key)) * ld + h * D + 4 * c;
+        kv = *reinterpret_cast<const float4*>(rp + E);
+        vv = *reinterpret_cast<const float4*>(rp + 2 * E);
+      }
+      *reinterpret_cast<float4*>(Ks + key * LD + 4 * c) = kv;
+      *reinterpret_cast<float4*>(Vs + key * LD + 4 * c) = vv;
+    }
+  }
+  __syncthreads();
+
+  const float c2 = rsqrtf(static_cast<float>(D)) * 1.4426950408889634f;
+  const int gq = lane >> 2, tq = lane & 3;
+  const int tile_end = min(ntiles, (static_cast<int>(blockIdx.x) + 1) * tiles_per_cta);
+  const uint32_t one = __float_as_uint(1.0f);
+
+  for (int tile = blockIdx.x * tiles_per_cta + warp; tile < tile_end; tile += nw) {
+    const int rowA = tile * 16 + gq, rowB = rowA + 8;
+    const bool vA = rowA < L, vB = rowB < L;
+    const int prA = geo_row_of_pixel(g, b, vA ? rowA : 0), prB = geo_row_of_pixel(g, b, vB ? rowB : 0);
+    uint32_t qa[D / 8][4];
+    {
+      const float* qA = qkv + static_cast<size_t>(prA) * ld + h * D + tq;
+      const float* qB = qkv + static_cast<size_t>(prB) * ld + h * D + tq;
+#pragma unroll
+      for (int ks = 0; ks < D / 8; ++ks) {
+        qa[ks][0] = vA ? __float_as_uint(qA[ks * 8]) : 0u;
+        qa[ks][1] = vB ? __float_as_uint(qB[ks * 8]) : 0u;
+        qa[ks][2] = vA ? __float_as_uint(qA[ks * 8 + 4]) : 0u;
+        qa[ks][3] = vB ? __float_as_uint(qB[ks * 8 + 4]) : 0u;
+      }
+    }
+    float o[NO][4];
+#pragma unroll
+    for (int n = 0; n < NO; ++n) { o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f; }
+    float mA = -INFINITY, mB = -INFINITY;
+
+    for (int j = 0; j < nch; ++j) {
+      const int kb = j * kAmKeys;
+      const int ng = min(8, (L - kb + 7) >> 3);   // 8-key groups with at least one real key
+      float s[8][4];
+#pragma unroll
+      for (int n = 0; n < 8; ++n) {
+        s[n][0] = s[n][1] = s[n][2] = s[n][3] = -INFINITY;
+        if (n < ng) {
+          s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f;
+          const float* kp = Ks + (kb + n * 8 + gq) * LD + tq;
+#pragma unroll
+          for (int ks = 0; ks < D / 8; ++ks)
+            am_mma_tf32(s[n], qa[ks], __float_as_uint(kp[ks * 8]), __float_as_uint(kp[ks * 8 + 4]));
+        }
+      }
+      if (kb + kAmKeys > L) {
+#pragma unroll
+        for (int n = 0; n < 8; ++n) {
+          const int k0 = kb + n * 8 + 2 * tq;
+          if (k0 >= L) { s[n][0] = -INFINITY; s[n][2] = -INFINITY; }
+          if (k0 + 1 >= L) { s[n][1] = -INFINITY; s[n][3] = -INFINITY; }
+        }
+      }
+      float xA = fmaxf(s[0][0], s[0][1]), xB = fmaxf(s[0][2], s[0][3]);
+#pragma unroll
+      for (int n = 1; n < 8; ++n) {
+        xA = fmaxf(xA, fmaxf(s[n][0], s[n][1]));
+        xB = fmaxf(xB, fmaxf(s[n][2], s[n][3]));
+      }
+      xA = fmaxf(xA, __shfl_xor_sync(0xffffffffu, xA, 1));
+      xB = fmaxf(xB, __shfl_xor_sync(0xffffffffu, xB, 1));
+      xA = fmaxf(xA, __shfl_xor_sync(0xffffffffu, xA, 2));
+      xB = fmaxf(xB, __shfl_xor_sync(0xffffffffu, xB, 2));
+      const bool upA = (xA - mA) * c2 > 8.0f, upB = (xB - mB) * c2 > 8.0f;   // lazy maximum, as in the bf16 kernel
+      if (__any_sync(0xffffffffu, upA || upB)) {
+        const float nA = upA ? xA : mA, nB = upB ? xB : mB;
+        const float fA = ex2_approx((mA - nA) * c2), fB = ex2_approx((mB - nB) * c2);
+        mA = nA; mB = nB;
+#pragma unroll
+        for (int n = 0; n < NO; ++n) { o[n][0] *= fA; o[n][1] *= fA; o[n][2] *= fB; o[n][3] *= fB; }
+      }
+      const float cA = -mA * c2, cB = -mB * c2;
+#pragma unroll
+      for (int n = 0; n < 8; ++n) {   // one 8-key step per score n-tile
+        if (n < ng) {
+          uint32_t pa[4];   // A columns t / t + 4 <-> keys 2 t / 2 t + 1: the score fragment as it is
+          pa[0] = __float_as_uint(ex2_approx(fmaf(s[n][0], c2, cA)));
+          pa[2] = __float_as_uint(ex2_approx(fmaf(s[n][1], c2, cA)));
+          pa[1] = __float_as_uint(ex2_approx(fmaf(s[n][2], c2, cB)));
+          pa[3] = __float_as_uint(ex2_approx(fmaf(s[n][3], c2, cB)));
+          const float* vp = Vs + (kb + n * 8 + 2 * tq) * LD + gq;
+#pragma unroll
+          for (int nt = 0; nt < D / 8; ++nt)
+            am_mma_tf32(o[nt], pa, __float_as_uint(vp[nt * 8]), __float_as_uint(vp[LD + nt * 8]));
+          am_mma_tf32(o[NO - 1], pa, one, one);
+        }
+      }
+    }
+    const float iA = 1.0f / o[NO - 1][0], iB = 1.0f / o[NO - 1][2];
+    float* oA = out + static_cast<size_t>(prA) * E + h * D + 2 * tq;
+    float* oB = out + static_cast<size_t>(prB) * E + h * D + 2 * tq;
+#pragma unroll
+    for (int n = 0; n < D / 8; ++n) {
+      if (vA) *reinterpret_cast<float2*>(oA + n * 8) = make_float2(o[n][0] * iA, o[n][1] * iA);
+      if (vB) *reinterpret_cast<float2*>(oB + n * 8) = make_float2(o[n][2] * iB, o[n][3] * iB);
+    }
+  }
+}
+
 }  // namespace dmb

@@ -332,6 +332,11 @@ class Engine : public IEngine {
     if (const char* e = getenv("DMB200_EAGER_GRAPH")) eager_graph_ = e[0] != '0';
     if (const char* e = getenv("DMB200_TAIL256")) use_tail256_ = e[0] != '0';
     if (const char* e = getenv("DMB200_ATTN_POLY")) attn_poly_ = e[0] != '0';           // 0: every exp2 on MUFU
+    if constexpr (std::is_same<T, float>::value) {
+      DMB_CUDA(cudaFuncSetAttribute(attention_mma_f32_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+      DMB_CUDA(cudaFuncSetAttribute(attention_mma_f32_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+      DMB_CUDA(cudaFuncSetAttribute(attention_mma_f32_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    }
     if constexpr (std::is_same<T, __nv_bfloat16>::value) {
       const int am_smem = 110 * 1024;
       if (const char* e = getenv("DMB200_ATTN_VAR")) attn_var_ = atoi(e) & 7;
@@ -1137,6 +1142,23 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
           if (D == 16) launch(attention_tc_kernel<16>, grid, kAttnThreads, smem, s, qkv.p, qkv.g, C, av.p, qpc);
           else if (D == 32) launch(attention_tc_kernel<32>, grid, kAttnThreads, smem, s, qkv.p, qkv.g, C, av.p, qpc);
           else launch(attention_tc_kernel<64>, grid, kAttnThreads, smem, s, qkv.p, qkv.g, C, av.p, qpc);
+          DMB_CHECK_LAUNCH();
+          count();
+          return;
+        }
+      }
+      if constexpr (std::is_same<T, float>::value) {
+        if (use_mma_attention_ && L > 16) {   // TF32 warp-level MMA attention (attention_mma.cuh)
+          const int ntiles = cdiv(L, 16);
+          const int nw = std::min(kAfMaxWarps, ntiles);
+          const int splits = std::max(1, std::min(cdiv(ntiles, nw), cdiv(2 * num_sms_, 4 * qkv.g.n)));
+          const int tpc = cdiv(ntiles, splits);
+          const dim3 grid(cdiv(ntiles, tpc), 4, qkv.g.n);
+          const size_t smem = attention_mma_f32_smem_bytes(L, D);
+          const int threads = 32 * std::min(nw, tpc);
+          if (D == 16) launch(attention_mma_f32_kernel<16>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p, tpc);
+          else if (D == 32) launch(attention_mma_f32_kernel<32>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p, tpc);
+          else launch(attention_mma_f32_kernel<64>, grid, threads, smem, s, qkv.p, qkv.g, C, av.p, tpc);
           DMB_CHECK_LAUNCH();
           count();
           return;
