@@ -317,7 +317,7 @@ def run_config4(args, ctx, dev, world, rank, T, coef, barrier):
         _, u8 = ctx.vae_decode(x, want_f32=False, want_u8=True)
         return u8
 
-    run_chunk(b, min(chunk, e - b), steps=20)          # plan + graph + decoder warm-up
+    run_chunk(b, min(chunk, e - b), steps=min(20, T))  # plan + graph + decoder warm-up
     import torch.cuda as tc
     e0, e1 = tc.Event(enable_timing=True), tc.Event(enable_timing=True)
     barrier()
