@@ -244,8 +244,10 @@ attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_const
         uint4 w4;
         __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-          wp[i] = __floats2bfloat162_rn(gelu_fast(v[8 * j + 2 * i] + bv[2 * i]), gelu_fast(v[8 * j + 2 * i + 1] + bv[2 * i + 1]));
+        for (int i = 0; i < 8; ++i) bv[i] += v[8 * j + i];
+        gelu_inplace<__nv_bfloat16, 8>(bv);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) wp[i] = __floats2bfloat162_rn(bv[2 * i], bv[2 * i + 1]);
         *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
       }
     }
@@ -507,8 +509,10 @@ attn_tail256_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_co
         uint4 w4;
         __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-          wp[i] = __floats2bfloat162_rn(gelu_fast(v[8 * jj + 2 * i] + bv[2 * i]), gelu_fast(v[8 * jj + 2 * i + 1] + bv[2 * i + 1]));
+        for (int i = 0; i < 8; ++i) bv[i] += v[8 * jj + i];
+        gelu_inplace<__nv_bfloat16, 8>(bv);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) wp[i] = __floats2bfloat162_rn(bv[2 * i], bv[2 * i + 1]);
         *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
       }
     }

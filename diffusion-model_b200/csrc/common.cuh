@@ -308,9 +308,60 @@ __device__ __forceinline__ float2 gelu_fast2(float2 x) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(d.y));
   return __fmul2_rn(x, make_float2(r0, r1));
 }
+// Four elements at once with ONE reciprocal: the streaming GroupNorm kernels sit on the MUFU pipe
+// (ncu: XU 50-60 % at 30 % occupancy, the highest pipe; ex2 + rcp = 2 MUFU per element at 16 per
+// clock per SM).  With d_i = 1 + 2^(t_i):  R = 1 / (d0 d1 d2 d3),  1/d0 = R d1 (d2 d3), ... --
+// 5 MUFU per four elements instead of 8, the extra multiplies on the packed fp32x2 pipe.  t is
+// clamped at 30 (d <= 2^30 + 1, the product stays below 2^121; beyond it x / d < |x| 1e-9, which
+// every caller rounds to zero or adds to a residual of order 1).  The quotients differ from
+// gelu_fast's by fp32 rounding only (three roundings instead of one): far below the bf16 rounding
+// of the stored result -- but not bit-identical with it, so a kernel uses one form throughout.
+#ifndef DMB_GELU4
+#define DMB_GELU4 1   // 0: every GELU of the bf16 mode takes its own reciprocal (gelu_fast / gelu_fast2)
+#endif
+constexpr bool kGelu4 = DMB_GELU4 != 0;
+__device__ __forceinline__ void gelu_fast4(float2& xa, float2& xb) {
+  const float2 k0 = make_float2(-3.4587828849907964e-06f, -3.4587828849907964e-06f);
+  const float2 k1 = make_float2(9.363872959511355e-05f, 9.363872959511355e-05f);
+  const float2 k2 = make_float2(0.0003210399590898305f, 0.0003210399590898305f);
+  const float2 k3 = make_float2(-0.10513131320476532f, -0.10513131320476532f);
+  const float2 k4 = make_float2(-2.3021068572998047f, -2.3021068572998047f);
+  const float2 xa2 = __fmul2_rn(xa, xa), xb2 = __fmul2_rn(xb, xb);
+  float2 ga = __ffma2_rn(k0, xa2, k1), gb = __ffma2_rn(k0, xb2, k1);
+  ga = __ffma2_rn(ga, xa2, k2); gb = __ffma2_rn(gb, xb2, k2);
+  ga = __ffma2_rn(ga, xa2, k3); gb = __ffma2_rn(gb, xb2, k3);
+  ga = __ffma2_rn(ga, xa2, k4); gb = __ffma2_rn(gb, xb2, k4);
+  const float2 ta = __fmul2_rn(ga, xa), tb = __fmul2_rn(gb, xb);
+  float e0, e1, e2, e3, R;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(fminf(ta.x, 30.f)));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(fminf(ta.y, 30.f)));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e2) : "f"(fminf(tb.x, 30.f)));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e3) : "f"(fminf(tb.y, 30.f)));
+  const float2 one = make_float2(1.0f, 1.0f);
+  const float2 da = __fadd2_rn(make_float2(e0, e1), one), db = __fadd2_rn(make_float2(e2, e3), one);
+  const float2 m = __fmul2_rn(da, db);                       // (d0 d2, d1 d3)
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(R) : "f"(m.x * m.y));
+  const float2 q = __fmul2_rn(make_float2(R, R), make_float2(m.y, m.x));   // (1 / (d0 d2), 1 / (d1 d3))
+  xa = __fmul2_rn(xa, __fmul2_rn(q, db));                    // 1/d0 = q.x d2, 1/d1 = q.y d3
+  xb = __fmul2_rn(xb, __fmul2_rn(q, da));                    // 1/d2 = q.x d0, 1/d3 = q.y d1
+}
 template <typename T> __device__ __forceinline__ float gelu_for(float x) {
   if constexpr (sizeof(T) == 2) return gelu_fast(x);
   else return gelu_erf(x);
+}
+// GELU of N (a multiple of 4) values in place: bf16 storage mode four at a time, fp32 mode the erf form
+template <typename T, int N> __device__ __forceinline__ void gelu_inplace(float* v) {
+  if constexpr (sizeof(T) == 2) {
+#pragma unroll
+    for (int j = 0; j < N; j += 4) {
+      float2 a = make_float2(v[j], v[j + 1]), b = make_float2(v[j + 2], v[j + 3]);
+      if constexpr (kGelu4) { gelu_fast4(a, b); } else { a = gelu_fast2(a); b = gelu_fast2(b); }
+      v[j] = a.x; v[j + 1] = a.y; v[j + 2] = b.x; v[j + 3] = b.y;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < N; ++j) v[j] = gelu_erf(v[j]);
+  }
 }
 __device__ __forceinline__ float silu(float x) { return x / (1.0f + expf(-x)); }
 

@@ -298,6 +298,7 @@ class Engine : public IEngine {
       if (const char* e = getenv("DMB200_PIX_MAXHW")) pix_max_hw_ = atoi(e);
       const char* re = getenv("DMB200_ROW3");   // 0: nine separate A tiles per K chunk
       row3_ = re ? atoi(re) : 1;
+      if (const char* e = getenv("DMB200_CONVT_PLANAR")) convt_planar_ = e[0] != '0';
       if (const char* e = getenv("DMB200_ENC_IN_MMA")) enc_in_mma_ = atoi(e) != 0;
     }
     const char* pe = getenv("DMB200_PAIRS");
@@ -491,6 +492,7 @@ class Engine : public IEngine {
   int pix_fill_pct_ = 90;              // narrow the N tile while there are fewer tiles than this share of the SMs
   bool pix_mode_ = true;   // DMB200_PIX=0: small maps keep the padded-row GEMM at every batch size
   int row3_ = 1;   // DMB200_ROW3=0: every tap of a 3x3 conv loads its own A tile
+  bool convt_planar_ = true;   // DMB200_CONVT_PLANAR=0: ConvTranspose phases scatter their rows from registers
   bool use_fused_tail_ = true;   // DMB200_FUSED_TAIL=0: out_proj / LayerNorm / ff1 / ff2 as four launches
   bool use_acc4_ = true;   // DMB200_ACC4=0: two epilogue warpgroups for every launch
   int min_bn_ = 16;
@@ -840,7 +842,8 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
       }
   }
   p.tma_store = (out_act && ep.epi == EPI_STORE && ep.map_mode == 0 && bn % ElemTraits<T>::kChunkK == 0 &&
-                 out_act->C % ElemTraits<T>::kChunkK == 0 && out_act->C >= p.n_tiles * bn &&
+                 out_act->C % ElemTraits<T>::kChunkK == 0 && out_act->C >= ep.out_col0 + p.n_tiles * bn &&
+                 ep.out_col0 % ElemTraits<T>::kChunkK == 0 &&
                  out_act->g.rows_alloc == a.g.rows_alloc && ep.out == out_act->p && ep.ldc == out_act->C)
                     ? 1 : 0;
   if (pix) DMB_REQUIRE(p.tma_store == 1, "pixel-major conv needs the TMA-store epilogue");
@@ -1532,19 +1535,26 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
   auto& ops = P.ops;
   VaePlan* pp = &P;
 
-  auto gn8 = [&](const Act<T>& raw, const std::string& name) {
-    Act<T> out = new_act(pool, raw.g.n, raw.g.H, raw.g.W, raw.C, false);
+  // planar: `raw` is the phase-planar output of a ConvTranspose (convT below): four phase slots per
+  // pixel of the input map; the normalised activation is written at 2H x 2W
+  auto gn8 = [&](const Act<T>& raw, const std::string& name, bool planar = false) {
+    Act<T> out = planar ? new_act(pool, raw.g.n, raw.g.H * 2, raw.g.W * 2, raw.C / 4, false)
+                        : new_act(pool, raw.g.n, raw.g.H, raw.g.W, raw.C, false);
     const int total_vec = raw.g.H * raw.g.W * raw.C / 8;
     const int chunks = std::max(1, std::min(32, total_vec / 4096));
     double2* partial = pool.alloc_n<double2>(static_cast<size_t>(raw.g.n) * chunks * 8);
     const float* gamma = f(name + ".weight");
     const float* beta = f(name + ".bias");
     ops.tag("vae gn8+gelu", 0, 3.0 * raw.g.n * total_vec * 8 * sizeof(T));
-    ops.push_back([this, raw, out, chunks, partial, gamma, beta](cudaStream_t s) {
-      gn8_stats_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, raw.g, raw.C, partial);
+    ops.push_back([this, raw, out, chunks, partial, gamma, beta, planar](cudaStream_t s) {
+      gn8_stats_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, raw.g, raw.C, partial, planar ? 4 : 1);
       DMB_CHECK_LAUNCH();
-      gn8_apply_gelu_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
-                                                                    raw.C, out.p);
+      if (planar)
+        gn8_apply_gelu_d2s_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
+                                                                          raw.C, out.g, out.p);
+      else
+        gn8_apply_gelu_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
+                                                                      raw.C, out.p);
       DMB_CHECK_LAUNCH();
       count(2);
     });
@@ -1558,12 +1568,19 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
     ops.push_back(op_conv(in, w, out));
     return out;
   };
+  // ConvTranspose2d(4, 2, 1) = four phase GEMMs of 2 x 2 taps.  Planar form (default): all four leave
+  // through the TMA-store epilogue into one matrix over the INPUT map's pixels, phase (2a + b) at columns
+  // (2a + b) C .. + C; the GroupNorm pass that follows moves them to their 2H x 2W positions
+  // (kernels.cuh, gn8_apply_gelu_d2s_kernel).  DMB200_CONVT_PLANAR=0: every phase scatters its rows
+  // of the 2H x 2W map from registers.
+  const bool planar = convt_planar_;
   auto convT = [&](const Act<T>& in, const std::string& wname) {
     const GemmW<T> w = gw_.at(wname);
-    Act<T> out = new_act(pool, in.g.n, in.g.H * 2, in.g.W * 2, w.N, false);
+    Act<T> out = planar ? new_act(pool, in.g.n, in.g.H, in.g.W, 4 * w.N, false)
+                        : new_act(pool, in.g.n, in.g.H * 2, in.g.W * 2, w.N, false);
     ops.tag("vae convT4x4 " + std::to_string(w.K) + "->" + std::to_string(w.N) + " @" + std::to_string(in.g.H),
             2.0 * in.g.n * in.g.H * in.g.W * 16.0 * w.K * w.N);
-    ops.push_back([this, in, w, out](cudaStream_t s) {
+    ops.push_back([this, in, w, out, planar](cudaStream_t s) {
       for (int a = 0; a < 2; ++a)
         for (int b = 0; b < 2; ++b) {
           int shifts[4];
@@ -1576,8 +1593,13 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
           GemmParams ep{};
           ep.epi = EPI_STORE;
           ep.out = out.p; ep.ldc = out.C; ep.bias = w.bias;
-          ep.map_mode = 1; ep.geo_out = out.g; ep.up_a = a; ep.up_b = b;
-          gemm(in, w, a * 2 + b, shifts, 4, ep, s);
+          if (planar) {
+            ep.out_col0 = (a * 2 + b) * w.N;
+            gemm(in, w, a * 2 + b, shifts, 4, ep, s, &out);
+          } else {
+            ep.map_mode = 1; ep.geo_out = out.g; ep.up_a = a; ep.up_b = b;
+            gemm(in, w, a * 2 + b, shifts, 4, ep, s);
+          }
         }
     });
     return out;
@@ -1599,11 +1621,11 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
     });
   }
   Act<T> a = gn8(r0, "vae.dec.1");
-  a = gn8(convT(a, "vae.dec.3"), "vae.dec.4");
+  a = gn8(convT(a, "vae.dec.3"), "vae.dec.4", planar);
   a = gn8(conv(a, "vae.dec.6"), "vae.dec.7");
-  a = gn8(convT(a, "vae.dec.9"), "vae.dec.10");
+  a = gn8(convT(a, "vae.dec.9"), "vae.dec.10", planar);
   a = gn8(conv(a, "vae.dec.12"), "vae.dec.13");
-  a = gn8(convT(a, "vae.dec.15"), "vae.dec.16");
+  a = gn8(convT(a, "vae.dec.15"), "vae.dec.16", planar);
   {
     const GemmW<T> w = gw_.at("vae.dec.18");
     ops.tag("vae conv3x3 64->3 @224 +sigmoid", 2.0 * n * 224.0 * 224 * 9 * 64 * 3);

@@ -64,6 +64,8 @@ struct GemmParams {
   Geo geo_out;
   int up_a, up_b;
   int tma_store;          // 1: epilogue stores through smem + TMA (tmap_out); 0: per-thread stores
+  int out_col0;           // EPI_STORE: first output column of the launch (the phase slot of a phase-planar
+                          // ConvTranspose output, engine.cu build_vae_plan); bias / residual are not shifted
   // pixel-major 3x3 conv (small maps at large batch, see PixTile): tmap_a / tmap_out are the 3D
   // (channel, PM row of the sample, sample) maps, M runs over SAMPLES, a tile belongs to one
   // output pixel and its taps are the pixel's in-image neighbours
@@ -457,8 +459,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 }
               }
               if (p.act == 1) {
-#pragma unroll
-                for (int j = 0; j < kP; ++j) v[j] = gelu_for<T>(v[j]);
+                gelu_inplace<T, kP>(v);
               }
               if (residual) {
                 const T* rp = residual + static_cast<size_t>(r) * p.ldc + col0;
@@ -512,7 +513,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           named_bar_sync(bar_id, 128);
           if (store_thread) {
             if (pix) tma_store_3d(&tmap_out, buf, n0 + k * kSubN, prow, m0);
-            else tma_store_2d(&tmap_out, buf, n0 + k * kSubN, m0);
+            else tma_store_2d(&tmap_out, buf, p.out_col0 + n0 + k * kSubN, m0);
             tma_store_commit();
           }
         }
@@ -554,8 +555,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 if (j < ncols) v[j] += __ldg(p.bias + col0 + j);
             }
             if (p.act == 1) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = gelu_for<T>(v[j]);
+              gelu_inplace<T, 32>(v);
             }
             if (residual) {
               const T* rp = residual + static_cast<size_t>(r) * p.ldc + col0;
@@ -573,7 +573,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
               sacc.add(stat_unit16(v));
               if (ncols > 16) sacc.add(stat_unit16(v + 16));
             }
-            T* op = out + static_cast<size_t>(out_r) * p.ldc + col0;
+            T* op = out + static_cast<size_t>(out_r) * p.ldc + p.out_col0 + col0;
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
               if (j < ncols) store8(op + j, v + j);

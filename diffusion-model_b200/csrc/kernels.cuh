@@ -432,16 +432,24 @@ gn1_apply_kernel(const T* __restrict__ raw, const long long* __restrict__ sample
         float xv[8];
         xr[u].unpack(xv);
         if constexpr (sizeof(T) == 2 && (MODE == GN_GELU || MODE == GN_RES_GELU)) {
-          // bf16 mode: affine, residual add and GELU on packed fp32x2 instructions (same operations,
-          // same order, same bits as the scalar form below)
+          // bf16 mode: affine, residual add and GELU on packed fp32x2 instructions, GELU four
+          // elements per reciprocal (common.cuh, gelu_fast4)
           float rv[8];
           if (MODE == GN_RES_GELU) rs[u].unpack(rv);
 #pragma unroll
-          for (int i = 0; i < 8; i += 2) {
-            float2 v = __ffma2_rn(make_float2(xv[i], xv[i + 1]), make_float2(sc[i], sc[i + 1]), make_float2(sh[i], sh[i + 1]));
-            if (MODE == GN_RES_GELU) v = __fadd2_rn(make_float2(rv[i], rv[i + 1]), v);
-            v = gelu_fast2(v);
-            xv[i] = v.x; xv[i + 1] = v.y;
+          for (int i = 0; i < 8; i += 4) {
+            float2 va = __ffma2_rn(make_float2(xv[i], xv[i + 1]), make_float2(sc[i], sc[i + 1]), make_float2(sh[i], sh[i + 1]));
+            float2 vb = __ffma2_rn(make_float2(xv[i + 2], xv[i + 3]), make_float2(sc[i + 2], sc[i + 3]), make_float2(sh[i + 2], sh[i + 3]));
+            if (MODE == GN_RES_GELU) {
+              va = __fadd2_rn(make_float2(rv[i], rv[i + 1]), va);
+              vb = __fadd2_rn(make_float2(rv[i + 2], rv[i + 3]), vb);
+            }
+            if constexpr (kGelu4) {
+              gelu_fast4(va, vb);
+            } else {
+              va = gelu_fast2(va); vb = gelu_fast2(vb);
+            }
+            xv[i] = va.x; xv[i + 1] = va.y; xv[i + 2] = vb.x; xv[i + 3] = vb.y;
           }
         } else {
 #pragma unroll
@@ -928,7 +936,7 @@ static __global__ void philox_fill_kernel(float* out, int B, int HW, unsigned lo
 // ---------------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256)
-gn8_stats_kernel(const T* __restrict__ raw, Geo g, int C, double2* __restrict__ partial) {
+gn8_stats_kernel(const T* __restrict__ raw, Geo g, int C, double2* __restrict__ partial, int phases = 1) {
   __shared__ double red[2][256];
   const int b = blockIdx.y, tid = threadIdx.x;
   const int vpr = C / 8;
@@ -961,12 +969,13 @@ gn8_stats_kernel(const T* __restrict__ raw, Geo g, int C, double2* __restrict__ 
   red[0][tid] = s; red[1][tid] = ss;
   __syncthreads();
   {
-    // thread j's vector column is j % vpr (begin is a multiple of vpr); group = column / (vpr/8).
-    // Warp w gathers group w: fixed lane order, then a fixed shuffle tree.
-    const int w = tid >> 5, lane = tid & 31, vpg = vpr / 8;
+    // thread j's vector column is j % vpr (begin is a multiple of vpr); group = column / (vpr/8) --
+    // for a phase-planar row (C = phases x channels, see gn8_apply_gelu_d2s_kernel) the column inside
+    // its phase slot.  Warp w gathers group w: fixed lane order, then a fixed shuffle tree.
+    const int w = tid >> 5, lane = tid & 31, vpp = vpr / phases, vpg = vpp / 8;
     double a = 0.0, q = 0.0;
     for (int j = lane; j < 256; j += 32) {
-      if (((j % vpr) / vpg) == w) { a += red[0][j]; q += red[1][j]; }
+      if ((((j % vpr) % vpp) / vpg) == w) { a += red[0][j]; q += red[1][j]; }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -1040,8 +1049,63 @@ gn8_apply_gelu_kernel(const T* __restrict__ raw, const double2* __restrict__ par
     for (int u = 0; u < U; ++u) {
       if (v0 + u * 256 < end) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) xv[u][i] = gelu_for<T>(fmaf(xv[u][i], ga[i], be[i]));
+        for (int i = 0; i < 8; ++i) xv[u][i] = fmaf(xv[u][i], ga[i], be[i]);
+        gelu_inplace<T, 8>(xv[u]);
         store8(out + off[u], xv[u]);
+      }
+    }
+  }
+}
+
+// The same for a PHASE-PLANAR input: the four ConvTranspose2d(4, 2, 1) phase GEMMs of a layer leave
+// through the TMA-store epilogue into one [pixel of the INPUT map][phase (2a + b)][channel] matrix
+// (row width C4 = 4 C) instead of scattering rows of the 2H x 2W map from registers; this kernel,
+// which reads and rewrites every element anyway, puts pixel (y, x)'s phase (a, b) at output pixel
+// (2y + a, 2x + b).  Both sides move whole 16-byte channel vectors.  models/vae.py:37-47.
+template <typename T>
+__global__ void __launch_bounds__(256)
+gn8_apply_gelu_d2s_kernel(const T* __restrict__ raw, const double2* __restrict__ partial, int n_chunks_stats,
+                          const float* __restrict__ gamma, const float* __restrict__ beta, Geo g, int C4,
+                          Geo g2, T* __restrict__ out) {
+  __shared__ float s_mean[8], s_rstd[8];
+  const int b = blockIdx.y, tid = threadIdx.x;
+  const int HW = g.H * g.W;
+  gn8_finish_stats(partial, b, n_chunks_stats, static_cast<double>(HW) * (C4 / 8), s_mean, s_rstd);
+  const int C = C4 / 4;
+  const int vpr = C4 / 8, vpp = vpr / 4, vpg = vpp / 8;
+  const int total = HW * vpr;
+  const int per = (((total + gridDim.x - 1) / gridDim.x) + vpr - 1) / vpr * vpr;
+  const int begin = blockIdx.x * per;
+  const int end = min(total, begin + per);
+  const int vsh = 31 - __clz(vpr);
+  const int col = tid & (vpr - 1);           // begin is a multiple of vpr and 256 a multiple of vpr
+  const int phase = col / vpp, vc = col - phase * vpp, c0 = vc * 8;
+  const float mean = s_mean[vc / vpg], rstd = s_rstd[vc / vpg];
+  float ga[8], be[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { ga[i] = gamma[c0 + i] * rstd; be[i] = beta[c0 + i] - mean * ga[i]; }
+  const int oy = phase >> 1, ox = phase & 1;
+  constexpr int U = 4;
+  for (int v0 = begin + tid; v0 < end; v0 += 256 * U) {
+    float xv[U][8];
+    size_t dst[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int v = v0 + u * 256;
+      if (v < end) {
+        const int pix = v >> vsh;
+        const int y = fdiv(pix, g.mW, g.W), x = pix - y * g.W;
+        load8(raw + (static_cast<size_t>(b) * g.S + (y + 1) * g.Wp + x) * C4 + col * 8, xv[u]);
+        dst[u] = static_cast<size_t>(geo_row(g2, b, 2 * y + oy, 2 * x + ox)) * C + c0;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (v0 + u * 256 < end) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) xv[u][i] = fmaf(xv[u][i], ga[i], be[i]);
+        gelu_inplace<T, 8>(xv[u]);
+        store8(out + dst[u], xv[u]);
       }
     }
   }
@@ -1291,7 +1355,8 @@ gn8_apply_gelu_s2d_kernel(const T* __restrict__ raw, const double2* __restrict__
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) xv[q][i] = inside[q] ? gelu_for<T>(fmaf(xv[q][i], ga[i], be[i])) : 0.f;
+      for (int i = 0; i < 8; ++i) xv[q][i] = inside[q] ? fmaf(xv[q][i], ga[i], be[i]) : 0.f;   // (GELU(0) = 0)
+      gelu_inplace<T, 8>(xv[q]);
       store8(dp + q * C, xv[q]);
     }
   }
