@@ -1550,11 +1550,11 @@ void Engine<T>::build_vae_plan(VaePlan& P, int n) {
       gn8_stats_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, raw.g, raw.C, partial, planar ? 4 : 1);
       DMB_CHECK_LAUNCH();
       if (planar)
-        gn8_apply_gelu_d2s_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
-                                                                          raw.C, out.g, out.p);
+        gn8_apply_gelu_kernel<T, true><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
+                                                                            raw.C, out.g, out.p);
       else
-        gn8_apply_gelu_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
-                                                                      raw.C, out.p);
+        gn8_apply_gelu_kernel<T, false><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
+                                                                             raw.C, out.g, out.p);
       DMB_CHECK_LAUNCH();
       count(2);
     });
@@ -1731,8 +1731,8 @@ void Engine<T>::build_vae_enc_plan(VaeEncPlan& P, int n) {
         gn8_apply_gelu_s2d_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta,
                                                                           raw.g, raw.C, out.g, out.p);
       else
-        gn8_apply_gelu_kernel<T><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
-                                                                      raw.C, out.p);
+        gn8_apply_gelu_kernel<T, false><<<dim3(chunks, raw.g.n), 256, 0, s>>>(raw.p, partial, chunks, gamma, beta, raw.g,
+                                                                             raw.C, out.g, out.p);
       DMB_CHECK_LAUNCH();
       count(2);
     });

@@ -940,29 +940,29 @@ gn8_stats_kernel(const T* __restrict__ raw, Geo g, int C, double2* __restrict__ 
   __shared__ double red[2][256];
   const int b = blockIdx.y, tid = threadIdx.x;
   const int vpr = C / 8;
-  const int HW = g.H * g.W;
-  const int total = HW * vpr;
-  const int per = (((total + gridDim.x - 1) / gridDim.x) + vpr - 1) / vpr * vpr;
+  // A sample's PM rows are one contiguous block and its pad rows hold zeros (no producer writes them
+  // anything else), which add nothing to either sum: the kernel streams all S rows with no index
+  // arithmetic, eight 16-byte loads in flight per thread (the first version decoded a pixel per load
+  // and waited for four: 76 registers, 2.2 TB/s, stalled on the loads -- profiles/r1_v7_ncu_full_gn8_stats.md).
+  const int total = g.S * vpr;
+  const int per = (((total + gridDim.x - 1) / gridDim.x) + 255) / 256 * 256;   // a multiple of 256, hence of vpr
   const int begin = blockIdx.x * per;
   const int end = min(total, begin + per);
+  const T* src = raw + static_cast<size_t>(b) * g.S * C;
   float s = 0.f, ss = 0.f;
-  constexpr int U = 4;   // loads in flight per thread (8 measured slower on the 224x224 maps)
-  const int vsh = 31 - __clz(vpr);   // vpr is a power of two (C = 64 .. 256)
+  constexpr int U = 8;
   for (int v0 = begin + tid; v0 < end; v0 += 256 * U) {
-    float xv[U][8];
+    Raw8<T> xr[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int v = v0 + u * 256;
-      if (v < end) {
-        const int pix = v >> vsh, c0 = (v & (vpr - 1)) * 8;
-        load8(raw + static_cast<size_t>(geo_row_of_pixel(g, b, pix)) * C + c0, xv[u]);
-      }
-    }
+    for (int u = 0; u < U; ++u)
+      if (v0 + u * 256 < end) xr[u].load(src + static_cast<size_t>(v0 + u * 256) * 8);
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (v0 + u * 256 < end) {
+        float xv[8];
+        xr[u].unpack(xv);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) { s += xv[u][i]; ss += xv[u][i] * xv[u][i]; }
+        for (int i = 0; i < 8; ++i) { s += xv[i]; ss = fmaf(xv[i], xv[i], ss); }
       }
     }
   }
@@ -1011,103 +1011,79 @@ __device__ __forceinline__ void gn8_finish_stats(const double2* __restrict__ par
   __syncthreads();
 }
 
-template <typename T>
+// Pass 2: normalise + affine + GELU.  Like pass 1 it walks the sample's contiguous PM block (one
+// division per 16-byte vector, to tell pad rows from pixels) and keeps the next batch of loads in
+// flight while it works on the current one.
+// kD2S = false: out has the geometry of raw; pad rows are rewritten as zeros.
+// kD2S = true:  raw is PHASE-PLANAR -- the four ConvTranspose2d(4, 2, 1) phase GEMMs of a layer leave
+//   through the TMA-store epilogue into one [pixel of the INPUT map][phase (2a + b)][channel] matrix
+//   (row width C = 4 x channels) instead of scattering rows of the 2H x 2W map from registers; this
+//   pass, which reads and rewrites every element anyway, puts pixel (y, x)'s phase (a, b) at pixel
+//   (2y + a, 2x + b) of out (geometry g2).  Both sides move whole 16-byte channel vectors.
+// models/vae.py:37-47.
+template <typename T, bool kD2S>
 __global__ void __launch_bounds__(256)
 gn8_apply_gelu_kernel(const T* __restrict__ raw, const double2* __restrict__ partial, int n_chunks_stats,
                       const float* __restrict__ gamma, const float* __restrict__ beta, Geo g, int C,
-                      T* __restrict__ out) {
+                      Geo g2, T* __restrict__ out) {
   __shared__ float s_mean[8], s_rstd[8];
   const int b = blockIdx.y, tid = threadIdx.x;
-  const int HW = g.H * g.W;
-  gn8_finish_stats(partial, b, n_chunks_stats, static_cast<double>(HW) * (C / 8), s_mean, s_rstd);
-  const int vpr = C / 8, vpg = vpr / 8;
-  const int total = HW * vpr;
-  const int per = (total + gridDim.x - 1) / gridDim.x;
+  gn8_finish_stats(partial, b, n_chunks_stats, static_cast<double>(g.H) * g.W * (C / 8), s_mean, s_rstd);
+  const int vpr = C / 8, vpp = kD2S ? vpr / 4 : vpr, vpg = vpp / 8;
+  const int total = g.S * vpr;
+  const int per = (((total + gridDim.x - 1) / gridDim.x) + 255) / 256 * 256;   // a multiple of 256, hence of vpr
   const int begin = blockIdx.x * per;
   const int end = min(total, begin + per);
-  // 256 is a multiple of the vectors per pixel: a thread keeps its channel vector (gamma, beta,
-  // group statistics folded into one multiply-add) for every iteration; four loads in flight
-  const int vsh = 31 - __clz(vpr);   // vpr is a power of two (C = 64 .. 256)
-  const int vc = (begin + tid) & (vpr - 1), c0 = vc * 8;
-  const float mean = s_mean[vc / vpg], rstd = s_rstd[vc / vpg];
-  float ga[8], be[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) { ga[i] = gamma[c0 + i] * rstd; be[i] = beta[c0 + i] - mean * ga[i]; }
-  constexpr int U = 4;
-  for (int v0 = begin + tid; v0 < end; v0 += 256 * U) {
-    float xv[U][8];
-    size_t off[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int v = v0 + u * 256;
-      if (v < end) {
-        off[u] = static_cast<size_t>(geo_row_of_pixel(g, b, v >> vsh)) * C + c0;
-        load8(raw + off[u], xv[u]);
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (v0 + u * 256 < end) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) xv[u][i] = fmaf(xv[u][i], ga[i], be[i]);
-        gelu_inplace<T, 8>(xv[u]);
-        store8(out + off[u], xv[u]);
-      }
-    }
-  }
-}
-
-// The same for a PHASE-PLANAR input: the four ConvTranspose2d(4, 2, 1) phase GEMMs of a layer leave
-// through the TMA-store epilogue into one [pixel of the INPUT map][phase (2a + b)][channel] matrix
-// (row width C4 = 4 C) instead of scattering rows of the 2H x 2W map from registers; this kernel,
-// which reads and rewrites every element anyway, puts pixel (y, x)'s phase (a, b) at output pixel
-// (2y + a, 2x + b).  Both sides move whole 16-byte channel vectors.  models/vae.py:37-47.
-template <typename T>
-__global__ void __launch_bounds__(256)
-gn8_apply_gelu_d2s_kernel(const T* __restrict__ raw, const double2* __restrict__ partial, int n_chunks_stats,
-                          const float* __restrict__ gamma, const float* __restrict__ beta, Geo g, int C4,
-                          Geo g2, T* __restrict__ out) {
-  __shared__ float s_mean[8], s_rstd[8];
-  const int b = blockIdx.y, tid = threadIdx.x;
-  const int HW = g.H * g.W;
-  gn8_finish_stats(partial, b, n_chunks_stats, static_cast<double>(HW) * (C4 / 8), s_mean, s_rstd);
-  const int C = C4 / 4;
-  const int vpr = C4 / 8, vpp = vpr / 4, vpg = vpp / 8;
-  const int total = HW * vpr;
-  const int per = (((total + gridDim.x - 1) / gridDim.x) + vpr - 1) / vpr * vpr;
-  const int begin = blockIdx.x * per;
-  const int end = min(total, begin + per);
-  const int vsh = 31 - __clz(vpr);
-  const int col = tid & (vpr - 1);           // begin is a multiple of vpr and 256 a multiple of vpr
+  const int vsh = 31 - __clz(vpr);   // vpr is a power of two
+  // a thread keeps its channel vector (gamma, beta and the group statistics folded into one multiply-add)
+  const int col = tid & (vpr - 1);
   const int phase = col / vpp, vc = col - phase * vpp, c0 = vc * 8;
+  const int Cout = kD2S ? C / 4 : C;
   const float mean = s_mean[vc / vpg], rstd = s_rstd[vc / vpg];
   float ga[8], be[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) { ga[i] = gamma[c0 + i] * rstd; be[i] = beta[c0 + i] - mean * ga[i]; }
+  const T* src = raw + static_cast<size_t>(b) * g.S * C;
+  T* dst = out + static_cast<size_t>(b) * g2.S * Cout + c0;
   const int oy = phase >> 1, ox = phase & 1;
   constexpr int U = 4;
-  for (int v0 = begin + tid; v0 < end; v0 += 256 * U) {
-    float xv[U][8];
-    size_t dst[U];
+  Raw8<T> cur[U], nxt[U];
+  int v0 = begin + tid;
+#pragma unroll
+  for (int u = 0; u < U; ++u)
+    if (v0 + u * 256 < end) cur[u].load(src + static_cast<size_t>(v0 + u * 256) * 8);
+  for (; v0 < end; v0 += 256 * U) {
+    const int vn = v0 + 256 * U;
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (vn + u * 256 < end) nxt[u].load(src + static_cast<size_t>(vn + u * 256) * 8);
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int v = v0 + u * 256;
       if (v < end) {
-        const int pix = v >> vsh;
-        const int y = fdiv(pix, g.mW, g.W), x = pix - y * g.W;
-        load8(raw + (static_cast<size_t>(b) * g.S + (y + 1) * g.Wp + x) * C4 + col * 8, xv[u]);
-        dst[u] = static_cast<size_t>(geo_row(g2, b, 2 * y + oy, 2 * x + ox)) * C + c0;
+        const int rr = v >> vsh;
+        const int yy = fdiv(rr, g.mWp, g.Wp), x = rr - yy * g.Wp;
+        const bool pixel = yy >= 1 && x != g.W;
+        float xv[8];
+        cur[u].unpack(xv);
+        if (pixel) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) xv[i] = fmaf(xv[i], ga[i], be[i]);
+          gelu_inplace<T, 8>(xv);
+        }
+        if constexpr (kD2S) {
+          if (pixel) store8(dst + static_cast<size_t>((2 * yy - 1 + oy) * g2.Wp + 2 * x + ox) * Cout, xv);
+        } else {
+          if (!pixel) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xv[i] = 0.f;
+          }
+          store8(dst + static_cast<size_t>(rr) * Cout, xv);
+        }
       }
     }
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (v0 + u * 256 < end) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) xv[u][i] = fmaf(xv[u][i], ga[i], be[i]);
-        gelu_inplace<T, 8>(xv[u]);
-        store8(out + dst[u], xv[u]);
-      }
-    }
+    for (int u = 0; u < U; ++u) cur[u] = nxt[u];
   }
 }
 
