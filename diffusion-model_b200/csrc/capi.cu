@@ -178,6 +178,63 @@ int dmb_add_noise(dmb_ctx* ctx, const float* x0, const int64_t* t, const float* 
   });
 }
 
+namespace {
+constexpr int kReconThreads = 1024;
+// one CTA per sample; thread t takes float4 vectors t, t + 1024, ... (then the scalar tail), sums in
+// double, and the CTA combines the 1024 sums with a fixed shuffle + shared-memory tree
+__global__ void __launch_bounds__(kReconThreads)
+recon_error_kernel(const float* __restrict__ a, const float* __restrict__ b, long long per_sample,
+                   double* __restrict__ sq_sum, double* __restrict__ abs_sum) {
+  __shared__ double red[2][kReconThreads / 32];
+  const float* pa = a + static_cast<size_t>(blockIdx.x) * per_sample;
+  const float* pb = b + static_cast<size_t>(blockIdx.x) * per_sample;
+  double sq = 0.0, ab = 0.0;
+  const bool vec = (per_sample % 4 == 0) && ((reinterpret_cast<uintptr_t>(pa) | reinterpret_cast<uintptr_t>(pb)) % 16 == 0);
+  const long long nvec = vec ? per_sample / 4 : 0;
+  for (long long i = threadIdx.x; i < nvec; i += kReconThreads) {
+    const float4 x = reinterpret_cast<const float4*>(pa)[i], y = reinterpret_cast<const float4*>(pb)[i];
+    const float d0 = x.x - y.x, d1 = x.y - y.y, d2 = x.z - y.z, d3 = x.w - y.w;
+    sq += static_cast<double>(d0) * d0 + static_cast<double>(d1) * d1 + static_cast<double>(d2) * d2 + static_cast<double>(d3) * d3;
+    ab += static_cast<double>(fabsf(d0)) + fabsf(d1) + fabsf(d2) + fabsf(d3);
+  }
+  for (long long i = nvec * 4 + threadIdx.x; i < per_sample; i += kReconThreads) {
+    const float d = pa[i] - pb[i];
+    sq += static_cast<double>(d) * d;
+    ab += fabsf(d);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    ab += __shfl_xor_sync(0xffffffffu, ab, o);
+  }
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = sq; red[1][threadIdx.x >> 5] = ab; }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    sq = red[0][threadIdx.x]; ab = red[1][threadIdx.x];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      sq += __shfl_xor_sync(0xffffffffu, sq, o);
+      ab += __shfl_xor_sync(0xffffffffu, ab, o);
+    }
+    if (threadIdx.x == 0) {
+      if (sq_sum) sq_sum[blockIdx.x] = sq;
+      if (abs_sum) abs_sum[blockIdx.x] = ab;
+    }
+  }
+}
+}  // namespace
+
+int dmb_recon_error(dmb_ctx* ctx, const float* a, const float* b, int B, int64_t per_sample,
+                    double* sq_sum, double* abs_sum, void* stream) {
+  return guarded([&] {
+    DMB_REQUIRE(ctx && a && b && (sq_sum || abs_sum), "ctx, a, b and one of sq_sum / abs_sum are required");
+    DMB_REQUIRE(B >= 1 && per_sample >= 1, "B >= 1 and per_sample >= 1 are required");
+    DMB_CUDA(cudaSetDevice(ctx->device));
+    recon_error_kernel<<<B, kReconThreads, 0, st(stream)>>>(a, b, static_cast<long long>(per_sample), sq_sum, abs_sum);
+    DMB_CHECK_LAUNCH();
+  });
+}
+
 int dmb_score_masks(dmb_ctx* ctx, const uint8_t* pred, int pred_channels, const uint8_t* gt, int gt_channels,
                     int B, int H, int W, int threshold, int invert, double sigma, int64_t* counts,
                     double* weighted_hit, void* stream) {

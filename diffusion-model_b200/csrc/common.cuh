@@ -291,7 +291,7 @@ __device__ __forceinline__ float gelu_fast(float x) {
 // Two elements at once on the packed fp32x2 instructions of sm_100 (FMUL2 / FFMA2 / FADD2): the
 // same operations in the same order as gelu_fast (bit-identical results), 8 issue slots + 4 MUFU per
 // pair instead of 18 + 4.  The streaming GroupNorm kernels are bound by instruction issue, not by
-// HBM (ncu: 55-65 % issue-slot utilisation at 30 % occupancy, profiles/r2_v9_ncu_full_gn1_apply.md).
+// HBM (ncu: 55-65 % issue-slot utilisation at 30 % occupancy, profiles/r2_v12_ncu_full_gn1_apply.md).
 __device__ __forceinline__ float2 gelu_fast2(float2 x) {
   const float2 x2 = __fmul2_rn(x, x);
   float2 g = make_float2(-3.4587828849907964e-06f, -3.4587828849907964e-06f);

@@ -46,6 +46,7 @@ _SIGNATURES = {
     "dmb_load_vae_enc_weights": (C.c_int, [_P, C.c_int, C.POINTER(C.c_char_p), C.POINTER(_P), C.POINTER(C.c_int64)]),
     "dmb_vae_encode": (C.c_int, [_P, _P, _P, C.c_int, _P, _P, _P, _P, _P]),
     "dmb_add_noise": (C.c_int, [_P, _P, _P, _P, C.c_int, _P, C.c_int, C.c_int64, _P, _P]),
+    "dmb_recon_error": (C.c_int, [_P, _P, _P, C.c_int, C.c_int64, _P, _P, _P]),
     "dmb_kl_per_sample_static": (C.c_int, [C.c_int, _P, _P, C.c_int, C.c_int64, C.c_float, _P, _P]),
     "dmb_score_masks": (C.c_int, [_P, _P, C.c_int, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
                                   _P, _P, _P]),
@@ -347,6 +348,20 @@ class Context:
         self._call("dmb_add_noise", self._h, _ptr(x0), _ptr(t), _ptr(ab), int(ab.numel()), _ptr(noise), B,
                    int(x0.numel() // B), _ptr(out), self._stream())
         return out
+
+    def recon_error(self, a, b):
+        """Per-sample float64 sums of (a - b)^2 and |a - b| (dmb_recon_error): the reconstruction term of
+        VAE.forward (vae.py:71-76) and the per-image errors of vae_recon_check.py:29-31."""
+        a = _check_dev(a.contiguous(), self.device, torch.float32, "a")
+        b = _check_dev(b.contiguous(), self.device, torch.float32, "b")
+        if a.shape != b.shape:
+            raise ValueError(f"shapes differ: {tuple(a.shape)} vs {tuple(b.shape)}")
+        B = a.shape[0]
+        sq = torch.empty((B,), device=self.device, dtype=torch.float64)
+        ab = torch.empty((B,), device=self.device, dtype=torch.float64)
+        self._call("dmb_recon_error", self._h, _ptr(a), _ptr(b), B, int(a.numel() // B), _ptr(sq), _ptr(ab),
+                   self._stream())
+        return sq, ab
 
     def score_masks(self, pred, gt, threshold=128, invert=True, sigma=2.0):
         """Device-side counters of eval_iou_noise.compute_metrics for a batch.  pred / gt: uint8 CUDA

@@ -4,7 +4,8 @@
 convolutions / transposed convolutions, GroupNorm(8)+GELU, sigmoid).  ``encode``
 (vae.py:51-62) runs there too: the strided 4x4 convolutions become
 2x2-tap GEMMs over a space-to-depth activation, and the 1x1 heads, the clamp, the
-reparameterisation and the KL term are one kernel.  Forward only: no autograd."""
+reparameterisation and the KL term are one kernel.  ``forward`` (vae.py:71-76) = encode, decode and
+the reconstruction error (dmb_recon_error).  Forward only: no autograd."""
 from __future__ import annotations
 
 import torch
@@ -119,5 +120,19 @@ class VAE(nn.Module):
                 eps = torch.randn((x.shape[0], 4, 28, 28), device=x.device, dtype=torch.float32)
             return ctx.vae_encode(x, eps, want_moments=True)
 
-    def forward(self, x):
-        raise NotImplementedError("VAE.forward (training) is outside the sampling path")
+    def forward(self, x, eps=None):
+        """encode -> decode -> loss, forward only (vae.py:71-76): returns
+        (x_recon, z, loss, {'recon_mse', 'kl'}) with loss = mse(x_recon, x) + 1e-6 * kl.  What
+        vae_recon_check.py and a validation pass need; there are no backward kernels, so a call that
+        would have to record a graph (grad mode on and a parameter that requires grad, i.e. a
+        training step) raises instead of returning a loss that cannot be differentiated."""
+        if torch.is_grad_enabled() and self.training and any(p.requires_grad for p in self.parameters()):
+            raise NotImplementedError("VAE.forward in training mode needs backward kernels, which libdmb200 does not "
+                                      "have (forward only): call it under torch.no_grad() or after .eval()")
+        with torch.no_grad():
+            z, kl = self.encode(x, eps)
+            x_recon = self.decode(z)
+            sq, _ = self._enc_ctx(x).recon_error(x_recon, x.to(torch.float32))
+            recon = (sq.sum() / float(x.numel())).to(torch.float32)
+            loss = recon + 1e-6 * kl
+        return x_recon, z, loss, {"recon_mse": recon, "kl": kl}

@@ -122,6 +122,15 @@ int dmb_vae_encode(dmb_ctx* ctx, const float* img, const float* eps, int B, floa
 int dmb_add_noise(dmb_ctx* ctx, const float* x0, const int64_t* t, const float* alpha_bars, int T,
                   const float* noise, int B, int64_t per_sample, float* x_t, void* stream);
 
+/* Reconstruction error of VAE.forward (vae.py:71-76: F.mse_loss(x_recon, x)) and of
+ * vae_recon_check.py:29-31 (per-image mean squared / absolute error): per sample, the float64 sums
+ * of (a - b)^2 and |a - b| over per_sample elements, accumulated in a fixed order (one CTA per
+ * sample: per-thread sums over a fixed stride, then a fixed tree), so two calls give the same bits.
+ * a, b (B, per_sample) fp32 [dev]; sq_sum, abs_sum (B) float64 [dev], either may be NULL.
+ * The caller divides (mean over the batch: sum(sq_sum) / (B * per_sample)). */
+int dmb_recon_error(dmb_ctx* ctx, const float* a, const float* b, int B, int64_t per_sample,
+                    double* sq_sum, double* abs_sum, void* stream);
+
 /* Allocation-free KL reduction.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
  * serving loops, harnesses that forbid it).  A variant of the KL term of dmb_vae_encode

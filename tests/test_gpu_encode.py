@@ -217,3 +217,59 @@ def test_input_conv_paths_agree(enc_golden, vae_pair):
             ctx.close()
     report("vae_encode_input_conv", rows)
     assert max(rows.values()) <= 3e-3, rows
+
+
+def test_vae_forward_matches_oracle(vae_pair):
+    """VAE.forward, forward only (vae.py:71-76): (x_recon, z, loss, {'recon_mse', 'kl'}) against the oracle's
+    encode -> decode -> F.mse_loss with the same normal draw; and the vae_recon_check.py sequence
+    (vae_recon_check.py:25-31: encode, decode, per-image mse / mae).  Stated tolerances (bf16 mode):
+    reconstruction max-abs <= 1.2e-2 (two networks in a row), recon_mse and kl relative <= 3e-2."""
+    import torch.nn.functional as F
+    vae, vsd = vae_pair
+    g = torch.Generator().manual_seed(9)
+    B = 5
+    x = torch.rand((B, 3, 224, 224), generator=g)
+    x = (x > 0.93).float() * 0.9 + 0.05 * torch.rand((B, 3, 224, 224), generator=g)   # sparse bright pixels on a dark field
+    eps = torch.randn((B, 4, 28, 28), generator=g)
+    z_ref, kl_ref, _, _ = R.vae_encode(vsd, x, eps)
+    rec_ref = R.vae_decode(vsd, z_ref)
+    mse_ref = F.mse_loss(rec_ref, x, reduction="mean")
+    x_recon, z, loss, parts = vae(x.to(DEV), eps.to(DEV))
+    assert set(parts) == {"recon_mse", "kl"} and loss.dim() == 0 and not loss.requires_grad
+    m = max_abs(x_recon.cpu(), rec_ref)
+    r_mse = abs(float(parts["recon_mse"]) - float(mse_ref)) / float(mse_ref)
+    r_kl = abs(float(parts["kl"]) - float(kl_ref)) / abs(float(kl_ref))
+    report("vae_forward", {"recon_max_abs": m, "mse_rel": r_mse, "kl_rel": r_kl, "z_rel_l2": rel_l2(z.cpu(), z_ref)})
+    assert m <= 1.2e-2 and r_mse <= 3e-2 and r_kl <= 3e-2 and rel_l2(z.cpu(), z_ref) <= 3e-2
+    assert abs(float(loss) - (float(parts["recon_mse"]) + 1e-6 * float(parts["kl"]))) <= 1e-6 * abs(float(loss))
+    # the reduction itself: exact against float64 torch on the tensors the device produced, and repeatable
+    from dmb200 import context_for
+    ctx = context_for(DEV)
+    sq, ab = ctx.recon_error(x_recon, x.to(DEV))
+    d = (x_recon.double() - x.to(DEV).double())
+    assert torch.allclose(sq, (d * d).flatten(1).sum(1), rtol=1e-12, atol=0)
+    assert torch.allclose(ab, d.abs().flatten(1).sum(1), rtol=1e-12, atol=0)
+    sq2, ab2 = ctx.recon_error(x_recon, x.to(DEV))
+    assert torch.equal(sq, sq2) and torch.equal(ab, ab2)
+    odd_a, odd_b = torch.rand((3, 1001), device=DEV), torch.rand((3, 1001), device=DEV)     # ragged: scalar path
+    sq3, _ = ctx.recon_error(odd_a, odd_b)
+    assert torch.allclose(sq3, ((odd_a.double() - odd_b.double()) ** 2).sum(1), rtol=1e-12, atol=0)
+    # vae_recon_check.py:25-31 -- per-image figures from the same calls the script makes
+    z_enc, _ = vae.encode(x.to(DEV), eps.to(DEV))
+    x_rec = vae.decode(z_enc)
+    mse = torch.mean((x_rec - x.to(DEV)) ** 2, dim=(1, 2, 3)).cpu()
+    mse_o = torch.mean((rec_ref - x) ** 2, dim=(1, 2, 3))
+    assert torch.allclose(mse, mse_o, rtol=3e-2)
+
+
+def test_vae_forward_refuses_a_training_step(vae_pair):
+    vae, _ = vae_pair
+    x = torch.rand((1, 3, 224, 224), device=DEV)
+    vae.train()
+    try:
+        with pytest.raises(NotImplementedError):
+            vae(x)
+        with torch.no_grad():
+            assert vae(x)[0].shape == (1, 3, 224, 224)
+    finally:
+        vae.eval()

@@ -339,6 +339,32 @@ def test_fused_kernels_agree_with_separate_launches(models, switch):
     assert r < 1e-2, (switch, r)
 
 
+@pytest.mark.parametrize("B", [3, 32])
+def test_planar_conv_transpose_is_bit_identical(models, B):
+    """VAE decoder: the phase-planar ConvTranspose output (four phase GEMMs through the TMA-store epilogue,
+    moved to their 2H x 2W pixels by the GroupNorm pass) holds exactly the numbers the
+    scattered form stores; the passes downstream are the same kernels reading the same values in the
+    same order, so the decoded images must be equal bit for bit.  B = 3 runs the narrowed tiles (the
+    per-thread store path of the epilogue), B = 32 the full chunk."""
+    vae = models[1]
+    g = torch.Generator().manual_seed(21)
+    z = torch.randn((B, 4, 28, 28), generator=g).cuda()
+    outs = []
+    for val in ("1", "0"):
+        ctx = _fresh_context({"DMB200_CONVT_PLANAR": val})
+        try:
+            ctx.ensure_vae(vae)
+            ctx.reset_launch_count()
+            img, u8 = ctx.vae_decode(z, want_f32=True, want_u8=True)
+            torch.cuda.synchronize()
+            outs.append((img.cpu(), u8.cpu(), ctx.launch_count()))
+        finally:
+            ctx.close()
+    assert outs[0][2] == outs[1][2], (outs[0][2], outs[1][2])
+    assert torch.equal(outs[0][1], outs[1][1])
+    assert torch.equal(outs[0][0], outs[1][0])
+
+
 def test_weight_sets_are_independent(golden, models):
     """Loading the U-Net after the VAE (or the other way round) must not drop the other's weights:
     decode, reload the U-Net in a fresh context, decode again."""

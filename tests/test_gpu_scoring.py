@@ -120,3 +120,52 @@ def test_scores_the_decoded_batch_in_place(golden):
     u8_h, gt_h = u8.cpu().numpy(), gt.cpu().numpy()
     for b in range(8):
         _same(got[b], R.compute_metrics(R.binarise(gt_h[b]), R.binarise(u8_h[b])))
+
+
+def test_command_line_run_directory(tmp_path, capsys):
+    """eval_iou_noise.py's command line (eval_iou_noise.py:303-482) on the GPU scorer: ground truth
+    p00000.jpg ... against pic1.png ..., one pair missing, two image sizes.  Every row of
+    metrics_detail.csv must equal the oracle's compute_metrics on the masks the reference's
+    load_binary_mask gives for the same files; the summary row and the run directory's layout are
+    the reference's."""
+    import pandas as pd
+    from PIL import Image
+    import eval_iou_noise as E
+    rng = np.random.default_rng(11)
+    gt_dir, gen_dir, out = tmp_path / "gt", tmp_path / "gen", tmp_path / "out"
+    gt_dir.mkdir(); gen_dir.mkdir()
+    sizes = [(224, 224)] * 5 + [(64, 96)] * 2
+    for i, (H, W) in enumerate(sizes):
+        gt = _line_mask(rng, H, W, 1 + i % 3)
+        pred = _line_mask(rng, H, W, 1 + i % 3, jitter=1) | (rng.random((H, W)) < 0.004 * i)
+        grey = np.where(gt, 20, 235).astype(np.uint8)                                  # dark strokes on white
+        Image.fromarray(grey, mode="L").save(gt_dir / f"p{i:05d}.jpg", quality=92)      # (JPEG: ringing near the strokes)
+        if i != 3:                                                                     # p00003 has no partner
+            rgb = np.stack([np.where(pred, 30, 250)] * 3, -1).astype(np.uint8)
+            rgb[..., 1] = np.clip(rgb[..., 1].astype(int) + rng.integers(-20, 20, (H, W)), 0, 255)
+            Image.fromarray(rgb, mode="RGB").save(gen_dir / f"pic{i + 1}.png")
+    run_dir = E.main(["--gt_dir", str(gt_dir), "--gen_dir", str(gen_dir), "--out_dir", str(out), "--invert",
+                      "--sigma", "2.5", "--save_diff"], device=DEV)
+    assert run_dir.parent == out and run_dir.name.startswith("run_")
+    detail = pd.read_csv(run_dir / "metrics_detail.csv", encoding="utf-8-sig")
+    summary = pd.read_csv(run_dir / "metrics_summary.csv", encoding="utf-8-sig")
+    assert list(detail.columns) == ["gt_index", "gt_file", "gen_file", "gt_bin", "gen_bin", "pair_bin", "diff_bin", "iou",
+                                    "gt_iou", "far_noise_ratio", "gauss_recall", "inter", "union", "gt_area", "pred_area", "fp"]
+    assert list(detail["gt_index"]) == [0, 1, 2, 4, 5, 6]
+    for _, row in detail.iterrows():
+        gt = E.load_binary_mask(gt_dir / row["gt_file"], threshold=128, invert=True)
+        pred = E.load_binary_mask(gen_dir / row["gen_file"], threshold=128, invert=True)
+        _same({k: float(row[k]) for k in EXACT + ("gauss_recall",)}, R.compute_metrics(gt, pred, sigma=2.5))
+        assert np.array_equal(np.array(Image.open(run_dir / row["gt_bin"])) == 255, gt)
+        assert np.array_equal(np.array(Image.open(run_dir / row["gen_bin"])) == 255, pred)
+        assert (run_dir / row["pair_bin"]).name == f"pair_gt{int(row['gt_index']):05d}_vs_pic{int(row['gt_index']) + 1}.png"
+        assert (run_dir / row["diff_bin"]).is_file()
+    s = summary.iloc[0]
+    assert int(s["n_pairs"]) == 6 and int(s["missing_pairs_skipped"]) == 1 and float(s["sigma"]) == 2.5 and bool(s["invert"])
+    assert abs(float(s["iou_mean"]) - detail["iou"].mean()) < 1e-12
+    assert abs(float(s["gauss_recall_p90"]) - np.percentile(detail["gauss_recall"], 90)) < 1e-12
+    cfg = dict(line.split("=", 1) for line in (run_dir / "config.txt").read_text().splitlines())
+    assert list(cfg) == ["gt_dir", "gen_dir", "threshold", "invert", "sigma", "distance_backend", "max_pairs",
+                         "save_diff", "missing_pairs_skipped"] and cfg["missing_pairs_skipped"] == "1"
+    assert "[OK] run_dir:" in capsys.readouterr().out
+    report("eval_cli", {"pairs": 6, "iou_mean": float(s["iou_mean"])})

@@ -251,3 +251,98 @@ def test_png_batch_writer_round_trips_pixels(tmp_path):
     from dmb200 import NativeError
     with pytest.raises(NativeError):
         write_png_batch(grey[:1], [str(tmp_path / "no_such_dir" / "x.png")])
+
+
+# ---- eval_iou_noise.py command line: host logic (pairing, summary row, visuals); the scoring itself is a GPU test ----
+
+REF_SUMMARY_COLUMNS = ["n_pairs", "missing_pairs_skipped", "threshold", "invert", "sigma", "distance_backend",
+                       "iou_mean", "iou_std", "gt_iou_mean", "gt_iou_std",
+                       "far_noise_ratio_mean", "far_noise_ratio_std", "far_noise_ratio_median",
+                       "far_noise_ratio_p90", "far_noise_ratio_p95", "gauss_recall_mean", "gauss_recall_std",
+                       "gauss_recall_median", "gauss_recall_p90", "gauss_recall_p95", "gauss_overdraw_rate_gt1",
+                       "run_dir"]   # eval_iou_noise.py:413-447, in order
+
+
+def test_eval_cli_pairs_files_like_the_reference(tmp_path):
+    """p00000.jpg <-> pic1.png, p00001.jpg <-> pic2.png ...; other names are ignored, case is not
+    (eval_iou_noise.py:34-71, 346-361)."""
+    import eval_iou_noise as E
+    gt, gen = tmp_path / "gt", tmp_path / "gen"
+    gt.mkdir(); gen.mkdir()
+    for n in ["p00002.jpg", "p00000.jpg", "P00001.JPG", "p00007.jpg", "q00003.jpg", "p00004.png", "p5.jpg.bak"]:
+        (gt / n).write_bytes(b"")
+    for n in ["pic3.png", "pic1.png", "PIC2.PNG", "pic10.png", "pic_4.png", "pic5.jpg"]:
+        (gen / n).write_bytes(b"")
+    (gt / "p00009.jpg").mkdir()   # a directory with a matching name is not a file
+    assert [i for i, _ in E.list_gt_files(gt)] == [0, 1, 2, 7]
+    assert [i for i, _ in E.list_gen_files(gen)] == [1, 2, 3, 10]
+    assert E._extract_gt_index("p00012.jpg") == 12 and E._extract_gt_index("p12.jpeg") is None
+    assert E._extract_gen_index("pic7.png") == 7 and E._extract_gen_index("pic7.PNG") == 7
+    pairs, missing = E.pair_files(gt, gen)
+    assert [(i, a.name, b.name) for i, a, b in pairs] == [(0, "p00000.jpg", "pic1.png"), (1, "P00001.JPG", "PIC2.PNG"),
+                                                           (2, "p00002.jpg", "pic3.png")]
+    assert missing == 1   # p00007 has no pic8
+    assert len(E.pair_files(gt, gen, max_pairs=2)[0]) == 2
+    assert len(E.pair_files(gt, gen, max_pairs=0)[0]) == 3 and len(E.pair_files(gt, gen, max_pairs=-1)[0]) == 3
+    if load_reference.available():
+        with load_reference.reference_modules() as ref:
+            ref_gt = [(i, p.name) for i, p in ref.eval_iou_noise.list_gt_files(gt)]
+            ref_gen = [(i, p.name) for i, p in ref.eval_iou_noise.list_gen_files(gen)]
+        assert ref_gt == [(i, p.name) for i, p in E.list_gt_files(gt)]
+        assert ref_gen == [(i, p.name) for i, p in E.list_gen_files(gen)]
+
+
+def test_eval_cli_summary_row_and_statistics(tmp_path):
+    import eval_iou_noise as E
+    rng = np.random.default_rng(3)
+    detail = [{"iou": float(a), "gt_iou": float(b), "far_noise_ratio": float(c), "gauss_recall": float(d)}
+              for a, b, c, d in rng.random((37, 4)) * [1, 1, 1, 1.3]]
+    row = E.summarise(detail, missing=2, threshold=128, invert=True, sigma=2.0, run_dir=tmp_path)
+    assert list(row) == REF_SUMMARY_COLUMNS
+    gr = np.array([r["gauss_recall"] for r in detail])
+    fn = np.array([r["far_noise_ratio"] for r in detail])
+    assert row["n_pairs"] == 37 and row["missing_pairs_skipped"] == 2
+    assert row["gauss_recall_mean"] == float(gr.mean()) and row["gauss_recall_std"] == float(gr.std(ddof=0))
+    assert row["gauss_recall_p90"] == float(np.percentile(gr, 90)) and row["far_noise_ratio_median"] == float(np.percentile(fn, 50))
+    assert row["gauss_overdraw_rate_gt1"] == float((gr > 1.0).mean())
+    assert all(np.isnan(v) for v in E.mean_std(np.array([])))
+    assert np.isnan(E.overdraw_rate(np.array([]))) and np.isnan(E.quantiles(np.array([]), [50])["p50"])
+    if load_reference.available():
+        with load_reference.reference_modules() as ref:
+            r = ref.eval_iou_noise
+            want = (r.mean_std(gr), r.quantiles(fn, [50, 90, 95]), r.overdraw_rate(gr, 1.0))
+        assert want == (E.mean_std(gr), E.quantiles(fn, [50, 90, 95]), E.overdraw_rate(gr, 1.0))
+
+
+def test_eval_cli_visuals(tmp_path):
+    """binarised / side-by-side / difference images: same pixels as the reference writes (:97-156)."""
+    from PIL import Image
+    import eval_iou_noise as E
+    rng = np.random.default_rng(4)
+    gt, gen = rng.random((20, 30)) < 0.3, rng.random((20, 30)) < 0.3
+    E.save_side_by_side(gt, gen, tmp_path / "pair.png")
+    E.save_diff_visual(gt, gen, tmp_path / "diff.png")
+    pair = np.array(Image.open(tmp_path / "pair.png"))
+    assert pair.shape == (20, 60) and np.array_equal(pair[:, :30] == 255, gt) and np.array_equal(pair[:, 30:] == 255, gen)
+    diff = np.array(Image.open(tmp_path / "diff.png"))
+    assert (diff[gt & gen] == [0, 0, 0]).all() and (diff[gt & ~gen] == [0, 0, 255]).all()
+    assert (diff[~gt & gen] == [255, 0, 0]).all() and (diff[~gt & ~gen] == [255, 255, 255]).all()
+    small = rng.random((10, 15)) < 0.5
+    E.save_side_by_side(gt, small, tmp_path / "pair2.png")           # other size: resized for display
+    assert np.array(Image.open(tmp_path / "pair2.png")).shape == (20, 60)
+    if load_reference.available():
+        with load_reference.reference_modules() as ref:
+            ref.eval_iou_noise.save_side_by_side(gt, gen, tmp_path / "rpair.png")
+            ref.eval_iou_noise.save_diff_visual(gt, gen, tmp_path / "rdiff.png")
+        assert np.array_equal(np.array(Image.open(tmp_path / "rpair.png")), pair)
+        assert np.array_equal(np.array(Image.open(tmp_path / "rdiff.png")), diff)
+
+
+def test_eval_cli_errors(tmp_path):
+    import eval_iou_noise as E
+    (tmp_path / "gt").mkdir()
+    with pytest.raises(FileNotFoundError):
+        E.main(["--gt_dir", str(tmp_path / "gt"), "--gen_dir", str(tmp_path / "nope"), "--out_dir", str(tmp_path / "o")])
+    (tmp_path / "gen").mkdir()
+    with pytest.raises(RuntimeError):   # no pairs (:363-369)
+        E.main(["--gt_dir", str(tmp_path / "gt"), "--gen_dir", str(tmp_path / "gen"), "--out_dir", str(tmp_path / "o")])
