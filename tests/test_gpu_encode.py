@@ -246,14 +246,14 @@ def test_vae_forward_matches_oracle(vae_pair):
     from dmb200 import context_for
     ctx = context_for(DEV)
     sq, ab = ctx.recon_error(x_recon, x.to(DEV))
-    d = (x_recon.double() - x.to(DEV).double())
+    d = (x_recon - x.to(DEV)).double()      # the difference in fp32, as the reference forms it; the sums in float64
     assert torch.allclose(sq, (d * d).flatten(1).sum(1), rtol=1e-12, atol=0)
     assert torch.allclose(ab, d.abs().flatten(1).sum(1), rtol=1e-12, atol=0)
     sq2, ab2 = ctx.recon_error(x_recon, x.to(DEV))
     assert torch.equal(sq, sq2) and torch.equal(ab, ab2)
     odd_a, odd_b = torch.rand((3, 1001), device=DEV), torch.rand((3, 1001), device=DEV)     # ragged: scalar path
     sq3, _ = ctx.recon_error(odd_a, odd_b)
-    assert torch.allclose(sq3, ((odd_a.double() - odd_b.double()) ** 2).sum(1), rtol=1e-12, atol=0)
+    assert torch.allclose(sq3, ((odd_a - odd_b).double() ** 2).sum(1), rtol=1e-12, atol=0)
     # vae_recon_check.py:25-31 -- per-image figures from the same calls the script makes
     z_enc, _ = vae.encode(x.to(DEV), eps.to(DEV))
     x_rec = vae.decode(z_enc)

@@ -340,12 +340,15 @@ def test_fused_kernels_agree_with_separate_launches(models, switch):
 
 
 @pytest.mark.parametrize("B", [3, 32])
-def test_planar_conv_transpose_is_bit_identical(models, B):
+def test_planar_conv_transpose_agrees_with_scatter(models, B):
     """VAE decoder: the phase-planar ConvTranspose output (four phase GEMMs through the TMA-store epilogue,
     moved to their 2H x 2W pixels by the GroupNorm pass) holds exactly the numbers the
-    scattered form stores; the passes downstream are the same kernels reading the same values in the
-    same order, so the decoded images must be equal bit for bit.  B = 3 runs the narrowed tiles (the
-    per-thread store path of the epilogue), B = 32 the full chunk."""
+    scattered form stores (checked element by element when it was built).  The GroupNorm statistics pass
+    then sums the same numbers in another order (it streams memory, and the two layouts order it
+    differently), so mean / rstd move in the last fp32 bits and a few bf16 roundings downstream flip:
+    the decoded images agree to that level -- measured 1e-3, far inside the decoder's 6e-3 parity
+    tolerance -- not bit for bit.  B = 3 runs the narrowed tiles (the per-thread store path of the
+    epilogue), B = 32 the full chunk."""
     vae = models[1]
     g = torch.Generator().manual_seed(21)
     z = torch.randn((B, 4, 28, 28), generator=g).cuda()
@@ -361,8 +364,11 @@ def test_planar_conv_transpose_is_bit_identical(models, B):
         finally:
             ctx.close()
     assert outs[0][2] == outs[1][2], (outs[0][2], outs[1][2])
-    assert torch.equal(outs[0][1], outs[1][1])
-    assert torch.equal(outs[0][0], outs[1][0])
+    m = float((outs[0][0] - outs[1][0]).abs().max())
+    du8 = int((outs[0][1].int() - outs[1][1].int()).abs().max())
+    report(f"variant_DMB200_CONVT_PLANAR_B{B}", {"max_abs": m, "u8_max_diff": du8,
+                                                 "u8_frac_diff": float((outs[0][1] != outs[1][1]).float().mean())})
+    assert m <= 3e-3 and du8 <= 1, (m, du8)
 
 
 def test_weight_sets_are_independent(golden, models):

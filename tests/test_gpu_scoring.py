@@ -147,8 +147,8 @@ def test_command_line_run_directory(tmp_path, capsys):
     run_dir = E.main(["--gt_dir", str(gt_dir), "--gen_dir", str(gen_dir), "--out_dir", str(out), "--invert",
                       "--sigma", "2.5", "--save_diff"], device=DEV)
     assert run_dir.parent == out and run_dir.name.startswith("run_")
-    detail = pd.read_csv(run_dir / "metrics_detail.csv", encoding="utf-8-sig")
-    summary = pd.read_csv(run_dir / "metrics_summary.csv", encoding="utf-8-sig")
+    detail = pd.read_csv(run_dir / "metrics_detail.csv", encoding="utf-8-sig", float_precision="round_trip")
+    summary = pd.read_csv(run_dir / "metrics_summary.csv", encoding="utf-8-sig", float_precision="round_trip")
     assert list(detail.columns) == ["gt_index", "gt_file", "gen_file", "gt_bin", "gen_bin", "pair_bin", "diff_bin", "iou",
                                     "gt_iou", "far_noise_ratio", "gauss_recall", "inter", "union", "gt_area", "pred_area", "fp"]
     assert list(detail["gt_index"]) == [0, 1, 2, 4, 5, 6]
