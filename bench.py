@@ -489,9 +489,21 @@ def run_native(args):
         raise SystemExit("bench.py --impl native needs a B200: the product has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
     B, T = args.batch, args.T
+    # The CPU legs run FIRST, on rank 0, before this job holds a CUDA context or an NCCL communicator:
+    # ranks that wait in an NCCL barrier poll with several host threads each, and an OpenMP workload
+    # that shares cores with pollers loses a scheduler time slice at every parallel region (measured at
+    # N = 2 with the legs at the end of the run: 4429 instead of 196 ms per step).  The other ranks wait
+    # in the process group's rendezvous, which blocks on a socket.
+    cpu = cpu_b1 = None
+    if rank == 0 and not args.no_cpu_baseline:
+        cpu = cpu_leg("baseline", batch=min(B, 16), n_steps=args.cpu_sample_steps, T=T, guidance=args.guidance)
+        if not args.no_extras:
+            # config 1 run outright on a 1-GPU launch (about a minute); bounded under torchrun
+            cpu_b1 = cpu_leg("config1", T=T, guidance=args.guidance, n_steps=None if world == 1 else 20)
+    if world > 1:
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(minutes=30))
     peaks, peak_src = load_peaks()
 
     torch.manual_seed(0)
@@ -706,14 +718,8 @@ def run_native(args):
     if args.config4_batch > 0:
         config4 = run_config4(args, ctx, dev, world, rank, T, coef, barrier)
 
-    cpu = cpu_b1 = None
-    if rank == 0 and not args.no_cpu_baseline:
-        cpu = cpu_leg("baseline", batch=min(B, 16), n_steps=args.cpu_sample_steps, T=T, guidance=args.guidance)
-        if not args.no_extras:
-            # config 1 run outright on a 1-GPU launch (about a minute); bounded under torchrun
-            cpu_b1 = cpu_leg("config1", T=T, guidance=args.guidance, n_steps=None if world == 1 else 20)
-            if batch1 is not None:
-                batch1["cpu_ms_per_denoise_step"] = cpu_b1["ms_per_denoise_step"]
+    if cpu_b1 is not None and batch1 is not None:
+        batch1["cpu_ms_per_denoise_step"] = cpu_b1["ms_per_denoise_step"]
 
     if rank == 0:
         line = {
