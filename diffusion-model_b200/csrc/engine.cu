@@ -290,6 +290,10 @@ class Engine : public IEngine {
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 3, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 3, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     {
       const char* pe3 = getenv("DMB200_PIX");
       pix_mode_ = !(pe3 && pe3[0] == '0');
@@ -298,6 +302,7 @@ class Engine : public IEngine {
       if (const char* e = getenv("DMB200_PIX_MAXHW")) pix_max_hw_ = atoi(e);
       const char* re = getenv("DMB200_ROW3");   // 0: nine separate A tiles per K chunk
       row3_ = re ? atoi(re) : 1;
+      if (const char* e = getenv("DMB200_ROW3_GROUP")) row3_group_ = std::max(0, std::min(3, atoi(e)));
       if (const char* e = getenv("DMB200_CONVT_PLANAR")) convt_planar_ = e[0] != '0';
       if (const char* e = getenv("DMB200_ENC_IN_MMA")) enc_in_mma_ = atoi(e) != 0;
     }
@@ -492,6 +497,7 @@ class Engine : public IEngine {
   int pix_fill_pct_ = 90;              // narrow the N tile while there are fewer tiles than this share of the SMs
   bool pix_mode_ = true;   // DMB200_PIX=0: small maps keep the padded-row GEMM at every batch size
   int row3_ = 1;   // DMB200_ROW3=0: every tap of a 3x3 conv loads its own A tile
+  int row3_group_ = 0;   // DMB200_ROW3_GROUP=1|2|3: kernel-row steps per pipeline stage (0: by N tile)
   bool convt_planar_ = true;   // DMB200_CONVT_PLANAR=0: ConvTranspose phases scatter their rows from registers
   bool use_fused_tail_ = true;   // DMB200_FUSED_TAIL=0: out_proj / LayerNorm / ff1 / ff2 as four launches
   bool use_acc4_ = true;   // DMB200_ACC4=0: two epilogue warpgroups for every launch
@@ -872,9 +878,23 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   const bool row3 = !pix && row3_ && ntaps == 9 && !acc4 && ring / row3_stage >= 3 && shifts[1] == shifts[0] + 1 &&
                     shifts[2] == shifts[1] + 1 && shifts[4] == shifts[3] + 1 && shifts[5] == shifts[4] + 1 &&
                     shifts[7] == shifts[6] + 1 && shifts[8] == shifts[7] + 1;
-  if (row3) group = 1;
+  // kRow3: steps per stage (gemm_tc.cuh).  A step is 12 MMAs = 3 bn cycles; one mbarrier hand-shake costs ~500,
+  // so narrow layers take 3 (bn <= 64) or 2 (bn = 128) steps per stage while at least three stages still fit.
+  // (Weights resident in shared memory for the whole launch were measured twice, alone and with this grouping:
+  // slower -- the A ring loses the stages the weights take; profiles/r2_experiment_resident_weights.patch.)
+  if (row3) {
+    const int n3 = 3 * p.k_chunks;
+    const int want = row3_group_ > 0 ? row3_group_ : std::min(3, cdiv(512, 3 * bn));
+    int cand[4], nc = 0;   // step counts in order of preference (n3 = 3 k_chunks: 2 divides it only for even k_chunks)
+    if (want == 2 && n3 % 2 != 0) cand[nc++] = 3;
+    for (int g = want; g >= 1; --g)
+      if (n3 % g == 0) cand[nc++] = g;
+    group = 1;
+    for (int i = 0; i < nc; ++i)
+      if (ring / (cand[i] * row3_stage) >= 3) { group = cand[i]; break; }
+  }
   p.group = group;
-  const int stage_bytes = row3 ? row3_stage : group * pair_bytes;
+  const int stage_bytes = row3 ? group * row3_stage : group * pair_bytes;
   p.stages = std::min(kMaxStages, ring / stage_bytes);
   p.idesc = umma_idesc(ElemTraits<T>::kFmt, kTileM * ctas, bn);
   p.tmem_cols = tmem_cols_for(bn * n_acc / 2);
@@ -896,7 +916,9 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = use_pdl_ ? 2 : 1;
-    if (row3) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1, 2, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
+    if (row3 && group == 3) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 3, 2, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
+    else if (row3 && group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2, 2, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
+    else if (row3) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1, 2, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
     else if (group == 1) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1>, ta, w.tmap_for(bn / 2), tout, p));
     else if (group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2>, ta, w.tmap_for(bn / 2), tout, p));
     else DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 4>, ta, w.tmap_for(bn / 2), tout, p));
@@ -908,7 +930,9 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
       else if (group == 2) launch(gemm_tc_kernel<T, 1, 2, 4>, grid, kT4, smem, s, ta, w.tmap_for(bn), tout, p);
       else launch(gemm_tc_kernel<T, 1, 4, 4>, grid, kT4, smem, s, ta, w.tmap_for(bn), tout, p);
     } else if (row3) {
-      launch(gemm_tc_kernel<T, 1, 1, 2, true>, grid, kGemmThreads, smem, s, a.tmap_halo, w.tmap_for(bn), tout, p);
+      if (group == 3) launch(gemm_tc_kernel<T, 1, 3, 2, true>, grid, kGemmThreads, smem, s, a.tmap_halo, w.tmap_for(bn), tout, p);
+      else if (group == 2) launch(gemm_tc_kernel<T, 1, 2, 2, true>, grid, kGemmThreads, smem, s, a.tmap_halo, w.tmap_for(bn), tout, p);
+      else launch(gemm_tc_kernel<T, 1, 1, 2, true>, grid, kGemmThreads, smem, s, a.tmap_halo, w.tmap_for(bn), tout, p);
     } else
     if (group == 1) launch(gemm_tc_kernel<T, 1, 1>, grid, kGemmThreads, smem, s, ta, w.tmap_for(bn), tout, p);
     else if (group == 2) launch(gemm_tc_kernel<T, 1, 2>, grid, kGemmThreads, smem, s, ta, w.tmap_for(bn), tout, p);

@@ -158,12 +158,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const uint32_t a_bytes = kTileM * 128;
   const uint32_t b_bytes = static_cast<uint32_t>(p.block_n / kCtas) * 128;
   const uint32_t pair_bytes = a_bytes + b_bytes;                       // one (tap, K chunk) operand pair
-  const uint32_t stage_bytes = kRow3 ? kHaloBytes + 3u * b_bytes : static_cast<uint32_t>(kGroup) * pair_bytes;
+  // kRow3: a stage = kGroup consecutive (kernel row, K chunk) steps -- a 130-row A window and the three weight
+  // tiles of the row's taps each.  One mbarrier hand-shake costs the issuing warps ~500 cycles and a step is only
+  // 12 MMAs (3 N cycles), so narrow layers take 3 or 2 steps per hand-shake: where a launch has few tiles per
+  // CTA (batch 1; the 64 -> 3 output conv of the VAE) the chain of hand-shakes is what it waits for.
+  const uint32_t step_bytes = kHaloBytes + 3u * b_bytes;
+  const uint32_t stage_bytes = kRow3 ? static_cast<uint32_t>(kGroup) * step_bytes : static_cast<uint32_t>(kGroup) * pair_bytes;
   // shared memory: [stage ring][epilogue staging]; kRow3: [staging][weight tiles of all stages][A windows]
   const uint32_t staging_bytes = p.tma_store ? static_cast<uint32_t>(gemm_staging_bytes(kAcc)) : 0u;
   uint8_t* staging = kRow3 ? smem : smem + static_cast<size_t>(p.stages) * stage_bytes;  // 1024-aligned (stage_bytes % 1024 == 0)
-  uint8_t* ring_b = smem + staging_bytes;                                       // kRow3: 3 weight tiles per stage
-  uint8_t* ring_a = ring_b + static_cast<size_t>(p.stages) * 3u * b_bytes;      // kRow3: one window per stage
+  uint8_t* ring_b = smem + staging_bytes;                                          // kRow3: 3 weight tiles per step
+  uint8_t* ring_a = ring_b + static_cast<size_t>(p.stages) * kGroup * 3u * b_bytes;  // kRow3: one window per step
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -228,29 +233,35 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
       };
       if constexpr (kRow3) {
-        // stage = (kernel row dy, K chunk): the 130-row window + the weight tiles of its three taps
+        // step = (kernel row dy, K chunk): the 130-row window + the weight tiles of its three taps; kGroup steps per stage
         int dy = 0, kc = 0;
-        for (int it = 0; it < 3 * p.k_chunks; ++it) {
-          const int a_row = m0 + p.a_shift[3 * dy + 1] - 1;
-          const int k_col = kc * Tr::kChunkK;
-          const int b0 = p.b_row[3 * dy] + n0, b1 = p.b_row[3 * dy + 1] + n0, b2 = p.b_row[3 * dy + 2] + n0;
-          if (++kc == p.k_chunks) { kc = 0; ++dy; }
-          uint8_t* sa = ring_a + stage * kHaloBytes;
-          uint8_t* sb = ring_b + stage * 3u * b_bytes;
+        for (int it0 = 0; it0 < 3 * p.k_chunks; it0 += kGroup) {
+          uint8_t* sa0 = ring_a + stage * (kGroup * kHaloBytes);
+          uint8_t* sb0 = ring_b + stage * (kGroup * 3u) * b_bytes;
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          if (elect_one()) {
-            if (kCtas == 1 || rank == 0) mbar_expect_tx(&full_bar[stage], stage_bytes * kCtas);
-            if constexpr (kCtas == 2) {
-              const uint32_t lead_bar = lead_full0 + stage * 8;
-              tma_load_2d_pair(sa, &tmap_a, lead_bar, k_col, a_row);
-              tma_load_2d_pair(sb, &tmap_b, lead_bar, k_col, b0);
-              tma_load_2d_pair(sb + b_bytes, &tmap_b, lead_bar, k_col, b1);
-              tma_load_2d_pair(sb + 2 * b_bytes, &tmap_b, lead_bar, k_col, b2);
-            } else {
-              tma_load_2d(sa, &tmap_a, &full_bar[stage], k_col, a_row);
-              tma_load_2d(sb, &tmap_b, &full_bar[stage], k_col, b0);
-              tma_load_2d(sb + b_bytes, &tmap_b, &full_bar[stage], k_col, b1);
-              tma_load_2d(sb + 2 * b_bytes, &tmap_b, &full_bar[stage], k_col, b2);
+          const bool issue = elect_one();
+          if (issue && (kCtas == 1 || rank == 0)) mbar_expect_tx(&full_bar[stage], stage_bytes * kCtas);
+#pragma unroll
+          for (int gi = 0; gi < kGroup; ++gi) {
+            const int a_row = m0 + p.a_shift[3 * dy + 1] - 1;
+            const int k_col = kc * Tr::kChunkK;
+            const int b0 = p.b_row[3 * dy] + n0, b1 = p.b_row[3 * dy + 1] + n0, b2 = p.b_row[3 * dy + 2] + n0;
+            if (++kc == p.k_chunks) { kc = 0; ++dy; }
+            uint8_t* sa = sa0 + gi * kHaloBytes;
+            uint8_t* sb = sb0 + gi * 3u * b_bytes;
+            if (issue) {
+              if constexpr (kCtas == 2) {
+                const uint32_t lead_bar = lead_full0 + stage * 8;
+                tma_load_2d_pair(sa, &tmap_a, lead_bar, k_col, a_row);
+                tma_load_2d_pair(sb, &tmap_b, lead_bar, k_col, b0);
+                tma_load_2d_pair(sb + b_bytes, &tmap_b, lead_bar, k_col, b1);
+                tma_load_2d_pair(sb + 2 * b_bytes, &tmap_b, lead_bar, k_col, b2);
+              } else {
+                tma_load_2d(sa, &tmap_a, &full_bar[stage], k_col, a_row);
+                tma_load_2d(sb, &tmap_b, &full_bar[stage], k_col, b0);
+                tma_load_2d(sb + b_bytes, &tmap_b, &full_bar[stage], k_col, b1);
+                tma_load_2d(sb + 2 * b_bytes, &tmap_b, &full_bar[stage], k_col, b2);
+              }
             }
           }
           __syncwarp();
@@ -315,27 +326,35 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         const uint32_t d_tmem = tmem_base + as * p.block_n;
         const int n_iter = (!kRow3 && p.pix) ? pix_tile(p, tile).ntap * p.k_chunks : n_iter_all;
         if constexpr (kRow3) {
-          const int n3 = 3 * p.k_chunks;
-          for (int it = 0; it < n3; ++it) {
-            const uint64_t adesc0 = umma_desc_sw128(smem_u32(ring_a + stage * kHaloBytes));
-            const uint64_t bdesc0 = umma_desc_sw128(smem_u32(ring_b + stage * 3u * b_bytes));
-            const uint64_t bstep = static_cast<uint64_t>(b_bytes >> 4);
+          const int n3 = 3 * p.k_chunks;   // a multiple of kGroup (host)
+          for (int it0 = 0; it0 < n3; it0 += kGroup) {
+            const uint32_t sa0 = smem_u32(ring_a + stage * (kGroup * kHaloBytes));
+            const uint32_t sb0 = smem_u32(ring_b + stage * (kGroup * 3u) * b_bytes);
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
-            if (elect_one()) {
+            const bool issue = elect_one();
 #pragma unroll
-              for (int dx = 0; dx < 3; ++dx) {
-                // window rows dx .. dx + 127: start address + 128 dx bytes (16-byte units)
-                const uint64_t ad = adesc0 + static_cast<uint64_t>(dx * 8);
+            for (int gi = 0; gi < kGroup; ++gi) {
+              const uint64_t adesc0 = umma_desc_sw128(sa0 + gi * kHaloBytes);
+              const uint64_t bdesc0 = umma_desc_sw128(sb0 + gi * 3u * b_bytes);
+              const uint64_t bstep = static_cast<uint64_t>(b_bytes >> 4);
+              if (issue) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                  const uint32_t acc = (it > 0 || dx > 0 || k > 0) ? 1u : 0u;
-                  if constexpr (kCtas == 2) umma_ss_pair<Tr::kTf32>(d_tmem, ad + (k * 2), bdesc0 + dx * bstep + (k * 2), p.idesc, acc);
-                  else umma_ss<Tr::kTf32>(d_tmem, ad + (k * 2), bdesc0 + dx * bstep + (k * 2), p.idesc, acc);
+                for (int dx = 0; dx < 3; ++dx) {
+                  // window rows dx .. dx + 127: start address + 128 dx bytes (16-byte units)
+                  const uint64_t ad = adesc0 + static_cast<uint64_t>(dx * 8);
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) {
+                    const uint32_t acc = (it0 + gi > 0 || dx > 0 || k > 0) ? 1u : 0u;
+                    if constexpr (kCtas == 2) umma_ss_pair<Tr::kTf32>(d_tmem, ad + (k * 2), bdesc0 + dx * bstep + (k * 2), p.idesc, acc);
+                    else umma_ss<Tr::kTf32>(d_tmem, ad + (k * 2), bdesc0 + dx * bstep + (k * 2), p.idesc, acc);
+                  }
                 }
               }
+            }
+            if (issue) {
               if constexpr (kCtas == 2) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
-              if (it == n3 - 1) {
+              if (it0 + kGroup >= n3) {
                 if constexpr (kCtas == 2) umma_commit_pair(&tmem_full_bar[as]); else umma_commit(&tmem_full_bar[as]);
               }
             }
