@@ -294,6 +294,12 @@ class Engine : public IEngine {
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 3, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 3, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 1, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 2, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 1, 3, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 1, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 2, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
+    DMB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<T, 2, 3, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmemMax));
     {
       const char* pe3 = getenv("DMB200_PIX");
       pix_mode_ = !(pe3 && pe3[0] == '0');
@@ -303,6 +309,7 @@ class Engine : public IEngine {
       const char* re = getenv("DMB200_ROW3");   // 0: nine separate A tiles per K chunk
       row3_ = re ? atoi(re) : 1;
       if (const char* e = getenv("DMB200_ROW3_GROUP")) row3_group_ = std::max(0, std::min(3, atoi(e)));
+      if (const char* e = getenv("DMB200_ACC4_CONV")) acc4_conv_ = e[0] != '0';
       if (const char* e = getenv("DMB200_CONVT_PLANAR")) convt_planar_ = e[0] != '0';
       if (const char* e = getenv("DMB200_ENC_IN_MMA")) enc_in_mma_ = atoi(e) != 0;
     }
@@ -498,6 +505,7 @@ class Engine : public IEngine {
   bool pix_mode_ = true;   // DMB200_PIX=0: small maps keep the padded-row GEMM at every batch size
   int row3_ = 1;   // DMB200_ROW3=0: every tap of a 3x3 conv loads its own A tile
   int row3_group_ = 0;   // DMB200_ROW3_GROUP=1|2|3: kernel-row steps per pipeline stage (0: by N tile)
+  bool acc4_conv_ = true;    // DMB200_ACC4_CONV=0: two accumulator stages / epilogue warpgroups for 3x3 convs with N tile <= 64 too
   bool convt_planar_ = true;   // DMB200_CONVT_PLANAR=0: ConvTranspose phases scatter their rows from registers
   bool use_fused_tail_ = true;   // DMB200_FUSED_TAIL=0: out_proj / LayerNorm / ff1 / ff2 as four launches
   bool use_acc4_ = true;   // DMB200_ACC4=0: two epilogue warpgroups for every launch
@@ -855,7 +863,10 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   if (pix) DMB_REQUIRE(p.tma_store == 1, "pixel-major conv needs the TMA-store epilogue");
   const int pair_bytes = kTileM * 128 + (bn / ctas) * 128;   // one (tap, K chunk) operand pair
   // Linear layers (one tap, short K, N tile <= 128): four accumulator stages / epilogue warpgroups
-  const bool acc4 = use_acc4_ && !pair && ntaps == 1 && bn <= 128 && p.tma_store;
+  // ... and the narrow 3x3 convs (N tile <= 64: 576 cycles of MMA per 128-row tile against an epilogue of a few
+  // thousand per warpgroup; 64->64 @28x28 at batch 256: 37.4 -> 31.9 us, same bits)
+  const bool acc4_conv = acc4_conv_ && row3_ && !pix && conv3 && bn <= 64 && p.tma_store;
+  const bool acc4 = use_acc4_ && ((!pair && ntaps == 1 && bn <= 128 && p.tma_store) || acc4_conv);
   const int n_acc = acc4 ? 4 : 2;
   const int staging = p.tma_store ? gemm_staging_bytes(n_acc) : 0;
   const int ring = kGemmSmemMax - 1024 - staging;
@@ -875,7 +886,7 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
   // 3x3 convs: one 130-row A window per (kernel row, K chunk) shared by the row's three taps,
   // when at least three such stages fit (any N tile for CTA pairs, <= 128 otherwise)
   const int row3_stage = static_cast<int>(kHaloBytes) + 3 * (bn / ctas) * 128;
-  const bool row3 = !pix && row3_ && ntaps == 9 && !acc4 && ring / row3_stage >= 3 && shifts[1] == shifts[0] + 1 &&
+  const bool row3 = !pix && row3_ && ntaps == 9 && (!acc4 || acc4_conv) && ring / row3_stage >= 3 && shifts[1] == shifts[0] + 1 &&
                     shifts[2] == shifts[1] + 1 && shifts[4] == shifts[3] + 1 && shifts[5] == shifts[4] + 1 &&
                     shifts[7] == shifts[6] + 1 && shifts[8] == shifts[7] + 1;
   // kRow3: steps per stage (gemm_tc.cuh).  A step is 12 MMAs = 3 bn cycles; one mbarrier hand-shake costs ~500,
@@ -916,7 +927,11 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = use_pdl_ ? 2 : 1;
-    if (row3 && group == 3) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 3, 2, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
+    if (acc4) cfg.blockDim = dim3(gemm_threads(4));
+    if (row3 && acc4 && group == 3) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 3, 4, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
+    else if (row3 && acc4 && group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2, 4, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
+    else if (row3 && acc4) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1, 4, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
+    else if (row3 && group == 3) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 3, 2, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
     else if (row3 && group == 2) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 2, 2, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
     else if (row3) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1, 2, true>, a.tmap_halo, w.tmap_for(bn / 2), tout, p));
     else if (group == 1) DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 1>, ta, w.tmap_for(bn / 2), tout, p));
@@ -924,7 +939,12 @@ void Engine<T>::gemm(const Act<T>& a, const GemmW<T>& w, int phase, const int* s
     else DMB_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<T, 2, 4>, ta, w.tmap_for(bn / 2), tout, p));
   } else {
     const int grid = std::min(p.m_tiles * p.n_tiles, num_sms_);
-    if (acc4) {
+    if (acc4 && row3) {
+      constexpr int kT4 = gemm_threads(4);
+      if (group == 3) launch(gemm_tc_kernel<T, 1, 3, 4, true>, grid, kT4, smem, s, a.tmap_halo, w.tmap_for(bn), tout, p);
+      else if (group == 2) launch(gemm_tc_kernel<T, 1, 2, 4, true>, grid, kT4, smem, s, a.tmap_halo, w.tmap_for(bn), tout, p);
+      else launch(gemm_tc_kernel<T, 1, 1, 4, true>, grid, kT4, smem, s, a.tmap_halo, w.tmap_for(bn), tout, p);
+    } else if (acc4) {
       constexpr int kT4 = gemm_threads(4);
       if (group == 1) launch(gemm_tc_kernel<T, 1, 1, 4>, grid, kT4, smem, s, ta, w.tmap_for(bn), tout, p);
       else if (group == 2) launch(gemm_tc_kernel<T, 1, 2, 4>, grid, kT4, smem, s, ta, w.tmap_for(bn), tout, p);

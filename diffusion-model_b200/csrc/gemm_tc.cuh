@@ -493,11 +493,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                   for (int i = 0; i < 8; ++i) v[8 * j + i] += rv[i];
                 }
               }
-              if constexpr (kHalves == 1) {   // (launches with statistics use two warpgroups)
-                if (p.sample_stats) {
+              if (p.sample_stats) {
 #pragma unroll
-                  for (int j = 0; j < kSubN / 16; ++j) sacc.add(stat_unit16(v + 16 * j));
-                }
+                for (int j = 0; j < kP / 16; ++j) sacc.add(stat_unit16(v + 16 * j));
               }
             } else {
 #pragma unroll
