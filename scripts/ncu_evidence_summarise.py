@@ -1,5 +1,5 @@
 """Turn the CSVs scripts/ncu_evidence.sh brought back into profiles/<tag>_*.md and profiles/roofline_traffic.json.
-usage: python scripts/ncu_evidence_summarise.py <tag>      (e.g. r2_v12)
+usage: python scripts/ncu_evidence_summarise.py <tag> [kernel ...]     (e.g. r2_v13 gemm_tc_kernel)
 one_step.py runs two eager steps: every summary keeps the SECOND step's launches (the first builds plans)."""
 import csv, hashlib, io, json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -43,12 +43,16 @@ notes = {"gemm_tc_kernel": "gemm_tc_kernel: every launch of one CFG step at batc
          "gn1_apply_kernel": "gn1_apply_kernel: every launch of one CFG step at batch 256 (statistics arrive as two 64-bit fixed-point sums per sample).",
          "attention_mma_kernel": "attention_mma_kernel: the attention launches of one CFG step at batch 256 (L = 784, 196, 196, 49, 49 -- L = 9 runs on CUDA cores).",
          "attn_tail": "attn_tail kernels (out-projection + residual + LayerNorm + MLP + residual in one launch; C = 64/128 and the C = 256 form)."}
+only = sys.argv[2:]    # optional: summarise only these kernels (the others keep their earlier captures)
 counts = {}
 for k, note in notes.items():
+    if only and k not in only:
+        continue
     counts[k] = second_half_raw(f"{G}/ev_full_{k}.raw.csv", f"{G}/ev_full2_{k}.raw.csv")
     S.full(f"{G}/ev_full2_{k}.raw.csv", f"{P}/{tag}_ncu_full_{k.replace('_kernel', '')}.md", note)
-S.full(f"{G}/ev_full_score_masks.raw.csv", f"{P}/{tag}_ncu_full_score_masks.md",
-       "score_masks_kernel (dmb_score_masks, 4096 images of 224x224; scripts/bench_scoring.py).")
+if not only or "score_masks" in only:
+    S.full(f"{G}/ev_full_score_masks.raw.csv", f"{P}/{tag}_ncu_full_score_masks.md",
+           "score_masks_kernel (dmb_score_masks, 4096 images of 224x224; scripts/bench_scoring.py).")
 
 rows = list(csv.reader(open(f"{G}/ev_full2_gemm_tc_kernel.raw.csv")))
 hdr, units, data = rows[0], rows[1], rows[2:]
@@ -68,3 +72,31 @@ json.dump({"gemm_tc_kernel_dram_bytes_per_launch": sum(dram) / len(dram), "launc
                    "csrc/gemm_tc.cuh hashes to source_sha16 and a step still has launches_per_step GEMM launches"},
           open(f"{P}/roofline_traffic.json", "w"), indent=1)
 print(n, counts, open(f"{P}/roofline_traffic.json").read())
+
+
+def bench_launches(src, dst):
+    """launch list of the bench command itself (gpu__time_duration.sum only): launches, total time, share per kernel"""
+    import collections, re
+    txt = open(src).read()
+    rows = list(csv.DictReader(io.StringIO(txt[txt.index('"ID"'):])))
+    agg, tot = collections.OrderedDict(), 0.0
+    for r in rows:
+        if r["Metric Name"] != "gpu__time_duration.sum":
+            continue
+        v = float(r["Metric Value"].replace(",", "")) * {"us": 1, "ms": 1e3, "ns": 1e-3}.get(r["Metric Unit"], 1)
+        n = re.sub(r"\(.*", "", r["Kernel Name"]).replace("void ", "").replace("dmb::", "")
+        a = agg.setdefault(n, [0, 0.0]); a[0] += 1; a[1] += v; tot += v
+    ours = sum(v[1] for k, v in agg.items() if not k.startswith("at::") and "nccl" not in k and "cub::" not in k)
+    with open(dst, "w") as f:
+        f.write("# ncu launch list of the bench command (`--metrics gpu__time_duration.sum --clock-control none`)\n\n"
+                "command: `python bench.py --steps 1 --warmup 3 --T 4 --no-cpu-baseline --no-extras` (after the same command exited 0 "
+                "without ncu; first 3000 launches).  Times are cold-cache and serialised: compare SHARES with the bench line's kernel "
+                "groups, not absolutes.\n\n"
+                f"{sum(v[0] for v in agg.values())} launches, {tot / 1e3:.1f} ms total; the repo's own kernels: {100 * ours / tot:.1f} % of the time\n\n"
+                "| kernel | launches | total us | share |\n|---|---:|---:|---:|\n")
+        for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            f.write(f"| `{k[:100]}` | {v[0]} | {v[1]:.1f} | {100 * v[1] / tot:.1f}% |\n")
+
+
+if os.path.exists(f"{G}/ev_bench_launches.csv"):
+    bench_launches(f"{G}/ev_bench_launches.csv", f"{P}/{tag}_ncu_bench_launches.md")
