@@ -38,6 +38,42 @@ struct TailParams {
   const float* b2;     // ff_self.3 bias
 };
 
+// Epilogue arithmetic on register PAIRS (fp32x2 instructions, one bf16x2 conversion per pair): the
+// scalar form spent ~20 issue slots per element on bf16 pack / unpack shuffles (SASS), and these
+// kernels are bound by issue slots and the latency of their dependent phases, not by HBM.
+__device__ __forceinline__ float2 bf2_to_f2(uint32_t w) {      // exact
+  return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+}
+__device__ __forceinline__ uint32_t f2_to_bf2(float2 v) {      // round to nearest even, .x in the low half
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(v.y), "f"(v.x));
+  return r;
+}
+// eight consecutive floats of a parameter vector as four pairs (kSmem: the vector was staged in
+// shared memory; otherwise read-only global loads)
+template <bool kSmem>
+__device__ __forceinline__ void ld_pairs(const float* src, float2* dst) {
+  float4 a, b;
+  if constexpr (kSmem) {
+    a = *reinterpret_cast<const float4*>(src); b = *reinterpret_cast<const float4*>(src + 4);
+  } else {
+    a = __ldg(reinterpret_cast<const float4*>(src)); b = __ldg(reinterpret_cast<const float4*>(src + 4));
+  }
+  dst[0] = make_float2(a.x, a.y); dst[1] = make_float2(a.z, a.w);
+  dst[2] = make_float2(b.x, b.y); dst[3] = make_float2(b.z, b.w);
+}
+// the five per-channel vectors of the tail (bp, ln_w, ln_b, b1, b2) -> prm[5][C]; they are model
+// parameters (no kernel of the stream writes them), so this may run before pdl_wait()
+template <int C, int kThreads>
+__device__ __forceinline__ void stage_tail_params(float* prm, const float* bp, const float* ln_w, const float* ln_b,
+                                                  const float* b1, const float* b2) {
+  for (int i = threadIdx.x; i < 5 * C; i += kThreads) {
+    const int k = i / C, c = i - k * C;
+    const float* src = k == 0 ? bp : k == 1 ? ln_w : k == 2 ? ln_b : k == 3 ? b1 : b2;
+    prm[i] = __ldg(src + c);
+  }
+}
+
 constexpr int kTailCols = 32;        // accumulator columns per thread
 constexpr int kTailThreads = 1024;   // kChains * (C / kTailCols) * 128 for both instantiations
 
@@ -65,8 +101,13 @@ attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_const
   __shared__ __align__(8) uint64_t ld_bar[kChains];
   __shared__ __align__(8) uint64_t mma_bar[kChains];
   __shared__ uint32_t tmem_base_smem;
+  // the per-channel vectors bp | ln_w | ln_b | b1 | b2 in shared memory where there is room (C = 64;
+  // at C = 128 the weights and two chains leave 2 KB of the 227 KB)
+  constexpr bool kPrmSmem = C == 64;
+  __shared__ __align__(16) float prm_smem[kPrmSmem ? 5 * C : 4];
 
   pdl_trigger();
+  if constexpr (kPrmSmem) stage_tail_params<C, kTailThreads>(prm_smem, p.bp, p.ln_w, p.ln_b, p.b1, p.b2);
   const int warp = threadIdx.x >> 5;
   const int chain = warp / (4 * kSplit);
   const int split = (warp >> 2) % kSplit;       // which 32 columns of the row this thread owns
@@ -105,6 +146,13 @@ attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_const
   const uint32_t idesc = umma_idesc(1u, 128, C);
   const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(chain * C);
   const int col0 = split * kTailCols;           // first column of this thread
+  const float* prm[5];                          // this thread's 32 columns of the five vectors
+  if constexpr (kPrmSmem) {
+#pragma unroll
+    for (int i = 0; i < 5; ++i) prm[i] = prm_smem + i * C + col0;
+  } else {
+    prm[0] = p.bp + col0; prm[1] = p.ln_w + col0; prm[2] = p.ln_b + col0; prm[3] = p.b1 + col0; prm[4] = p.b2 + col0;
+  }
   const uint32_t t_row = d_tmem + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(col0);
   const uint32_t a_addr = smem_u32(bufA);
   const uint32_t w_addr = smem_u32(wsm);
@@ -143,11 +191,6 @@ attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_const
     ph_mma ^= 1;
     tc_fence_after();
   };
-  auto load_vec8 = [&](const float* src, float* dst) {
-    const float4 a = __ldg(reinterpret_cast<const float4*>(src));
-    const float4 b = __ldg(reinterpret_cast<const float4*>(src + 4));
-    dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; dst[3] = a.w; dst[4] = b.x; dst[5] = b.y; dst[6] = b.z; dst[7] = b.w;
-  };
 
   // consecutive tiles go to different CTAs first, so a small launch still spreads over the chip
   for (int tile = blockIdx.x + gridDim.x * chain; tile < p.m_tiles; tile += gridDim.x * kChains) {
@@ -178,30 +221,27 @@ attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_const
       float o[kTailCols];
       tmem_ld32(t_row, o);
       tmem_ld_wait();
-      float s = 0.f, ss = 0.f;
+      float2 s2 = make_float2(0.f, 0.f), ss2 = make_float2(0.f, 0.f);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         uint4* rp = reinterpret_cast<uint4*>(rowR + (((j0 + j) ^ sw) << 4));
         const uint4 u = *rp;
-        const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&u);
-        float bv[8];
-        load_vec8(p.bp + col0 + 8 * j, bv);
-        uint4 w4;
-        __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+        const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+        float2 bv[4];
+        ld_pairs<kPrmSmem>(prm[0] + 8 * j, bv);
+        uint32_t ww[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const float2 xr = __bfloat1622float2(hp[i]);
-          const __nv_bfloat162 ob = __floats2bfloat162_rn(o[8 * j + 2 * i] + bv[2 * i] + xr.x,
-                                                          o[8 * j + 2 * i + 1] + bv[2 * i + 1] + xr.y);
-          wp[i] = ob;
-          const float2 of = __bfloat1622float2(ob);   // LayerNorm sees the rounded o, as it would from HBM
+          const float2 acc = make_float2(o[8 * j + 2 * i], o[8 * j + 2 * i + 1]);
+          ww[i] = f2_to_bf2(__fadd2_rn(__fadd2_rn(acc, bv[i]), bf2_to_f2(uw[i])));
+          const float2 of = bf2_to_f2(ww[i]);   // LayerNorm sees the rounded o, as it would from HBM
           o[8 * j + 2 * i] = of.x; o[8 * j + 2 * i + 1] = of.y;
-          s += of.x + of.y;
-          ss = fmaf(of.x, of.x, fmaf(of.y, of.y, ss));
+          s2 = __fadd2_rn(s2, of);
+          ss2 = __ffma2_rn(of, of, ss2);
         }
-        *rp = w4;
+        *rp = make_uint4(ww[0], ww[1], ww[2], ww[3]);
       }
-      scratch[split * 128 + t] = make_float2(s, ss);
+      scratch[split * 128 + t] = make_float2(s2.x + s2.y, ss2.x + ss2.y);
       named_bar_sync(bar_id, kChainThreads);
       float ts = 0.f, tss = 0.f;
 #pragma unroll
@@ -212,18 +252,19 @@ attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_const
       const float mean = ts * (1.0f / C);
       const float rstd = rsqrtf(fmaxf(tss * (1.0f / C) - mean * mean, 0.f) + 1e-5f);
       named_bar_sync(bar_id, kChainThreads);   // the partials are read: A may be overwritten
+      const float2 nm = make_float2(-mean, -mean), rs = make_float2(rstd, rstd);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float wv[8], bv[8];
-        load_vec8(p.ln_w + col0 + 8 * j, wv);
-        load_vec8(p.ln_b + col0 + 8 * j, bv);
-        uint4 w4;
-        __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+        float2 wv[4], bv[4];
+        ld_pairs<kPrmSmem>(prm[1] + 8 * j, wv);
+        ld_pairs<kPrmSmem>(prm[2] + 8 * j, bv);
+        uint32_t ww[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-          wp[i] = __floats2bfloat162_rn((o[8 * j + 2 * i] - mean) * rstd * wv[2 * i] + bv[2 * i],
-                                        (o[8 * j + 2 * i + 1] - mean) * rstd * wv[2 * i + 1] + bv[2 * i + 1]);
-        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
+        for (int i = 0; i < 4; ++i) {
+          const float2 d = __fmul2_rn(__fadd2_rn(make_float2(o[8 * j + 2 * i], o[8 * j + 2 * i + 1]), nm), rs);
+          ww[i] = f2_to_bf2(__ffma2_rn(d, wv[i], bv[i]));
+        }
+        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = make_uint4(ww[0], ww[1], ww[2], ww[3]);
       }
     }
     fence_async_proxy();
@@ -239,16 +280,19 @@ attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_const
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float bv[8];
-        load_vec8(p.b1 + col0 + 8 * j, bv);
-        uint4 w4;
-        __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+        float2 bv[4];
+        ld_pairs<kPrmSmem>(prm[3] + 8 * j, bv);
+        float h[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) bv[i] += v[8 * j + i];
-        gelu_inplace<__nv_bfloat16, 8>(bv);
+        for (int i = 0; i < 4; ++i) {
+          const float2 a = __fadd2_rn(bv[i], make_float2(v[8 * j + 2 * i], v[8 * j + 2 * i + 1]));
+          h[2 * i] = a.x; h[2 * i + 1] = a.y;
+        }
+        gelu_inplace<__nv_bfloat16, 8>(h);
+        uint32_t ww[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) wp[i] = __floats2bfloat162_rn(bv[2 * i], bv[2 * i + 1]);
-        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
+        for (int i = 0; i < 4; ++i) ww[i] = f2_to_bf2(make_float2(h[2 * i], h[2 * i + 1]));
+        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = make_uint4(ww[0], ww[1], ww[2], ww[3]);
       }
     }
     fence_async_proxy();
@@ -268,15 +312,14 @@ attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_const
         uint4 w4 = make_uint4(0u, 0u, 0u, 0u);
         if (valid) {
           const uint4 u = *reinterpret_cast<const uint4*>(rowR + off);
-          const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&u);
-          float bv[8];
-          load_vec8(p.b2 + col0 + 8 * j, bv);
-          __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+          const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+          float2 bv[4];
+          ld_pairs<kPrmSmem>(prm[4] + 8 * j, bv);
+          uint32_t ww[4];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float2 of = __bfloat1622float2(hp[i]);
-            wp[i] = __floats2bfloat162_rn(v[8 * j + 2 * i] + bv[2 * i] + of.x, v[8 * j + 2 * i + 1] + bv[2 * i + 1] + of.y);
-          }
+          for (int i = 0; i < 4; ++i)
+            ww[i] = f2_to_bf2(__fadd2_rn(__fadd2_rn(make_float2(v[8 * j + 2 * i], v[8 * j + 2 * i + 1]), bv[i]), bf2_to_f2(uw[i])));
+          w4 = make_uint4(ww[0], ww[1], ww[2], ww[3]);
         }
         *reinterpret_cast<uint4*>(rowA + off) = w4;
       }
@@ -332,8 +375,10 @@ attn_tail256_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_co
   __shared__ __align__(8) uint64_t ld_bar;
   __shared__ __align__(8) uint64_t mma_bar;
   __shared__ uint32_t tmem_base_smem;
+  __shared__ __align__(16) float prm_smem[5 * 256];   // bp | ln_w | ln_b | b1 | b2
 
   pdl_trigger();
+  stage_tail_params<256, kTail256Threads>(prm_smem, p.bp, p.ln_w, p.ln_b, p.b1, p.b2);
   const int warp = threadIdx.x >> 5;
   const int split = warp >> 2;                  // which 32 columns of the row this thread owns
   const int q = warp & 3;                       // TMEM lane quadrant of this warp
@@ -359,6 +404,7 @@ attn_tail256_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_co
 
   const uint32_t idesc = umma_idesc(1u, 128, C);
   const int col0 = split * kTailCols;
+  const float* prm = prm_smem + col0;            // this thread's 32 columns; vector k at prm + k * C
   const uint32_t t_row = d_tmem + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(col0);
   const uint32_t a_addr = smem_u32(bufA), w_addr = smem_u32(wsm);
   const int sw = t & 7;
@@ -401,11 +447,6 @@ attn_tail256_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_co
     ph_mma ^= 1;
     tc_fence_after();
   };
-  auto load_vec8 = [&](const float* src, float* dst) {
-    const float4 a = __ldg(reinterpret_cast<const float4*>(src));
-    const float4 b = __ldg(reinterpret_cast<const float4*>(src + 4));
-    dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; dst[3] = a.w; dst[4] = b.x; dst[5] = b.y; dst[6] = b.z; dst[7] = b.w;
-  };
 
   if (static_cast<int>(blockIdx.x) < p.m_tiles) load_w(&tmap_wp);
   for (int tile = blockIdx.x; tile < p.m_tiles; tile += gridDim.x) {
@@ -437,7 +478,7 @@ attn_tail256_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_co
     // ---- o = acc + bp + x_ln (kept in registers as packed bf16); h = LayerNorm(o) -> A
     uint32_t ob[16];
     {
-      float s = 0.f, ss = 0.f;
+      float2 s2 = make_float2(0.f, 0.f), ss2 = make_float2(0.f, 0.f);
 #pragma unroll
       for (int half = 0; half < 2; ++half) {   // 16 accumulator columns at a time: 64 registers per thread
         float o[16];
@@ -446,22 +487,20 @@ attn_tail256_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_co
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
           const int j = 2 * half + jj;
-          const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&xr[j]);
-          float bv[8];
-          load_vec8(p.bp + col0 + 8 * j, bv);
+          const uint32_t uw[4] = {xr[j].x, xr[j].y, xr[j].z, xr[j].w};
+          float2 bv[4];
+          ld_pairs<true>(prm + 0 * C + 8 * j, bv);
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const float2 xv = __bfloat1622float2(hp[i]);
-            const __nv_bfloat162 o2 = __floats2bfloat162_rn(o[8 * jj + 2 * i] + bv[2 * i] + xv.x,
-                                                            o[8 * jj + 2 * i + 1] + bv[2 * i + 1] + xv.y);
-            ob[4 * j + i] = *reinterpret_cast<const uint32_t*>(&o2);
-            const float2 of = __bfloat1622float2(o2);   // LayerNorm sees the rounded o, as it would from HBM
-            s += of.x + of.y;
-            ss = fmaf(of.x, of.x, fmaf(of.y, of.y, ss));
+            const float2 acc = make_float2(o[8 * jj + 2 * i], o[8 * jj + 2 * i + 1]);
+            ob[4 * j + i] = f2_to_bf2(__fadd2_rn(__fadd2_rn(acc, bv[i]), bf2_to_f2(uw[i])));
+            const float2 of = bf2_to_f2(ob[4 * j + i]);   // LayerNorm sees the rounded o, as it would from HBM
+            s2 = __fadd2_rn(s2, of);
+            ss2 = __ffma2_rn(of, of, ss2);
           }
         }
       }
-      scratch[split * 128 + t] = make_float2(s, ss);   // (GEMM 0 has retired: bufA is idle)
+      scratch[split * 128 + t] = make_float2(s2.x + s2.y, ss2.x + ss2.y);   // (GEMM 0 has retired: bufA is idle)
       named_bar_sync(1, kTail256Threads);
       float ts = 0.f, tss = 0.f;
 #pragma unroll
@@ -472,20 +511,19 @@ attn_tail256_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_co
       const float mean = ts * (1.0f / C);
       const float rstd = rsqrtf(fmaxf(tss * (1.0f / C) - mean * mean, 0.f) + 1e-5f);
       named_bar_sync(1, kTail256Threads);   // the partials are read: A may be overwritten
+      const float2 nm = make_float2(-mean, -mean), rs = make_float2(rstd, rstd);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float wv[8], bv[8];
-        load_vec8(p.ln_w + col0 + 8 * j, wv);
-        load_vec8(p.ln_b + col0 + 8 * j, bv);
-        uint4 w4;
-        __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+        float2 wv[4], bv[4];
+        ld_pairs<true>(prm + 1 * C + 8 * j, wv);
+        ld_pairs<true>(prm + 2 * C + 8 * j, bv);
+        uint32_t ww[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const float2 of = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ob[4 * j + i]));
-          wp[i] = __floats2bfloat162_rn((of.x - mean) * rstd * wv[2 * i] + bv[2 * i],
-                                        (of.y - mean) * rstd * wv[2 * i + 1] + bv[2 * i + 1]);
+          const float2 d = __fmul2_rn(__fadd2_rn(bf2_to_f2(ob[4 * j + i]), nm), rs);
+          ww[i] = f2_to_bf2(__ffma2_rn(d, wv[i], bv[i]));
         }
-        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
+        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = make_uint4(ww[0], ww[1], ww[2], ww[3]);
       }
     }
     fence_async_proxy();
@@ -504,16 +542,19 @@ attn_tail256_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_co
 #pragma unroll
       for (int jj = 0; jj < 2; ++jj) {
         const int j = 2 * half + jj;
-        float bv[8];
-        load_vec8(p.b1 + col0 + 8 * j, bv);
-        uint4 w4;
-        __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+        float2 bv[4];
+        ld_pairs<true>(prm + 3 * C + 8 * j, bv);
+        float h[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) bv[i] += v[8 * jj + i];
-        gelu_inplace<__nv_bfloat16, 8>(bv);
+        for (int i = 0; i < 4; ++i) {
+          const float2 a = __fadd2_rn(bv[i], make_float2(v[8 * jj + 2 * i], v[8 * jj + 2 * i + 1]));
+          h[2 * i] = a.x; h[2 * i + 1] = a.y;
+        }
+        gelu_inplace<__nv_bfloat16, 8>(h);
+        uint32_t ww[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) wp[i] = __floats2bfloat162_rn(bv[2 * i], bv[2 * i + 1]);
-        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
+        for (int i = 0; i < 4; ++i) ww[i] = f2_to_bf2(make_float2(h[2 * i], h[2 * i + 1]));
+        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = make_uint4(ww[0], ww[1], ww[2], ww[3]);
       }
     }
     fence_async_proxy();
@@ -534,14 +575,14 @@ attn_tail256_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_co
         const int j = 2 * half + jj;
         uint4 w4 = make_uint4(0u, 0u, 0u, 0u);
         if (valid) {
-          float bv[8];
-          load_vec8(p.b2 + col0 + 8 * j, bv);
-          __nv_bfloat162* wp = reinterpret_cast<__nv_bfloat162*>(&w4);
+          float2 bv[4];
+          ld_pairs<true>(prm + 4 * C + 8 * j, bv);
+          uint32_t ww[4];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float2 of = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ob[4 * j + i]));
-            wp[i] = __floats2bfloat162_rn(v[8 * jj + 2 * i] + bv[2 * i] + of.x, v[8 * jj + 2 * i + 1] + bv[2 * i + 1] + of.y);
-          }
+          for (int i = 0; i < 4; ++i)
+            ww[i] = f2_to_bf2(__fadd2_rn(__fadd2_rn(make_float2(v[8 * jj + 2 * i], v[8 * jj + 2 * i + 1]), bv[i]),
+                                         bf2_to_f2(ob[4 * j + i])));
+          w4 = make_uint4(ww[0], ww[1], ww[2], ww[3]);
         }
         *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
       }

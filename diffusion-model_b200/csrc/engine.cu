@@ -344,6 +344,7 @@ class Engine : public IEngine {
     if (const char* e = getenv("DMB200_ATTN_MMA")) use_mma_attention_ = e[0] != '0';    // 0: the tcgen05 kernel
     if (const char* e = getenv("DMB200_EAGER_GRAPH")) eager_graph_ = e[0] != '0';
     if (const char* e = getenv("DMB200_TAIL256")) use_tail256_ = e[0] != '0';
+    if (const char* e = getenv("DMB200_CONVIN_Z")) conv_in_z_ = std::max(0, std::min(7, atoi(e)));
     if (const char* e = getenv("DMB200_ATTN_POLY")) attn_poly_ = e[0] != '0';           // 0: every exp2 on MUFU
     if constexpr (std::is_same<T, float>::value) {
       DMB_CUDA(cudaFuncSetAttribute(attention_mma_f32_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
@@ -489,6 +490,7 @@ class Engine : public IEngine {
   long long* stat_arena_cur_ = nullptr;   // bump cursor into the statistics arena of the plan being built
   size_t stat_arena_left_ = 0;
   bool use_tc_attention_ = true;
+  int conv_in_z_ = 0;               // DMB200_CONVIN_Z: CTAs per sample of the U-Net's input conv (0: 7 below 64 samples, else 1)
   bool use_tail256_ = true;         // DMB200_TAIL256=0: the C = 256 attention blocks keep their separate Linear / LayerNorm launches
   bool eager_graph_ = true;         // DMB200_EAGER_GRAPH=0: dmb_denoise_cond_step launches its kernels one by one
   bool use_mma_attention_ = true;   // warp-level MMA attention (attention_mma.cuh) for maps > 3x3 in bf16 mode
@@ -1321,7 +1323,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.tag("conv_in 4->64 @28", 2.0 * n0 * kLatH * kLatW * 36.0 * 64);
     ops.push_back([this, r0, w0, pp, B](cudaStream_t s) {
       if constexpr (std::is_same<T, __nv_bfloat16>::value)
-        launch(conv_in_mma_kernel, dim3(r0.g.n, 1, r0.g.n >= 64 ? 1 : 7), kConvInThreads, 0, s, pp->x_state, B, w0, nullptr, 1.0f, r0.g, 64,
+        launch(conv_in_mma_kernel, dim3(r0.g.n, 1, conv_in_z_ ? conv_in_z_ : (r0.g.n >= 64 ? 1 : 7)), kConvInThreads, 0, s, pp->x_state, B, w0, nullptr, 1.0f, r0.g, 64,
                                                                       r0.p, r0.sstat);
       else
         conv_in_kernel<T><<<dim3(cdiv(kLatH * kLatW, 128), r0.g.n, 1), 128, 0, s>>>(pp->x_state, B, w0, nullptr, 1.0f,

@@ -215,18 +215,54 @@ conv_in_mma_kernel(const float* __restrict__ x, int B_src, const float* __restri
   pdl_wait();
   constexpr int PW = kLatW + 2, PH = kLatH + 2, PLANE = PW * PH;   // zero-bordered latent plane
   __shared__ float img[kLatC * PLANE];
-  __shared__ float ws[64 * 36];
+  __shared__ __align__(16) float ws[64 * 36];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int be = blockIdx.x, co0 = blockIdx.y * 64;
   const float inv_div = 1.0f / in_div;
   const float* xs = x + static_cast<size_t>(be % B_src) * kLatC * kLatH * kLatW;
-  for (int i = tid; i < kLatC * PLANE; i += kConvInThreads) {
-    const int ci = i / PLANE, rem = i - ci * PLANE, py = rem / PW, px = rem - py * PW;
-    float v = 0.f;
-    if (py >= 1 && py <= kLatH && px >= 1 && px <= kLatW) v = xs[(ci * kLatH + py - 1) * kLatW + px - 1] * inv_div;
-    img[i] = v;
+  // Staging: every global load of the CTA is issued before the first one is used (one memory latency in
+  // front of the MMA loop; as a load -> store loop the compiler kept them serial: 15 + 9 dependent
+  // round trips, about half of this kernel's time).  The latent is 784 float4 (a 28-float image row is
+  // seven of them), the 64 x 36 weights 576; both bases are 256-byte aligned (Pool / upload()).
+  {
+    constexpr int kXV = kLatC * kLatH * kLatW / 4, kWV = 64 * 36 / 4;
+    constexpr int kXU = (kXV + kConvInThreads - 1) / kConvInThreads, kWU = (kWV + kConvInThreads - 1) / kConvInThreads;
+    static_assert(kLatW % 4 == 0, "image rows are whole float4s");
+    float4 xv[kXU], wv[kWU];
+    const float4* x4 = reinterpret_cast<const float4*>(xs);
+    const bool x_al = (reinterpret_cast<uintptr_t>(xs) & 15) == 0;
+    const float4* w4 = reinterpret_cast<const float4*>(w_oihw + static_cast<size_t>(co0) * 36);
+#pragma unroll
+    for (int u = 0; u < kXU; ++u)
+      if (tid + u * kConvInThreads < kXV) {
+        if (x_al) {
+          xv[u] = __ldg(x4 + tid + u * kConvInThreads);
+        } else {   // a caller's latent that is not 16-byte aligned (VAE decode takes the pointer as given)
+          const float* q = xs + 4 * (tid + u * kConvInThreads);
+          xv[u] = make_float4(__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
+        }
+      }
+#pragma unroll
+    for (int u = 0; u < kWU; ++u)
+      if (tid + u * kConvInThreads < kWV) wv[u] = __ldg(w4 + tid + u * kConvInThreads);
+    // the zero border of the four planes (two rows, two columns each)
+    for (int i = tid; i < kLatC * PLANE; i += kConvInThreads) {
+      const int ci = i / PLANE, rem = i - ci * PLANE, py = rem / PW, px = rem - py * PW;
+      if (py == 0 || py == PH - 1 || px == 0 || px == PW - 1) img[i] = 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < kXU; ++u) {
+      const int e = (tid + u * kConvInThreads) * 4;
+      if (e < kXV * 4) {
+        const int ci = e / (kLatH * kLatW), rem = e - ci * (kLatH * kLatW), py = rem / kLatW, px = rem - py * kLatW;
+        float* d = img + ci * PLANE + (py + 1) * PW + px + 1;
+        d[0] = xv[u].x * inv_div; d[1] = xv[u].y * inv_div; d[2] = xv[u].z * inv_div; d[3] = xv[u].w * inv_div;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kWU; ++u)
+      if (tid + u * kConvInThreads < kWV) *reinterpret_cast<float4*>(ws + (tid + u * kConvInThreads) * 4) = wv[u];
   }
-  for (int i = tid; i < 64 * 36; i += kConvInThreads) ws[i] = w_oihw[static_cast<size_t>(co0) * 36 + i];
   __syncthreads();
 
   const int gq = lane >> 2, tq = lane & 3;
@@ -789,35 +825,83 @@ __global__ void __launch_bounds__(128)
 cfg_step_kernel(const T* __restrict__ feat, Geo g, int B, const StepParams* __restrict__ pp) {
   pdl_trigger();
   pdl_wait();
-  const StepParams p = *pp;
+  // The 128 feature rows (64 channels) of this CTA's pixels, both guidance halves, are staged through
+  // shared memory: eight lanes fetch one row's 16-byte chunks, so a warp instruction covers four
+  // whole rows (a thread reading its own row touched 32 different 128-byte lines per instruction);
+  // chunk c of row r sits at chunk slot c ^ (r & 7), which makes thread r's reads of its own row
+  // conflict-free.  Every load of the CTA is issued before the first one is used.
+  constexpr int kRowElems = 64;
+  constexpr int kChunks = kRowElems * static_cast<int>(sizeof(T)) / 16;   // 16-byte chunks per row: 8 (bf16) / 16 (fp32)
+  constexpr int kE = 16 / static_cast<int>(sizeof(T));                    // elements per chunk
+  constexpr int kBuf = sizeof(T) == 2 ? 2 : 1;   // bf16: both halves in flight at once; fp32 (32 KB per half): one after the other
+  __shared__ __align__(16) uint8_t rows[kBuf][128 * kChunks * 16];
   __shared__ float ws[kLatC * 64];
   __shared__ float bs[kLatC];
-  for (int i = threadIdx.x; i < kLatC * 64; i += blockDim.x) ws[i] = p.w_out[i];
-  if (threadIdx.x < kLatC) bs[threadIdx.x] = p.b_out[threadIdx.x];
-  __syncthreads();
   const int HW = g.H * g.W;
   const int b = blockIdx.y;
-  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
-  if (pix >= HW) return;
-  const int y = pix / g.W, x = pix % g.W;
+  const int tid = threadIdx.x;
+  const int pix0 = blockIdx.x * 128;
+  const int pix = pix0 + tid;
+  // thread -> (row, chunk) of its k-th staged vector: 128 rows x kChunks chunks over 128 threads
+  auto load_half = [&](int half, uint4* st) {
+#pragma unroll
+    for (int k = 0; k < kChunks; ++k) {
+      const int v = tid + k * 128, rl = v / kChunks, c = v - rl * kChunks;
+      const int pq = pix0 + rl;
+      if (pq < HW) {
+        const int yq = fdiv(pq, g.mW, g.W), xq = pq - yq * g.W;
+        st[k] = *(reinterpret_cast<const uint4*>(feat + static_cast<size_t>(geo_row(g, b + half * B, yq, xq)) * kRowElems) + c);
+      }
+    }
+  };
+  auto store_half = [&](int buf, const uint4* st) {
+#pragma unroll
+    for (int k = 0; k < kChunks; ++k) {
+      const int v = tid + k * 128, rl = v / kChunks, c = v - rl * kChunks;
+      if (pix0 + rl < HW) *reinterpret_cast<uint4*>(rows[buf] + rl * (kChunks * 16) + ((c ^ (rl & 7)) << 4)) = st[k];
+    }
+  };
+  // the out conv of this thread's pixel from its staged row: k ascending, as one thread per row did
+  auto dot_half = [&](int buf, float* e) {
+#pragma unroll
+    for (int ch = 0; ch < kChunks; ++ch) {
+      const uint8_t* src = rows[buf] + tid * (kChunks * 16) + ((ch ^ (tid & 7)) << 4);
+      float v[kE];
+      if constexpr (sizeof(T) == 2) {
+        load8(reinterpret_cast<const T*>(src), v);
+      } else {
+        const float4 a = *reinterpret_cast<const float4*>(src);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+      }
+#pragma unroll
+      for (int i = 0; i < kE; ++i)
+#pragma unroll
+        for (int c = 0; c < kLatC; ++c) e[c] = fmaf(v[i], ws[c * 64 + ch * kE + i], e[c]);
+    }
+  };
+  uint4 stage[kBuf][kChunks];
+  load_half(0, stage[0]);
+  if constexpr (kBuf == 2) load_half(1, stage[1]);
+  const StepParams p = *pp;
+  for (int i = tid; i < kLatC * 64; i += 128) ws[i] = p.w_out[i];
+  if (tid < kLatC) bs[tid] = p.b_out[tid];
+  store_half(0, stage[0]);
+  if constexpr (kBuf == 2) store_half(1, stage[1]);
+  __syncthreads();
   float eu[kLatC], ec[kLatC];
 #pragma unroll
   for (int c = 0; c < kLatC; ++c) { eu[c] = bs[c]; ec[c] = bs[c]; }
-  const T* fu = feat + static_cast<size_t>(geo_row(g, b, y, x)) * 64;
-  const T* fc = feat + static_cast<size_t>(geo_row(g, b + B, y, x)) * 64;
-#pragma unroll
-  for (int k0 = 0; k0 < 64; k0 += 8) {
-    float vu[8], vc[8];
-    load8(fu + k0, vu);
-    load8(fc + k0, vc);
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-#pragma unroll
-      for (int c = 0; c < kLatC; ++c) {
-        eu[c] = fmaf(vu[i], ws[c * 64 + k0 + i], eu[c]);
-        ec[c] = fmaf(vc[i], ws[c * 64 + k0 + i], ec[c]);
-      }
+  if constexpr (kBuf == 2) {
+    if (pix < HW) { dot_half(0, eu); dot_half(1, ec); }
+  } else {
+    if (pix < HW) dot_half(0, eu);
+    load_half(1, stage[0]);
+    __syncthreads();            // every thread has read its row of the first half
+    store_half(0, stage[0]);
+    __syncthreads();
+    if (pix < HW) dot_half(0, ec);
   }
+  if (pix >= HW) return;
   const long long t = p.t_vec[b];
   const int slot = (p.slot_t0 - static_cast<int>(t)) / p.t_stride;
   // the Python layer asserts 1 <= t <= T like the reference (diff.py:140); the row index is clamped
