@@ -349,6 +349,252 @@ attn_tail_kernel(const __grid_constant__ CUtensorMap tmap_av, const __grid_const
 }
 
 // ---------------------------------------------------------------------------
+// Head of the attention block as ONE kernel (models/unet_cond.py:47-49, in front of the MHA core):
+//
+//   x_ln = LayerNorm(x)                      (self.ln; also the residual of the block, so it is stored)
+//   qkv  = x_ln Wqkv^T + bqkv                (nn.MultiheadAttention in_proj)
+//
+// Same shape as attn_tail_kernel: the in-projection's three [C, C] blocks (q | k | v rows of in_proj_weight)
+// stay resident, a 128-row tile of x arrives by TMA, is normalised in place (thread = one row x 32 columns,
+// the row sums cross warpgroups through shared memory) and is then both the source of the x_ln TMA store and
+// the A operand of three MMAs; each 128 x C accumulator gets its bias and leaves through the second buffer.
+// Replaces a LayerNorm launch and a Linear launch where the LayerNorm is not already applied by the producing
+// GroupNorm kernel (large activations): x_ln is not re-read from HBM and two passes become one.
+// Rounding points are those of the separate launches (x_ln and qkv rounded to bf16); the LayerNorm variance
+// is the one-pass E[x^2] - mean^2 in fp32 (the separate kernel subtracts the mean first).
+// ---------------------------------------------------------------------------
+struct LnQkvParams {
+  Geo geo;
+  int m_tiles;
+  const float* ln_w;
+  const float* ln_b;
+  const float* bqkv;   // in_proj_bias [3 C]
+};
+
+template <int C, int kChains>
+__global__ void __launch_bounds__(kTailThreads, 1)
+ln_qkv_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+              const __grid_constant__ CUtensorMap tmap_xln, const __grid_constant__ CUtensorMap tmap_qkv,
+              const LnQkvParams p) {
+  static_assert(C == 64 || C == 128, "weights of wider blocks do not fit in shared memory");
+  constexpr int kSplit = C / kTailCols;
+  constexpr int kChainThreads = 128 * kSplit;
+  static_assert(kChains * kChainThreads == kTailThreads, "thread layout");
+  constexpr int kKC = C / 64;
+  constexpr uint32_t kChunkBytes = 128 * 128;
+  constexpr uint32_t kWChunkBytes = C * 128;
+  constexpr uint32_t kTmemCols = kChains * C;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t w_bar;
+  __shared__ __align__(8) uint64_t ld_bar[kChains];
+  __shared__ __align__(8) uint64_t mma_bar[kChains];
+  __shared__ uint32_t tmem_base_smem;
+  constexpr bool kPrmSmem = C == 64;   // ln_w | ln_b | bq | bk | bv
+  __shared__ __align__(16) float prm_smem[kPrmSmem ? 5 * C : 4];
+
+  pdl_trigger();
+  if constexpr (kPrmSmem) stage_tail_params<C, kTailThreads>(prm_smem, p.ln_w, p.ln_b, p.bqkv, p.bqkv + C, p.bqkv + 2 * C);
+  const int warp = threadIdx.x >> 5;
+  const int chain = warp / (4 * kSplit);
+  const int split = (warp >> 2) % kSplit;
+  const int q = warp & 3;
+  const bool lead = (warp % (4 * kSplit)) == 0;
+  const int t = q * 32 + (threadIdx.x & 31);
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  uint8_t* wsm = smem;                                         // [3][kKC][C rows][128 B]
+  uint8_t* bufA = smem + 3 * kKC * kWChunkBytes + chain * (2 * kKC * kChunkBytes);   // x -> x_ln
+  uint8_t* bufO = bufA + kKC * kChunkBytes;                                          // q / k / v staging
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmap_x); tma_prefetch_desc(&tmap_w); tma_prefetch_desc(&tmap_xln); tma_prefetch_desc(&tmap_qkv);
+    mbar_init(&w_bar, 1);
+    for (int i = 0; i < kChains; ++i) { mbar_init(&ld_bar[i], 1); mbar_init(&mma_bar[i], 1); }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(&tmem_base_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();
+
+  if (threadIdx.x == 0) {   // the three [C, C] blocks of in_proj_weight, once per CTA
+    mbar_expect_tx(&w_bar, 3 * kKC * kWChunkBytes);
+    for (int part = 0; part < 3; ++part)
+      for (int kc = 0; kc < kKC; ++kc)
+        tma_load_2d(wsm + (part * kKC + kc) * kWChunkBytes, &tmap_w, &w_bar, kc * 64, part * C);
+  }
+
+  const uint32_t idesc = umma_idesc(1u, 128, C);
+  const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(chain * C);
+  const int col0 = split * kTailCols;
+  const float* prm[5];
+  if constexpr (kPrmSmem) {
+#pragma unroll
+    for (int i = 0; i < 5; ++i) prm[i] = prm_smem + i * C + col0;
+  } else {
+    prm[0] = p.ln_w + col0; prm[1] = p.ln_b + col0;
+    prm[2] = p.bqkv + col0; prm[3] = p.bqkv + C + col0; prm[4] = p.bqkv + 2 * C + col0;
+  }
+  const uint32_t t_row = d_tmem + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(col0);
+  const uint32_t a_addr = smem_u32(bufA);
+  const uint32_t w_addr = smem_u32(wsm);
+  const int bar_id = 1 + chain;
+  const int sw = t & 7;
+  const uint32_t row_off = (col0 >> 6) * kChunkBytes + t * 128;
+  const int j0 = (col0 & 63) >> 3;
+  uint8_t* rowA = bufA + row_off;
+  uint8_t* rowO = bufO + row_off;
+  float2* scratch = reinterpret_cast<float2*>(bufO);   // LayerNorm partials (bufO is idle until the first epilogue)
+  uint32_t ph_ld = 0, ph_mma = 0;
+  bool w_ready = false;
+
+  auto issue_gemm = [&](int which) {
+    if (lead) {
+      tc_fence_after();
+      if (elect_one()) {
+#pragma unroll
+        for (int kc = 0; kc < kKC; ++kc) {
+          const uint64_t ad = umma_desc_sw128(a_addr + kc * kChunkBytes);
+          const uint64_t bd = umma_desc_sw128(w_addr + (which * kKC + kc) * kWChunkBytes);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_ss<false>(d_tmem, ad + (k * 2), bd + (k * 2), idesc, (kc > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&mma_bar[chain]);
+      }
+      __syncwarp();
+    }
+  };
+
+  for (int tile = blockIdx.x + gridDim.x * chain; tile < p.m_tiles; tile += gridDim.x * kChains) {
+    const int m0 = tile * 128;
+    int b = 0, y = 0, x = 0;
+    const bool valid = geo_decode(p.geo, m0 + t, b, y, x);
+
+    if (lead) {
+      if (elect_one()) {
+        tma_store_wait_read<0>();   // the previous tile's stores have read bufA and bufO
+        mbar_expect_tx(&ld_bar[chain], kKC * kChunkBytes);
+#pragma unroll
+        for (int kc = 0; kc < kKC; ++kc) tma_load_2d(bufA + kc * kChunkBytes, &tmap_x, &ld_bar[chain], kc * 64, m0);
+      }
+      __syncwarp();
+    }
+    if (!w_ready) { mbar_wait(&w_bar, 0); w_ready = true; }
+    mbar_wait(&ld_bar[chain], ph_ld);
+    ph_ld ^= 1;
+
+    // ---- x_ln = LayerNorm(x), in place in A (pad pixels stay zero, as the separate kernel leaves them)
+    {
+      float2 xv[16];
+      float2 s2 = make_float2(0.f, 0.f), ss2 = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint4 u = *reinterpret_cast<const uint4*>(rowA + (((j0 + j) ^ sw) << 4));
+        const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          xv[4 * j + i] = bf2_to_f2(uw[i]);
+          s2 = __fadd2_rn(s2, xv[4 * j + i]);
+          ss2 = __ffma2_rn(xv[4 * j + i], xv[4 * j + i], ss2);
+        }
+      }
+      scratch[split * 128 + t] = make_float2(s2.x + s2.y, ss2.x + ss2.y);
+      named_bar_sync(bar_id, kChainThreads);
+      float ts = 0.f, tss = 0.f;
+#pragma unroll
+      for (int g = 0; g < kSplit; ++g) {   // the same order in every thread of the row
+        const float2 v = scratch[g * 128 + t];
+        ts += v.x; tss += v.y;
+      }
+      const float mean = ts * (1.0f / C);
+      const float rstd = rsqrtf(fmaxf(tss * (1.0f / C) - mean * mean, 0.f) + 1e-5f);
+      const float2 nm = make_float2(-mean, -mean), rs = make_float2(rstd, rstd);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint4 w4 = make_uint4(0u, 0u, 0u, 0u);
+        if (valid) {
+          float2 wv[4], bv[4];
+          ld_pairs<kPrmSmem>(prm[0] + 8 * j, wv);
+          ld_pairs<kPrmSmem>(prm[1] + 8 * j, bv);
+          uint32_t ww[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 d = __fmul2_rn(__fadd2_rn(xv[4 * j + i], nm), rs);
+            ww[i] = f2_to_bf2(__ffma2_rn(d, wv[i], bv[i]));
+          }
+          w4 = make_uint4(ww[0], ww[1], ww[2], ww[3]);
+        }
+        *reinterpret_cast<uint4*>(rowA + (((j0 + j) ^ sw) << 4)) = w4;
+      }
+    }
+    fence_async_proxy();
+    tc_fence_before();
+    named_bar_sync(bar_id, kChainThreads);
+    if (lead) {
+      if (elect_one()) {
+#pragma unroll
+        for (int kc = 0; kc < kKC; ++kc) tma_store_2d(&tmap_xln, bufA + kc * kChunkBytes, kc * 64, m0);
+        tma_store_commit();
+      }
+      __syncwarp();
+    }
+    issue_gemm(0);
+
+    // ---- q, k, v: acc + bias -> O -> TMA store into columns [part C, part C + C) of qkv
+#pragma unroll
+    for (int part = 0; part < 3; ++part) {
+      mbar_wait(&mma_bar[chain], ph_mma);
+      ph_mma ^= 1;
+      tc_fence_after();
+      float v[kTailCols];
+      tmem_ld32(t_row, v);
+      tmem_ld_wait();
+      tc_fence_before();
+      if (lead) {
+        if (elect_one()) tma_store_wait_read<0>();   // the previous part's store has read O
+        __syncwarp();
+      }
+      named_bar_sync(bar_id, kChainThreads);   // every thread holds its accumulator columns: TMEM and O are free
+      if (part < 2) issue_gemm(part + 1);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint4 w4 = make_uint4(0u, 0u, 0u, 0u);
+        if (valid) {
+          float2 bv[4];
+          ld_pairs<kPrmSmem>(prm[2 + part] + 8 * j, bv);
+          uint32_t ww[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) ww[i] = f2_to_bf2(__fadd2_rn(make_float2(v[8 * j + 2 * i], v[8 * j + 2 * i + 1]), bv[i]));
+          w4 = make_uint4(ww[0], ww[1], ww[2], ww[3]);
+        }
+        *reinterpret_cast<uint4*>(rowO + (((j0 + j) ^ sw) << 4)) = w4;
+      }
+      fence_async_proxy();
+      named_bar_sync(bar_id, kChainThreads);
+      if (lead) {
+        if (elect_one()) {
+#pragma unroll
+          for (int kc = 0; kc < kKC; ++kc) tma_store_2d(&tmap_qkv, bufO + kc * kChunkBytes, part * C + kc * 64, m0);
+          tma_store_commit();
+        }
+        __syncwarp();
+      }
+    }
+  }
+  if (lead) tma_store_wait_all<0>();
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------
 // The same tail for C = 256 (sa2 on 7x7 maps, sa3 on 3x3 maps): the three weight matrices (3 x 128
 // KB) do not fit next to a tile, so ONE matrix is resident at a time.  Its four 32 KB K chunks are
 // loaded by TMA as soon as the previous GEMM's MMAs have retired, i.e. they land while the epilogue

@@ -328,6 +328,8 @@ class Engine : public IEngine {
       DMB_CUDA(cudaFuncSetAttribute(attn_tail256_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail256_smem_bytes()));
       DMB_CUDA(cudaFuncSetAttribute(attn_tail_kernel<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail_smem_bytes<64, 4>()));
       DMB_CUDA(cudaFuncSetAttribute(attn_tail_kernel<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail_smem_bytes<128, 2>()));
+      DMB_CUDA(cudaFuncSetAttribute(ln_qkv_kernel<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail_smem_bytes<64, 4>()));
+      DMB_CUDA(cudaFuncSetAttribute(ln_qkv_kernel<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, attn_tail_smem_bytes<128, 2>()));
     }
     {
       const char* le = getenv("DMB200_FUSE_LN1");
@@ -344,6 +346,7 @@ class Engine : public IEngine {
     if (const char* e = getenv("DMB200_ATTN_MMA")) use_mma_attention_ = e[0] != '0';    // 0: the tcgen05 kernel
     if (const char* e = getenv("DMB200_EAGER_GRAPH")) eager_graph_ = e[0] != '0';
     if (const char* e = getenv("DMB200_TAIL256")) use_tail256_ = e[0] != '0';
+    if (const char* e = getenv("DMB200_LN_QKV")) use_ln_qkv_ = e[0] != '0';
     if (const char* e = getenv("DMB200_CONVIN_Z")) conv_in_z_ = std::max(0, std::min(7, atoi(e)));
     if (const char* e = getenv("DMB200_ATTN_POLY")) attn_poly_ = e[0] != '0';           // 0: every exp2 on MUFU
     if constexpr (std::is_same<T, float>::value) {
@@ -491,6 +494,7 @@ class Engine : public IEngine {
   size_t stat_arena_left_ = 0;
   bool use_tc_attention_ = true;
   int conv_in_z_ = 0;               // DMB200_CONVIN_Z: CTAs per sample of the U-Net's input conv (0: 7 below 64 samples, else 1)
+  bool use_ln_qkv_ = true;          // DMB200_LN_QKV=0: the attention block's LayerNorm and in-projection as separate launches everywhere
   bool use_tail256_ = true;         // DMB200_TAIL256=0: the C = 256 attention blocks keep their separate Linear / LayerNorm launches
   bool eager_graph_ = true;         // DMB200_EAGER_GRAPH=0: dmb_denoise_cond_step launches its kernels one by one
   bool use_mma_attention_ = true;   // warp-level MMA attention (attention_mma.cuh) for maps > 3x3 in bf16 mode
@@ -1139,14 +1143,42 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
       });
       return out;
     };
-    Act<T> xl = x_is_normed ? x : ln(x, p + ".ln");
+    // LayerNorm + in-projection in one kernel (ln_qkv_kernel) where the LayerNorm is still its own pass
+    bool lnqkv = false;
+    if constexpr (std::is_same<T, __nv_bfloat16>::value)
+      lnqkv = !x_is_normed && use_ln_qkv_ && use_fused_tail_ && (C == 64 || C == 128);
+    Act<T> xl = x_is_normed ? x : (lnqkv ? new_act(pool, nn, H, W, C, false) : ln(x, p + ".ln"));
     Act<T> qkv = new_act(pool, nn, H, W, 3 * C, false);
     const double tok = static_cast<double>(nn) * H * W;
     auto lin_tag = [&](int K, int N) {
       ops.tag("linear " + std::to_string(K) + "->" + std::to_string(N) + " @" + std::to_string(H), 2.0 * tok * K * N);
     };
-    lin_tag(C, 3 * C);
-    ops.push_back(op_lin(xl, gw_.at(p + ".qkv"), qkv, 0, nullptr));
+    if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+      if (lnqkv) {
+        const GemmW<T>& wq = gw_.at(p + ".qkv");
+        LnQkvParams lp{};
+        lp.geo = x.g;
+        lp.m_tiles = cdiv(x.g.rows_valid, kTileM);
+        lp.ln_w = f(p + ".ln.weight");
+        lp.ln_b = f(p + ".ln.bias");
+        lp.bqkv = wq.bias;
+        DMB_REQUIRE(lp.bqkv && wq.rows_per_tap == 3 * C, "in-projection: bias and an unpadded [3C, C] weight");
+        ops.tag("ln_qkv " + std::to_string(C) + " @" + std::to_string(H), 2.0 * tok * C * 3 * C, 5.0 * tok * C * sizeof(T));
+        ops.push_back([this, x, xl, qkv, wq, lp, C](cudaStream_t s) {
+          const int grid = std::min(lp.m_tiles, num_sms_);
+          if (C == 64)
+            launch(ln_qkv_kernel<64, 4>, grid, kTailThreads, attn_tail_smem_bytes<64, 4>(), s, x.tmap, wq.tmap_for(64), xl.tmap, qkv.tmap, lp);
+          else
+            launch(ln_qkv_kernel<128, 2>, grid, kTailThreads, attn_tail_smem_bytes<128, 2>(), s, x.tmap, wq.tmap_for(128), xl.tmap, qkv.tmap, lp);
+          DMB_CHECK_LAUNCH();
+          count();
+        });
+      }
+    }
+    if (!lnqkv) {
+      lin_tag(C, 3 * C);
+      ops.push_back(op_lin(xl, gw_.at(p + ".qkv"), qkv, 0, nullptr));
+    }
     Act<T> av = new_act(pool, nn, H, W, C, false);
     ops.tag("attention L=" + std::to_string(H * W) + " d=" + std::to_string(C / 4), 4.0 * nn * H * W * H * W * C);
     ops.push_back([this, qkv, av, C](cudaStream_t s) {

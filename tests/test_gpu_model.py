@@ -300,7 +300,7 @@ def test_strided_ddim_extension_matches_oracle(models):
 
 
 @pytest.mark.parametrize("switch", ["DMB200_FUSED_TAIL", "DMB200_ROW3", "DMB200_FUSE_LN1", "DMB200_ATTN_MMA",
-                                    "DMB200_ATTN_POLY", "DMB200_TAIL256"])
+                                    "DMB200_ATTN_POLY", "DMB200_TAIL256", "DMB200_LN_QKV"])
 def test_fused_kernels_agree_with_separate_launches(models, switch):
     """The fused attention-block tail (attn_tail_kernel) and the kernel-row A windows of the 3x3
     convs (kRow3) are re-schedulings of the same arithmetic: the U-Net output must agree with the
@@ -316,8 +316,12 @@ def test_fused_kernels_agree_with_separate_launches(models, switch):
     x = torch.randn((B, 4, 28, 28), generator=g).cuda()
     t = torch.tensor([1000, 700, 400, 100, 10, 1], dtype=torch.long).cuda()
     outs, launches = [], []
+    # the two LayerNorm fusions exclude each other per block: the GroupNorm kernel applies the block's first
+    # LayerNorm on small activations (all six blocks at this batch), ln_qkv_kernel takes the blocks where it
+    # does not (C = 64 / 128) -- each is tested with the other one out of the way
+    fixed = {"DMB200_FUSE_LN1": {"DMB200_LN_QKV": "0"}, "DMB200_LN_QKV": {"DMB200_FUSE_LN1": "0"}}.get(switch, {})
     for val in ("1", "0"):
-        ctx = _fresh_context({switch: val})
+        ctx = _fresh_context({switch: val, **fixed})
         try:
             ctx.ensure_unet(unet)
             ctx.reset_launch_count()
@@ -333,6 +337,8 @@ def test_fused_kernels_agree_with_separate_launches(models, switch):
         assert launches[1] - launches[0] == 18, launches
     if switch == "DMB200_TAIL256":      # sa2 and sa3: 3 Linear + 1 LayerNorm launches -> 1, twice
         assert launches[1] - launches[0] == 6, launches
+    if switch == "DMB200_LN_QKV":       # sa1, sa4, sa5, sa6: LayerNorm + in-projection launches -> 1 (one-pass variance)
+        assert launches[1] - launches[0] == 4, launches
     if switch == "DMB200_FUSE_LN1":     # 6 LayerNorm launches saved; same arithmetic in the same order
         assert launches[1] - launches[0] == 6, launches
         assert r < 1e-6, r
