@@ -347,6 +347,7 @@ class Engine : public IEngine {
     if (const char* e = getenv("DMB200_EAGER_GRAPH")) eager_graph_ = e[0] != '0';
     if (const char* e = getenv("DMB200_TAIL256")) use_tail256_ = e[0] != '0';
     if (const char* e = getenv("DMB200_LN_QKV")) use_ln_qkv_ = e[0] != '0';
+    if (const char* e = getenv("DMB200_GN_INPLACE")) gn_inplace_ = e[0] != '0';
     if (const char* e = getenv("DMB200_CONVIN_Z")) conv_in_z_ = std::max(0, std::min(7, atoi(e)));
     if (const char* e = getenv("DMB200_ATTN_POLY")) attn_poly_ = e[0] != '0';           // 0: every exp2 on MUFU
     if constexpr (std::is_same<T, float>::value) {
@@ -494,6 +495,7 @@ class Engine : public IEngine {
   size_t stat_arena_left_ = 0;
   bool use_tc_attention_ = true;
   int conv_in_z_ = 0;               // DMB200_CONVIN_Z: CTAs per sample of the U-Net's input conv (0: 7 below 64 samples, else 1)
+  bool gn_inplace_ = true;          // DMB200_GN_INPLACE=0: GroupNorm apply writes a separate tensor instead of rewriting the conv output in place
   bool use_ln_qkv_ = true;          // DMB200_LN_QKV=0: the attention block's LayerNorm and in-projection as separate launches everywhere
   bool use_tail256_ = true;         // DMB200_TAIL256=0: the C = 256 attention blocks keep their separate Linear / LayerNorm launches
   bool eager_graph_ = true;         // DMB200_EAGER_GRAPH=0: dmb_denoise_cond_step launches its kernels one by one
@@ -1054,7 +1056,11 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
   auto gn = [&](const Act<T>& raw, const std::string& gname, int mode, const Act<T>* residual, int emb_off,
                 int n_out = 0, const std::string& ln_name = std::string()) {
     if (n_out == 0) n_out = raw.g.n;
-    Act<T> out = new_act(pool, n_out, raw.g.H, raw.g.W, raw.C, false);
+    // In place where nothing else reads the un-normalised conv output (no debug taps, no fan-out of a shared
+    // guidance prefix): a thread rewrites exactly the 16-byte vectors it has just read (pad rows are zeros on
+    // both sides), so the pass touches half the cache lines and the next conv finds more of its input in L2.
+    const bool inplace = gn_inplace_ && !keep_taps_ && n_out == raw.g.n;
+    Act<T> out = inplace ? raw : new_act(pool, n_out, raw.g.H, raw.g.W, raw.C, false);
     // fused where the launch is latency-bound (small maps / small batch: one launch and one pass
     // less); on large activations the two streaming kernels are faster than the fused one, whose
     // per-token shuffles make it issue-bound (measured at batch 256: 57 vs 34 + 15 us at 28x28)
