@@ -1336,10 +1336,15 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     Act<T> cat = new_act(pool, x.g.n, skip.g.H, skip.g.W, skip.C + x.C, false);
     ops.tag("upcat", 0, 2.0 * cat.g.n * cat.g.H * cat.g.W * cat.C * sizeof(T));
     ops.push_back([this, x, skip, cat](cudaStream_t s) {
-      const int vpr = cat.C / 8;
-      const int quarter = cdiv(cdiv(static_cast<long long>(cat.g.H) * cat.g.W * vpr, kUpcatU), vpr) * vpr;
-      launch(upcat_kernel<T>, dim3(cdiv(quarter, 256), cat.g.n), 256, 0, s, skip.p, skip.C, skip.g.n, x.p, x.g, x.C, cat.g,
-             cat.p, quarter);
+      // (vectors per sample of each part / kUpcatU, rounded up to whole pixels)
+      auto quarter_of = [&](int c) {
+        const int vpr = c / 8;
+        return static_cast<int>(cdiv(cdiv(static_cast<long long>(cat.g.H) * cat.g.W * vpr, kUpcatU), vpr) * vpr);
+      };
+      const int qa = quarter_of(skip.C), qb = quarter_of(x.C);
+      const int blocks_a = cdiv(qa, 256), blocks_b = cdiv(qb, 256);
+      launch(upcat_kernel<T>, dim3(blocks_a + blocks_b, cat.g.n), 256, 0, s, skip.p, skip.C, skip.g.n, x.p, x.g, x.C, cat.g,
+             cat.p, blocks_a, qa, qb);
       DMB_CHECK_LAUNCH();
       count();
     });

@@ -567,23 +567,29 @@ __global__ void maxpool2_kernel(const T* __restrict__ in, Geo gi, Geo go, int C,
 
 // Up-stage input: cat([skip, pad(bilinear_x2_align_corners(x))], channel).
 // models/unet_cond.py:76, 87-97.  Output geometry = skip geometry.
-// grid = (chunks of the sample's H*W*C/8 vectors, n); a thread moves kUpcatU vectors of the same
-// channel group, all loads first (a 16-byte vector per thread does not keep HBM busy).
+// grid = (blocks_a + blocks_b, n): the first blocks_a blocks of a sample copy the skip channels, the others
+// interpolate the upsampled channels -- a warp is all copy or all interpolation (with both kinds of vector in
+// one row of threads every warp ran both paths with half of its lanes idle, and the kernel is bound by issue
+// slots).  A thread moves kUpcatU vectors of the same channel group, all loads first (a 16-byte vector per
+// thread does not keep HBM busy).
 constexpr int kUpcatU = 4;
 template <typename T>
 __global__ void __launch_bounds__(256, 4)
 upcat_kernel(const T* __restrict__ skip, int Cs, int n_skip, const T* __restrict__ xin, Geo gx,
-             int Cx, Geo go, T* __restrict__ out, int quarter /* vectors per sample / kUpcatU, multiple of C/8 */) {
+             int Cx, Geo go, T* __restrict__ out, int blocks_a, int quarter_a, int quarter_b
+             /* vectors per sample and part / kUpcatU, multiples of the part's vectors per pixel */) {
   pdl_trigger();
   pdl_wait();
   const int C = Cs + Cx;
-  const int vpr = C / 8;
+  const bool copy = static_cast<int>(blockIdx.x) < blocks_a;
+  const int vpr = (copy ? Cs : Cx) / 8;            // this part's vectors per pixel
+  const int quarter = copy ? quarter_a : quarter_b;
   const int per_sample = go.H * go.W * vpr;
-  const int v0 = blockIdx.x * blockDim.x + threadIdx.x;
+  const int v0 = (static_cast<int>(blockIdx.x) - (copy ? 0 : blocks_a)) * blockDim.x + threadIdx.x;
   if (v0 >= quarter) return;
   const int b = blockIdx.y;
   const int pix0 = v0 / vpr;
-  const int c0 = (v0 - pix0 * vpr) * 8;       // the same for all kUpcatU vectors: quarter % vpr == 0
+  const int cpart = (v0 - pix0 * vpr) * 8;    // channel inside the part; the same for all kUpcatU vectors: quarter % vpr == 0
   const int pstep = quarter / vpr;
   int row[kUpcatU], py[kUpcatU], px[kUpcatU];
   bool ok[kUpcatU];
@@ -595,19 +601,20 @@ upcat_kernel(const T* __restrict__ skip, int Cs, int n_skip, const T* __restrict
     px[u] = pix - py[u] * go.W;
     row[u] = geo_row(go, b, py[u], px[u]);
   }
-  if (c0 < Cs) {
+  if (copy) {
     // the skip tensor may hold only the shared half of a guidance pair (n_skip = go.n / 2)
     const int shift = b >= n_skip ? n_skip * go.S : 0;
     Raw8<T> r[kUpcatU];
 #pragma unroll
     for (int u = 0; u < kUpcatU; ++u)
-      if (ok[u]) r[u].load(skip + static_cast<size_t>(row[u] - shift) * Cs + c0);
+      if (ok[u]) r[u].load(skip + static_cast<size_t>(row[u] - shift) * Cs + cpart);
 #pragma unroll
     for (int u = 0; u < kUpcatU; ++u)
-      if (ok[u]) r[u].store(out + static_cast<size_t>(row[u]) * C + c0);
+      if (ok[u]) r[u].store(out + static_cast<size_t>(row[u]) * C + cpart);
     return;
   }
-  const int cx = c0 - Cs;
+  const int cx = cpart;
+  const int c0 = Cs + cpart;
   const int Hu = 2 * gx.H, Wu = 2 * gx.W;
   // align_corners=True: src = dst * (in - 1) / (out - 1), computed in fp32 like ATen.
   const float sy = (Hu > 1) ? static_cast<float>(gx.H - 1) / static_cast<float>(Hu - 1) : 0.f;
