@@ -118,30 +118,34 @@ attention_mma_kernel(const __nv_bfloat16* __restrict__ qkv, Geo g, int E, __nv_b
 
   pdl_trigger();
   pdl_wait();
-  // ---- stage K and V of the (sample, head): 16-byte loads, two keys' worth in flight per thread
+  // ---- stage K and V of the (sample, head): 16-byte loads, kSU key chunks of each in flight per thread.  d_head
+  // 32 / 64: the whole head in one round trip (L = 196, d 32: 82 -> 78 us at batch 256); d_head 16 keeps two per
+  // round -- measured with eight: L = 784 419 -> 425 us, L = 196 49 -> 51 us (three CTAs per SM already overlap
+  // one CTA's staging with the others' MMAs, and the deeper batch costs registers)
   {
+    constexpr int kSU = (D == 16) ? 2 : 8;
     const int total = lpad * CPR;
     const uint4 zero = make_uint4(0, 0, 0, 0);
-    for (int i0 = tid; i0 < total; i0 += 2 * blockDim.x) {
-      uint4 kv[2], vv[2];
-      int key[2], c[2];
+    for (int i0 = tid; i0 < total; i0 += kSU * blockDim.x) {
+      uint4 kv[kSU], vv[kSU];
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
+      for (int u = 0; u < kSU; ++u) {
         const int idx = i0 + u * blockDim.x;
-        key[u] = idx / CPR;
-        c[u] = idx - key[u] * CPR;
+        const int key = idx / CPR, c = idx - key * CPR;
         kv[u] = zero; vv[u] = zero;
-        if (idx < total && key[u] < L) {
-          const __nv_bfloat16* rp = qkv + static_cast<size_t>(geo_row_of_pixel(g, b, key[u])) * ld + h * D + 8 * c[u];
+        if (idx < total && key < L) {
+          const __nv_bfloat16* rp = qkv + static_cast<size_t>(geo_row_of_pixel(g, b, key)) * ld + h * D + 8 * c;
           kv[u] = *reinterpret_cast<const uint4*>(rp + E);
           vv[u] = *reinterpret_cast<const uint4*>(rp + 2 * E);
         }
       }
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        if (i0 + u * blockDim.x < total) {
-          *reinterpret_cast<uint4*>(Ks + am_off<D>(key[u], c[u])) = kv[u];
-          *reinterpret_cast<uint4*>(Vs + am_off<D>(key[u], c[u])) = vv[u];
+      for (int u = 0; u < kSU; ++u) {
+        const int idx = i0 + u * blockDim.x;
+        if (idx < total) {
+          const int key = idx / CPR, c = idx - key * CPR;
+          *reinterpret_cast<uint4*>(Ks + am_off<D>(key, c)) = kv[u];
+          *reinterpret_cast<uint4*>(Vs + am_off<D>(key, c)) = vv[u];
         }
       }
     }

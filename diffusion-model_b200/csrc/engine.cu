@@ -347,6 +347,7 @@ class Engine : public IEngine {
     if (const char* e = getenv("DMB200_EAGER_GRAPH")) eager_graph_ = e[0] != '0';
     if (const char* e = getenv("DMB200_TAIL256")) use_tail256_ = e[0] != '0';
     if (const char* e = getenv("DMB200_LN_QKV")) use_ln_qkv_ = e[0] != '0';
+    if (const char* e = getenv("DMB200_ATTN_MMA_MINL")) attn_mma_min_l_ = std::max(1, atoi(e));
     if (const char* e = getenv("DMB200_GN_INPLACE")) gn_inplace_ = e[0] != '0';
     if (const char* e = getenv("DMB200_CONVIN_Z")) conv_in_z_ = std::max(0, std::min(7, atoi(e)));
     if (const char* e = getenv("DMB200_ATTN_POLY")) attn_poly_ = e[0] != '0';           // 0: every exp2 on MUFU
@@ -496,6 +497,7 @@ class Engine : public IEngine {
   bool use_tc_attention_ = true;
   int conv_in_z_ = 0;               // DMB200_CONVIN_Z: CTAs per sample of the U-Net's input conv (0: 7 below 64 samples, else 1)
   bool gn_inplace_ = true;          // DMB200_GN_INPLACE=0: GroupNorm apply writes a separate tensor instead of rewriting the conv output in place
+  int attn_mma_min_l_ = 9;          // DMB200_ATTN_MMA_MINL=17: 3x3 maps (L = 9) on the CUDA-core kernel again (17.3 vs 13.4 us at batch 256)
   bool use_ln_qkv_ = true;          // DMB200_LN_QKV=0: the attention block's LayerNorm and in-projection as separate launches everywhere
   bool use_tail256_ = true;         // DMB200_TAIL256=0: the C = 256 attention blocks keep their separate Linear / LayerNorm launches
   bool eager_graph_ = true;         // DMB200_EAGER_GRAPH=0: dmb_denoise_cond_step launches its kernels one by one
@@ -1190,7 +1192,7 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     ops.push_back([this, qkv, av, C](cudaStream_t s) {
       const int L = qkv.g.H * qkv.g.W, D = C / 4;
       if constexpr (std::is_same<T, __nv_bfloat16>::value) {
-        if (use_mma_attention_ && use_tc_attention_ && L > 16) {
+        if (use_mma_attention_ && use_tc_attention_ && L >= attn_mma_min_l_) {
           // one CTA per (sample, head) with up to 7 warps, each owning 16-row query tiles; when the
           // batch is too small to fill the chip twice the tiles are spread over more CTAs
           const int ntiles = cdiv(L, 16);

@@ -42,11 +42,15 @@ S.step(f"{G}/ev_step2.csv", f"{P}/{tag}_ncu_step_launches.md",
 notes = {"gemm_tc_kernel": "gemm_tc_kernel: every launch of one CFG step at batch 256 (3x3 convs incl. kRow3 and pixel-major tiles, qkv projections).",
          "gn1_apply_kernel": "gn1_apply_kernel: every launch of one CFG step at batch 256 (statistics arrive as two 64-bit fixed-point sums per sample).",
          "attention_mma_kernel": "attention_mma_kernel: the attention launches of one CFG step at batch 256 (L = 784, 196, 196, 49, 49 -- L = 9 runs on CUDA cores).",
-         "attn_tail": "attn_tail kernels (out-projection + residual + LayerNorm + MLP + residual in one launch; C = 64/128 and the C = 256 form)."}
+         "attn_tail": "attn_tail kernels (out-projection + residual + LayerNorm + MLP + residual in one launch; C = 64/128 and the C = 256 form).",
+         "ln_qkv_kernel": "ln_qkv_kernel: LayerNorm + in-projection of the attention blocks with C = 64 / 128 at batch 256 (sa1, sa4, sa5, sa6).",
+         "upcat_kernel": "upcat_kernel: skip copy + bilinear x2 + concat of the three Up stages (copy and interpolation in separate blocks).",
+         "cfg_step_kernel": "cfg_step_kernel: out conv on both guidance halves + CFG combine + DDPM update (feature rows staged through shared memory).",
+         "conv_in_mma_kernel": "conv_in_mma_kernel: 4 -> 64 input conv on mma.sync (all global loads of a CTA issued up front)."}
 only = sys.argv[2:]    # optional: summarise only these kernels (the others keep their earlier captures)
 counts = {}
 for k, note in notes.items():
-    if only and k not in only:
+    if (only and k not in only) or not os.path.exists(f"{G}/ev_full_{k}.raw.csv"):
         continue
     counts[k] = second_half_raw(f"{G}/ev_full_{k}.raw.csv", f"{G}/ev_full2_{k}.raw.csv")
     S.full(f"{G}/ev_full2_{k}.raw.csv", f"{P}/{tag}_ncu_full_{k.replace('_kernel', '')}.md", note)
