@@ -842,7 +842,7 @@ cfg_step_kernel(const T* __restrict__ feat, Geo g, int B, const StepParams* __re
   constexpr int kE = 16 / static_cast<int>(sizeof(T));                    // elements per chunk
   constexpr int kBuf = sizeof(T) == 2 ? 2 : 1;   // bf16: both halves in flight at once; fp32 (32 KB per half): one after the other
   __shared__ __align__(16) uint8_t rows[kBuf][128 * kChunks * 16];
-  __shared__ float ws[kLatC * 64];
+  __shared__ __align__(16) float ws[kLatC * 64];
   __shared__ float bs[kLatC];
   const int HW = g.H * g.W;
   const int b = blockIdx.y;
@@ -881,9 +881,16 @@ cfg_step_kernel(const T* __restrict__ feat, Geo g, int B, const StepParams* __re
         v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
       }
 #pragma unroll
-      for (int i = 0; i < kE; ++i)
+      for (int c = 0; c < kLatC; ++c) {   // (weights as 16-byte broadcast reads; per output the same ascending-k FMA chain)
+        float wv[kE];
 #pragma unroll
-        for (int c = 0; c < kLatC; ++c) e[c] = fmaf(v[i], ws[c * 64 + ch * kE + i], e[c]);
+        for (int i = 0; i < kE; i += 4) {
+          const float4 w4 = *reinterpret_cast<const float4*>(ws + c * 64 + ch * kE + i);
+          wv[i] = w4.x; wv[i + 1] = w4.y; wv[i + 2] = w4.z; wv[i + 3] = w4.w;
+        }
+#pragma unroll
+        for (int i = 0; i < kE; ++i) e[c] = fmaf(v[i], wv[i], e[c]);
+      }
     }
   };
   uint4 stage[kBuf][kChunks];
@@ -892,6 +899,17 @@ cfg_step_kernel(const T* __restrict__ feat, Geo g, int B, const StepParams* __re
   const StepParams p = *pp;
   for (int i = tid; i < kLatC * 64; i += 128) ws[i] = p.w_out[i];
   if (tid < kLatC) bs[tid] = p.b_out[tid];
+  // the step's scalars and this pixel's x_t: a chain of dependent loads (pp -> t -> coefficients) that would
+  // otherwise start only after the dot products
+  const long long t = p.t_vec[b];
+  // the Python layer asserts 1 <= t <= T like the reference (diff.py:140); the row index is clamped
+  // as well so that a raw C-ABI caller with a bad t cannot read outside the table
+  const long long tr = t < 1 ? 0 : (t > p.T ? p.T - 1 : t - 1);
+  const float c1 = p.coef[tr * 3 + 0], sqrt_a = p.coef[tr * 3 + 1], sigma = p.coef[tr * 3 + 2];
+  const size_t base = static_cast<size_t>(b) * kLatC * HW + min(pix, HW - 1);
+  float xin[kLatC];
+#pragma unroll
+  for (int c = 0; c < kLatC; ++c) xin[c] = p.x_in[base + c * HW];
   store_half(0, stage[0]);
   if constexpr (kBuf == 2) store_half(1, stage[1]);
   __syncthreads();
@@ -909,12 +927,7 @@ cfg_step_kernel(const T* __restrict__ feat, Geo g, int B, const StepParams* __re
     if (pix < HW) dot_half(0, ec);
   }
   if (pix >= HW) return;
-  const long long t = p.t_vec[b];
   const int slot = (p.slot_t0 - static_cast<int>(t)) / p.t_stride;
-  // the Python layer asserts 1 <= t <= T like the reference (diff.py:140); the row index is clamped
-  // as well so that a raw C-ABI caller with a bad t cannot read outside the table
-  const long long tr = t < 1 ? 0 : (t > p.T ? p.T - 1 : t - 1);
-  const float c1 = p.coef[tr * 3 + 0], sqrt_a = p.coef[tr * 3 + 1], sigma = p.coef[tr * 3 + 2];
   float nz[kLatC] = {0.f, 0.f, 0.f, 0.f};
   if (t != 1) {
     if (p.noise) {
@@ -925,10 +938,9 @@ cfg_step_kernel(const T* __restrict__ feat, Geo g, int B, const StepParams* __re
       philox_normal4(p.seed, p.sample_offset + b, static_cast<uint32_t>(t), static_cast<uint32_t>(pix), nz);
     }
   }
-  const size_t base = static_cast<size_t>(b) * kLatC * HW + pix;
 #pragma unroll
   for (int c = 0; c < kLatC; ++c) {
-    const float xv = p.x_in[base + c * HW];
+    const float xv = xin[c];
     const float eps = eu[c] + p.guidance * (ec[c] - eu[c]);
     if (p.x_dump) p.x_dump[p.dump_step_stride * slot + base + c * HW] = xv;
     if (p.eps_out) p.eps_out[p.dump_step_stride * slot + base + c * HW] = eps;
