@@ -1326,8 +1326,8 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     Act<T> pooled = new_act(pool, x.g.n, x.g.H / 2, x.g.W / 2, x.C, false);
     ops.tag("maxpool", 0, 1.25 * pooled.g.n * x.g.H * x.g.W * x.C * sizeof(T));
     ops.push_back([this, x, pooled](cudaStream_t s) {
-      const long long total = static_cast<long long>(pooled.g.n) * pooled.g.H * pooled.g.W * (x.C / 8);
-      launch(maxpool2_kernel<T>, cdiv(total, 256), 256, 0, s, x.p, x.g, pooled.g, x.C, pooled.p);
+      const int per_sample = pooled.g.H * pooled.g.W * (x.C / 8);
+      launch(maxpool2_kernel<T>, dim3(cdiv(per_sample, 256), pooled.g.n), 256, 0, s, x.p, x.g, pooled.g, x.C, pooled.p);
       DMB_CHECK_LAUNCH();
       count();
     });
