@@ -347,6 +347,7 @@ class Engine : public IEngine {
     if (const char* e = getenv("DMB200_EAGER_GRAPH")) eager_graph_ = e[0] != '0';
     if (const char* e = getenv("DMB200_TAIL256")) use_tail256_ = e[0] != '0';
     if (const char* e = getenv("DMB200_LN_QKV")) use_ln_qkv_ = e[0] != '0';
+    if (const char* e = getenv("DMB200_GN_SPLITS")) gn_splits_ = atoi(e);
     if (const char* e = getenv("DMB200_ATTN_MMA_MINL")) attn_mma_min_l_ = std::max(1, atoi(e));
     if (const char* e = getenv("DMB200_GN_INPLACE")) gn_inplace_ = e[0] != '0';
     if (const char* e = getenv("DMB200_CONVIN_Z")) conv_in_z_ = std::max(0, std::min(7, atoi(e)));
@@ -498,6 +499,7 @@ class Engine : public IEngine {
   int conv_in_z_ = 0;               // DMB200_CONVIN_Z: CTAs per sample of the U-Net's input conv (0: 7 below 64 samples, else 1)
   bool gn_inplace_ = true;          // DMB200_GN_INPLACE=0: GroupNorm apply writes a separate tensor instead of rewriting the conv output in place
   int attn_mma_min_l_ = 9;          // DMB200_ATTN_MMA_MINL=17: 3x3 maps (L = 9) on the CUDA-core kernel again (17.3 vs 13.4 us at batch 256)
+  int gn_splits_ = 0;               // DMB200_GN_SPLITS: CTAs per sample of gn1_apply (0: by batch, see gn())
   bool use_ln_qkv_ = true;          // DMB200_LN_QKV=0: the attention block's LayerNorm and in-projection as separate launches everywhere
   bool use_tail256_ = true;         // DMB200_TAIL256=0: the C = 256 attention blocks keep their separate Linear / LayerNorm launches
   bool eager_graph_ = true;         // DMB200_EAGER_GRAPH=0: dmb_denoise_cond_step launches its kernels one by one
@@ -1083,9 +1085,12 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     const T* res = residual ? residual->p : nullptr;
     const float* embproj = P.embproj;
     const int total_vec = raw.g.H * raw.g.W * raw.C / 8;
-    // enough CTAs to fill the chip at small batch, whole samples per CTA at large batch
-    const int want = (8 * num_sms_ + n_out - 1) / n_out;
-    const int splits = std::max(1, std::min(std::min(want, 16), total_vec / 512));
+    // enough CTAs to fill the chip at small batch, few and long CTAs at large batch (measured at batch 256 with
+    // 1 / 2 / 3 / 6 / 13 CTAs per sample: step 2.445 / 2.433 / 2.455 / 2.510 / 2.594 ms -- the prologue of a CTA
+    // costs more than the last partial wave)
+    const int want = (6 * num_sms_ + n_out - 1) / n_out;
+    int splits = std::max(1, std::min(std::min(want, 16), total_vec / 512));
+    if (gn_splits_ > 0) splits = std::max(1, std::min(gn_splits_, total_vec / 256));   // experiment override
     if (mode == GN_ADD_EMB && !emb_joined) {   // first consumer of the embedding projections: join the side stream
       emb_joined = true;
       ops.tag("emb join");
