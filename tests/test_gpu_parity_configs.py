@@ -92,6 +92,40 @@ def test_config3_batch256_step_parity(models, precision):
         assert r["x_max_abs"] < tol[2] * r["x_ref_max"], (k, r)
 
 
+def test_mid_batch_kernel_mix_step_parity(models):
+    """A batch between the tested extremes (48: doubled 96).  It selects a MIX of the launch forms: the first
+    LayerNorm of sa5 / sa4 / sa2 / sa3 is applied by the GroupNorm kernel (activations <= 4 MB) while sa6 and sa1
+    go through ln_qkv_kernel, the convs keep the pixel-matrix tiles (pixel-major needs a doubled batch >= 256) with
+    batch-dependent N tiles.  Same check and tolerance as the batch-256 step, on three samples."""
+    from dmb200 import context_for
+    from diff import Diffuser
+    unet, _, sd, _ = models
+    B = 48
+    y, vals, mask, counts = synth.mixed_conditions(B, seed=3)
+    pick = torch.tensor([0, counts[0][1] + 1, B - 1])
+    d = Diffuser(num_timesteps=1000, device=DEV)
+    ctx = context_for(DEV, "bf16")
+    ctx.ensure_unet(unet)
+    _, alphas, abars = R.schedule(1000)
+    g = torch.Generator().manual_seed(48)
+    x = torch.randn((B, 4, 28, 28), generator=g) * 5.0
+    nz = torch.randn((B, 4, 28, 28), generator=g)
+    t = torch.full((B,), 400, dtype=torch.long)
+    out, eps = ctx.denoise_cond_step(x.to(DEV), t.to(DEV), y.to(DEV), 0, vals.to(DEV), mask.to(DEV), 3.0,
+                                     d.step_coefficients(), noise=nz.to(DEV), want_eps=True)
+    with torch.no_grad():
+        x_ref, eps_ref = R.denoise_cond(sd, x[pick], t[pick], y[pick], 3.0, 0, vals[pick], mask[pick], nz[pick],
+                                        alphas, abars)
+    out, eps = out.cpu()[pick], eps.cpu()[pick]
+    row = {"eps_rel_l2": rel_l2(eps, eps_ref), "eps_max_abs": max_abs(eps, eps_ref),
+           "eps_ref_max": float(eps_ref.abs().max()), "x_max_abs": max_abs(out, x_ref),
+           "x_ref_max": float(x_ref.abs().max())}
+    report("mid_batch48_step_bf16", row)
+    assert row["eps_rel_l2"] < 1.6e-2, row
+    assert row["eps_max_abs"] < 2.5e-2 * row["eps_ref_max"], row
+    assert row["x_max_abs"] < 6e-4 * row["x_ref_max"], row
+
+
 def test_config3_batch256_short_loop_matches_oracle_subset(models):
     """The CUDA-graph loop at the benched batch: 6 steps from t = 1000 with injected noise, against
     the oracle run on four of the 256 samples.  Tolerance: latent rel-L2 <= 4e-3 (a step's x error
