@@ -41,7 +41,7 @@ S.step(f"{G}/ev_step2.csv", f"{P}/{tag}_ncu_step_launches.md",
        f"DMB200_EAGER_GRAPH=0 python scripts/one_step.py 256 2  (second step: {n} launches)")
 notes = {"gemm_tc_kernel": "gemm_tc_kernel: every launch of one CFG step at batch 256 (3x3 convs incl. kRow3 and pixel-major tiles, qkv projections).",
          "gn1_apply_kernel": "gn1_apply_kernel: every launch of one CFG step at batch 256 (statistics arrive as two 64-bit fixed-point sums per sample).",
-         "attention_mma_kernel": "attention_mma_kernel: the attention launches of one CFG step at batch 256 (L = 784, 196, 196, 49, 49 -- L = 9 runs on CUDA cores).",
+         "attention_mma_kernel": "attention_mma_kernel: the attention launches of one CFG step at batch 256 (L = 784, 196, 196, 49, 49, 9).",
          "attn_tail": "attn_tail kernels (out-projection + residual + LayerNorm + MLP + residual in one launch; C = 64/128 and the C = 256 form).",
          "ln_qkv_kernel": "ln_qkv_kernel: LayerNorm + in-projection of the attention blocks with C = 64 / 128 at batch 256 (sa1, sa4, sa5, sa6).",
          "upcat_kernel": "upcat_kernel: skip copy + bilinear x2 + concat of the three Up stages (copy and interpolation in separate blocks).",
