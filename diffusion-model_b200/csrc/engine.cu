@@ -350,6 +350,7 @@ class Engine : public IEngine {
     if (const char* e = getenv("DMB200_GN_SPLITS")) gn_splits_ = atoi(e);
     if (const char* e = getenv("DMB200_ATTN_MMA_MINL")) attn_mma_min_l_ = std::max(1, atoi(e));
     if (const char* e = getenv("DMB200_GN_INPLACE")) gn_inplace_ = e[0] != '0';
+    if (const char* e = getenv("DMB200_ALIAS_ACTS")) alias_acts_ = e[0] != '0';
     if (const char* e = getenv("DMB200_CONVIN_Z")) conv_in_z_ = std::max(0, std::min(7, atoi(e)));
     if (const char* e = getenv("DMB200_ATTN_POLY")) attn_poly_ = e[0] != '0';           // 0: every exp2 on MUFU
     if constexpr (std::is_same<T, float>::value) {
@@ -497,6 +498,7 @@ class Engine : public IEngine {
   size_t stat_arena_left_ = 0;
   bool use_tc_attention_ = true;
   int conv_in_z_ = 0;               // DMB200_CONVIN_Z: CTAs per sample of the U-Net's input conv (0: 7 below 64 samples, else 1)
+  bool alias_acts_ = true;          // DMB200_ALIAS_ACTS=0: attention-block tails / ln_qkv write separate tensors instead of storing over their input tiles
   bool gn_inplace_ = true;          // DMB200_GN_INPLACE=0: GroupNorm apply writes a separate tensor instead of rewriting the conv output in place
   int attn_mma_min_l_ = 9;          // DMB200_ATTN_MMA_MINL=17: 3x3 maps (L = 9) on the CUDA-core kernel again (17.3 vs 13.4 us at batch 256)
   int gn_splits_ = 0;               // DMB200_GN_SPLITS: CTAs per sample of gn1_apply (0: by batch, see gn())
@@ -1160,7 +1162,9 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     bool lnqkv = false;
     if constexpr (std::is_same<T, __nv_bfloat16>::value)
       lnqkv = !x_is_normed && use_ln_qkv_ && use_fused_tail_ && (C == 64 || C == 128);
-    Act<T> xl = x_is_normed ? x : (lnqkv ? new_act(pool, nn, H, W, C, false) : ln(x, p + ".ln"));
+    // (ln_qkv_kernel normalises a tile in shared memory and stores it over the rows it loaded: x_ln takes x's
+    // buffer -- nothing reads the un-normalised x after this block's LayerNorm -- unless debug taps keep x)
+    Act<T> xl = x_is_normed ? x : (lnqkv ? (alias_acts_ && !keep_taps_ ? x : new_act(pool, nn, H, W, C, false)) : ln(x, p + ".ln"));
     Act<T> qkv = new_act(pool, nn, H, W, 3 * C, false);
     const double tok = static_cast<double>(nn) * H * W;
     auto lin_tag = [&](int K, int N) {
@@ -1269,8 +1273,9 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
     });
     if constexpr (std::is_same<T, __nv_bfloat16>::value) {
       if (use_fused_tail_ && use_tail256_ && C == 256) {
-        // the same chain with one weight matrix resident at a time (attn_tail256_kernel)
-        Act<T> out = new_act(pool, nn, H, W, C, false);
+        // the same chain with one weight matrix resident at a time (attn_tail256_kernel); the block's output
+        // takes the attention output's buffer (a tile is stored over the rows it was loaded from)
+        Act<T> out = alias_acts_ ? av : new_act(pool, nn, H, W, C, false);
         const GemmW<T>&wp = gw_.at(p + ".proj"), &w1 = gw_.at(p + ".ff1"), &w2 = gw_.at(p + ".ff2");
         TailParams tp{};
         tp.geo = av.g;
@@ -1290,8 +1295,8 @@ void Engine<T>::build_unet_plan(Plan<T>& P) {
         return out;
       }
       if (use_fused_tail_ && (C == 64 || C == 128)) {
-        // out_proj + residual, LayerNorm, ff1 + GELU, ff2 + residual on chip (attn_tail.cuh)
-        Act<T> out = new_act(pool, nn, H, W, C, false);
+        // out_proj + residual, LayerNorm, ff1 + GELU, ff2 + residual on chip (attn_tail.cuh), stored over av
+        Act<T> out = alias_acts_ ? av : new_act(pool, nn, H, W, C, false);
         const GemmW<T>&wp = gw_.at(p + ".proj"), &w1 = gw_.at(p + ".ff1"), &w2 = gw_.at(p + ".ff2");
         TailParams tp{};
         tp.geo = av.g;
